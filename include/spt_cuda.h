@@ -1,0 +1,159 @@
+/*
+ * spt_cuda.h -- C ABI of the B200-native (sm_100a) path-tracing hot path that replaces, as a
+ * drop-in, the CPU tracers of ilia-glushchenko/SimplePathTracer.
+ *
+ * Plain C, plain pointers and sizes, no C++/torch types.  Citations are into the reference
+ * tree (/root/reference/...).  What each entry point stands in for:
+ *
+ *   spt_cuda_render        void RenderSegment(RenderSegmentData)      include/SingleThreadPathTracer.hpp:114
+ *                          void RenderSegmentTask(RenderSegmentData)  include/TaskBasedPathTracer.hpp:54
+ *                          (selected by SptParams.pass_cap: 0 / 10), including io::WritePixel into the
+ *                          caller's g_data (include/IOHelpers.hpp:17-22, include/Globals.hpp:19)
+ *   spt_cuda_accumulate    the same per-pixel sample loop, leaving linear (sum r, sum g, sum b, count)
+ *                          in a DEVICE float4 accumulator so that sample ranges / GPUs can be combined
+ *   spt_cuda_resolve       the normalise + io::WritePixel tail of both tracers
+ *                          (SingleThreadPathTracer.hpp:133-134, TaskBasedPathTracer.hpp:196-205)
+ *   spt_cuda_first_hit     cd::FindClosestIntersectionSphere + contact helpers on jitter-free pinhole rays
+ *   spt_cuda_closest_hit   cd::FindClosestIntersectionSphere  include/Collision.hpp:87-109
+ *   spt_cuda_set_scene     the SoA scene globals  include/Globals.hpp:31-37
+ *
+ * Inputs the reference keeps in globals (scene, camera, image size, sample/bounce counts) are passed
+ * explicitly; the host mirror include/CudaPathTracer.hpp gathers them from the globals.
+ *
+ * There is NO CPU fallback: every function fails with a non-zero status when no CUDA device is usable.
+ * All functions return 0 on success, otherwise an SptStatus / CUDA error code; text via spt_cuda_last_error().
+ */
+#ifndef SPT_CUDA_H
+#define SPT_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Material values: include/Definitions.hpp:7-13 (enum class Material : uint8_t) */
+enum { SPT_SKYBOX = 0, SPT_REFLECTIVE = 1, SPT_REFRACTIVE = 2, SPT_DIFFUSE = 3 };
+
+enum SptStatus {
+    SPT_OK = 0,
+    SPT_ERR_INVALID = -1,   /* bad argument (null pointer, empty segment outside the image, w != 0, ...) */
+    SPT_ERR_NO_DEVICE = -2, /* no usable CUDA device: there is no CPU path */
+    SPT_ERR_NO_SCENE = -3,  /* spt_cuda_set_scene has not been called */
+    SPT_ERR_CUDA = -4       /* a CUDA runtime call failed; see spt_cuda_last_error() */
+};
+
+/* Scene = the reference's SoA globals, host pointers laid out as the vectors' .data()
+ * (Vec4 = 4 packed floats with w = 0, include/Math.hpp:9-14). */
+typedef struct SptScene {
+    uint32_t n;               /* g_sphereNumber */
+    const float *centers4;    /* g_spheres   n*4 */
+    const float *radii;       /* g_radii     n   */
+    const uint8_t *materials; /* g_materials n   */
+    const float *colors4;     /* g_colors    n*4, 0..255 radiance scale */
+    const float *fuzz;        /* g_diffuses  n   */
+} SptScene;
+
+typedef struct SptCamera {
+    float view[16]; /* viewMatrix.array, row-major (Globals.hpp:21; built as Renderer.hpp:321). Row 3 must be 0. */
+    float eye[4];   /* eyePos (Globals.hpp:23), w = 0 */
+    float sky[4];   /* initColor (Globals.hpp:29) */
+} SptCamera;
+
+/* == RenderSegmentData (include/Definitions.hpp:15-21): half-open pixel rectangle */
+typedef struct SptSegment {
+    uint32_t yBegin, yEnd, xBegin, xEnd;
+} SptSegment;
+
+enum { SPT_VARIANT_MEGAKERNEL = 0, SPT_VARIANT_WAVEFRONT = 1 };
+enum {
+    SPT_FLAG_STRICT_LOOP = 1u, /* closest-hit evaluates every sphere with the reference's exact op sequence
+                                  (no conservative pre-filter); results are identical either way */
+    SPT_FLAG_COUNTERS = 2u     /* maintain SptCounters (cheap: per-thread registers, one atomic per warp) */
+};
+
+typedef struct SptParams {
+    uint32_t width, height;            /* g_width, g_height (Globals.hpp:14-15) */
+    uint32_t depth;                    /* g_bounces (Globals.hpp:12) */
+    uint32_t pass_cap;                 /* 0: RenderSegment semantics (specular recursion unbounded);
+                                          10: RenderSegmentTask's literal pass count (TaskBasedPathTracer.hpp:81):
+                                          paths alive after pass_cap specular events are dropped, not counted */
+    uint32_t sample_begin, sample_end; /* sample indices of every pixel; [0, g_samples) for a whole render */
+    uint64_t seed;                     /* counter-based RNG seed (replaces Random.hpp:88-89's clock seed) */
+    uint32_t variant;                  /* SPT_VARIANT_* */
+    uint32_t flags;                    /* SPT_FLAG_* */
+} SptParams;
+
+typedef struct SptCounters {
+    uint64_t segments; /* closest-hit calls (one per ray segment) */
+    uint64_t tests;    /* ray-sphere boolean tests the algorithm defines = segments * n */
+    uint64_t samples;  /* camera samples traced */
+    uint64_t dropped;  /* samples dropped by pass_cap */
+    uint64_t exact;    /* sphere evaluations that went through the exact (reference-order) sequence */
+} SptCounters;
+
+typedef struct SptTiming {
+    float trace_ms;     /* device time of the tracing kernel(s) of the last call, CUDA events on the context stream */
+    float resolve_ms;   /* device time of the resolve kernel of the last call */
+    uint32_t launches;  /* kernels launched by the last call */
+    uint32_t reserved;
+} SptTiming;
+
+typedef struct SptDeviceInfo {
+    char name[64];
+    int sm_count;
+    int cc_major, cc_minor;
+    int clock_khz;
+    size_t smem_per_block_optin;
+    size_t global_mem;
+} SptDeviceInfo;
+
+typedef struct SptContext SptContext;
+
+/* lifetime.  `device` is a CUDA ordinal.  The context owns a stream, the device copy of the scene and scratch. */
+int spt_cuda_create(SptContext **out, int device);
+void spt_cuda_destroy(SptContext *ctx);
+/* run on a caller stream (cudaStream_t passed as void*) instead of the context's own; NULL restores it */
+int spt_cuda_set_stream(SptContext *ctx, void *cuda_stream);
+int spt_cuda_device_info(SptContext *ctx, SptDeviceInfo *out);
+
+/* upload the scene (copied; no host pointer is retained) */
+int spt_cuda_set_scene(SptContext *ctx, const SptScene *scene);
+
+/* Whole hot path with HOST buffers: trace samples [sample_begin,sample_end) of every pixel of `seg`,
+ * normalise, gamma-encode and write the segment's bytes into rgb8 (width*height*3, the caller's g_data;
+ * pixel (x,y) lands at the reference's flipped slot, SingleThreadPathTracer.hpp:120).  accum4 (optional,
+ * width*height*4 floats, row y*width+x NOT flipped) receives the linear sums and counts. Blocking. */
+int spt_cuda_render(SptContext *ctx, const SptCamera *cam, const SptParams *params, SptSegment seg,
+                    uint8_t *rgb8, float *accum4);
+
+/* Device-buffer pieces (asynchronous on the context stream):
+ * d_accum4: width*height float4, caller-zeroed; each call ADDS its samples. */
+int spt_cuda_accumulate(SptContext *ctx, const SptCamera *cam, const SptParams *params, SptSegment seg,
+                        float *d_accum4);
+int spt_cuda_resolve(SptContext *ctx, const float *d_accum4, uint32_t width, uint32_t height, SptSegment seg,
+                     uint8_t *d_rgb8);
+int spt_cuda_synchronize(SptContext *ctx);
+
+/* Parity probes (host buffers, blocking).  Outputs are indexed (x-xBegin) + (y-yBegin)*(xEnd-xBegin). */
+int spt_cuda_first_hit(SptContext *ctx, const SptCamera *cam, uint32_t width, uint32_t height, SptSegment seg,
+                       uint32_t flags, uint32_t *idx, float *t, float *normal3);
+int spt_cuda_closest_hit(SptContext *ctx, uint32_t count, const float *dir3, const float *org3, uint32_t flags,
+                         uint32_t *idx);
+
+int spt_cuda_get_counters(SptContext *ctx, SptCounters *out); /* accumulated since the last reset */
+int spt_cuda_reset_counters(SptContext *ctx);
+int spt_cuda_get_timing(SptContext *ctx, SptTiming *out);
+
+/* FP32 CUDA-core peak of this device, measured with dependent-FMA chains on all SMs (the roofline
+ * denominator BASELINE.md section 4 asks for).  scalar: fma.rn.f32; packed: fma.rn.f32x2. */
+int spt_cuda_measure_fp32_peak(SptContext *ctx, float *tflops_scalar, float *tflops_packed);
+
+const char *spt_cuda_last_error(void);
+const char *spt_cuda_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPT_CUDA_H */

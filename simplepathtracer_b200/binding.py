@@ -1,0 +1,340 @@
+"""ctypes binding of include/spt_cuda.h (plumbing; see package docstring)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import shutil
+import subprocess
+from dataclasses import dataclass, field
+from typing import Optional, Sequence
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+LIB_NAME = "libspt_cuda.so"
+
+MEGAKERNEL, WAVEFRONT = 0, 1
+FLAG_STRICT_LOOP, FLAG_COUNTERS = 1, 2
+SKYBOX, REFLECTIVE, REFRACTIVE, DIFFUSE = 0, 1, 2, 3  # include/Definitions.hpp:7-13
+
+f32p = C.POINTER(C.c_float)
+u32p = C.POINTER(C.c_uint32)
+u8p = C.POINTER(C.c_uint8)
+
+
+class SptError(RuntimeError):
+    pass
+
+
+def library_path() -> str:
+    return os.path.join(HERE, LIB_NAME)
+
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-lineinfo", "-O3", "-std=c++17",
+    "--fmad=false",  # belt and braces: every rounded op is spelled out with __f*_rn as well
+    "-Xcompiler", "-fPIC", "-shared",
+]
+
+
+def build_library(verbose: bool = False, force: bool = False) -> str:
+    """Compile the CUDA library for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
+    out = library_path()
+    srcs = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cuh", ".cpp", ".hpp", ".h"))]
+    srcs += [os.path.join(ROOT, "include", f) for f in sorted(os.listdir(os.path.join(ROOT, "include"))) if f.endswith((".h", ".hpp"))]
+    hostdir = os.path.join(ROOT, "include", "spt_host")
+    if os.path.isdir(hostdir):
+        srcs += [os.path.join(hostdir, f) for f in sorted(os.listdir(hostdir))]
+    if not force and os.path.exists(out) and all(os.path.getmtime(out) >= os.path.getmtime(s) for s in srcs):
+        return out
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    units = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cpp"))]
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-I", os.path.join(ROOT, "include")] + units + ["-o", out]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise SptError("nvcc failed:\n" + res.stdout + res.stderr)
+    if verbose:
+        print(res.stderr)
+    return out
+
+
+@dataclass
+class Scene:
+    """SoA scene laid out as the reference globals (include/Globals.hpp:31-37)."""
+
+    centers: np.ndarray  # (n,4) f32  g_spheres
+    radii: np.ndarray  # (n,)  f32  g_radii
+    materials: np.ndarray  # (n,)  u8   g_materials
+    colors: np.ndarray  # (n,4) f32  g_colors
+    fuzz: np.ndarray  # (n,)  f32  g_diffuses
+
+    @property
+    def n(self) -> int:
+        return int(self.radii.shape[0])
+
+    @staticmethod
+    def of(obj) -> "Scene":
+        return Scene(
+            np.ascontiguousarray(obj.centers, np.float32).reshape(-1, 4),
+            np.ascontiguousarray(obj.radii, np.float32).reshape(-1),
+            np.ascontiguousarray(obj.materials, np.uint8).reshape(-1),
+            np.ascontiguousarray(obj.colors, np.float32).reshape(-1, 4),
+            np.ascontiguousarray(obj.fuzz, np.float32).reshape(-1),
+        )
+
+    def save(self, path: str) -> None:
+        np.savez_compressed(path, centers=self.centers, radii=self.radii, materials=self.materials, colors=self.colors, fuzz=self.fuzz)
+
+    @staticmethod
+    def load(path: str) -> "Scene":
+        z = np.load(path)
+        return Scene.of(type("S", (), {k: z[k] for k in ("centers", "radii", "materials", "colors", "fuzz")}))
+
+
+@dataclass
+class Camera:
+    """viewMatrix / eyePos / initColor (include/Globals.hpp:21-29); defaults = the reference's camera."""
+
+    view: np.ndarray = field(default_factory=lambda: np.diag([1, 1, 1, 0]).astype(np.float32))
+    eye: np.ndarray = field(default_factory=lambda: np.array([0, 1, -3, 0], np.float32))
+    sky: np.ndarray = field(default_factory=lambda: np.array([137, 207, 240, 0], np.float32))
+
+    @staticmethod
+    def of(obj) -> "Camera":
+        return Camera(
+            np.ascontiguousarray(obj.view, np.float32).reshape(4, 4),
+            np.ascontiguousarray(obj.eye, np.float32).reshape(4),
+            np.ascontiguousarray(obj.sky, np.float32).reshape(4),
+        )
+
+
+class Segment(C.Structure):
+    """== RenderSegmentData (include/Definitions.hpp:15-21)"""
+
+    _fields_ = [("yBegin", C.c_uint32), ("yEnd", C.c_uint32), ("xBegin", C.c_uint32), ("xEnd", C.c_uint32)]
+
+
+class _CScene(C.Structure):
+    _fields_ = [("n", C.c_uint32), ("centers4", f32p), ("radii", f32p), ("materials", u8p), ("colors4", f32p), ("fuzz", f32p)]
+
+
+class _CCamera(C.Structure):
+    _fields_ = [("view", C.c_float * 16), ("eye", C.c_float * 4), ("sky", C.c_float * 4)]
+
+
+class _CParams(C.Structure):
+    _fields_ = [
+        ("width", C.c_uint32),
+        ("height", C.c_uint32),
+        ("depth", C.c_uint32),
+        ("pass_cap", C.c_uint32),
+        ("sample_begin", C.c_uint32),
+        ("sample_end", C.c_uint32),
+        ("seed", C.c_uint64),
+        ("variant", C.c_uint32),
+        ("flags", C.c_uint32),
+    ]
+
+
+class Counters(C.Structure):
+    _fields_ = [("segments", C.c_uint64), ("tests", C.c_uint64), ("samples", C.c_uint64), ("dropped", C.c_uint64), ("exact", C.c_uint64)]
+
+    def asdict(self):
+        return {k: int(getattr(self, k)) for k, _ in self._fields_}
+
+
+class Timing(C.Structure):
+    _fields_ = [("trace_ms", C.c_float), ("resolve_ms", C.c_float), ("launches", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class DeviceInfo(C.Structure):
+    _fields_ = [
+        ("name", C.c_char * 64),
+        ("sm_count", C.c_int),
+        ("cc_major", C.c_int),
+        ("cc_minor", C.c_int),
+        ("clock_khz", C.c_int),
+        ("smem_per_block_optin", C.c_size_t),
+        ("global_mem", C.c_size_t),
+    ]
+
+
+EXPORTS = [
+    "spt_cuda_create", "spt_cuda_destroy", "spt_cuda_set_stream", "spt_cuda_device_info", "spt_cuda_set_scene",
+    "spt_cuda_render", "spt_cuda_accumulate", "spt_cuda_resolve", "spt_cuda_synchronize", "spt_cuda_first_hit",
+    "spt_cuda_closest_hit", "spt_cuda_get_counters", "spt_cuda_reset_counters", "spt_cuda_get_timing",
+    "spt_cuda_measure_fp32_peak", "spt_cuda_last_error", "spt_cuda_version",
+]
+
+_LIB = None
+
+
+def load_library():
+    """dlopen the in-tree CUDA library.  Raises (never falls back) when it is missing."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = library_path()
+    if not os.path.exists(path):
+        raise SptError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (needs nvcc). "
+                       "There is no CPU fallback.")
+    L = C.CDLL(path)
+    L.spt_cuda_last_error.restype = C.c_char_p
+    L.spt_cuda_version.restype = C.c_char_p
+    L.spt_cuda_create.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+    L.spt_cuda_destroy.argtypes = [C.c_void_p]
+    L.spt_cuda_destroy.restype = None
+    L.spt_cuda_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+    L.spt_cuda_device_info.argtypes = [C.c_void_p, C.POINTER(DeviceInfo)]
+    L.spt_cuda_set_scene.argtypes = [C.c_void_p, C.POINTER(_CScene)]
+    L.spt_cuda_render.argtypes = [C.c_void_p, C.POINTER(_CCamera), C.POINTER(_CParams), Segment, C.c_void_p, C.c_void_p]
+    L.spt_cuda_accumulate.argtypes = [C.c_void_p, C.POINTER(_CCamera), C.POINTER(_CParams), Segment, C.c_void_p]
+    L.spt_cuda_resolve.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, Segment, C.c_void_p]
+    L.spt_cuda_synchronize.argtypes = [C.c_void_p]
+    L.spt_cuda_first_hit.argtypes = [C.c_void_p, C.POINTER(_CCamera), C.c_uint32, C.c_uint32, Segment, C.c_uint32, C.c_void_p,
+                                     C.c_void_p, C.c_void_p]
+    L.spt_cuda_closest_hit.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+    L.spt_cuda_get_counters.argtypes = [C.c_void_p, C.POINTER(Counters)]
+    L.spt_cuda_reset_counters.argtypes = [C.c_void_p]
+    L.spt_cuda_get_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
+    L.spt_cuda_measure_fp32_peak.argtypes = [C.c_void_p, f32p, f32p]
+    _LIB = L
+    return L
+
+
+def _ccam(cam: Camera) -> _CCamera:
+    c = _CCamera()
+    c.view[:] = [float(v) for v in cam.view.reshape(-1)]
+    c.eye[:] = [float(v) for v in cam.eye.reshape(-1)]
+    c.sky[:] = [float(v) for v in cam.sky.reshape(-1)]
+    return c
+
+
+def _seg(seg, width, height) -> Segment:
+    if seg is None:
+        return Segment(0, height, 0, width)  # RenderImage's {0, g_height, 0, g_width} (Renderer.hpp:306)
+    if isinstance(seg, Segment):
+        return seg
+    return Segment(*[int(v) for v in seg])
+
+
+def _devptr(x) -> int:
+    """Device pointer of a torch tensor / anything with data_ptr(), or a raw int."""
+    return int(x.data_ptr()) if hasattr(x, "data_ptr") else int(x)
+
+
+class PathTracer:
+    """One context on one GPU: RenderSegment / RenderSegmentTask as CUDA (include/spt_cuda.h)."""
+
+    def __init__(self, device: int = 0):
+        self.L = load_library()
+        h = C.c_void_p()
+        self._check(self.L.spt_cuda_create(C.byref(h), device))
+        self.h = h
+        self.device = device
+        self.scene: Optional[Scene] = None
+
+    def _check(self, rc: int):
+        if rc != 0:
+            raise SptError(f"spt_cuda error {rc}: {self.L.spt_cuda_last_error().decode()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.spt_cuda_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ------------------------------------------------------------------
+    def device_info(self) -> dict:
+        d = DeviceInfo()
+        self._check(self.L.spt_cuda_device_info(self.h, C.byref(d)))
+        return {"name": d.name.decode(), "sm_count": d.sm_count, "cc": (d.cc_major, d.cc_minor), "clock_khz": d.clock_khz,
+                "smem_per_block_optin": d.smem_per_block_optin, "global_mem": d.global_mem}
+
+    def set_stream(self, cuda_stream: int):
+        self._check(self.L.spt_cuda_set_stream(self.h, C.c_void_p(cuda_stream)))
+
+    def set_scene(self, scene) -> None:
+        sc = Scene.of(scene)
+        cs = _CScene(sc.n, sc.centers.ctypes.data_as(f32p), sc.radii.ctypes.data_as(f32p), sc.materials.ctypes.data_as(u8p),
+                     sc.colors.ctypes.data_as(f32p), sc.fuzz.ctypes.data_as(f32p))
+        self._check(self.L.spt_cuda_set_scene(self.h, C.byref(cs)))
+        self.scene = sc
+
+    def _params(self, width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags) -> _CParams:
+        return _CParams(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags)
+
+    def render(self, cam, width, height, spp, depth, pass_cap=0, seed=1, seg=None, sample_begin=0, variant=MEGAKERNEL,
+               flags=0, rgb8: Optional[np.ndarray] = None, want_accum: bool = False):
+        """Whole hot path with host buffers (spt_cuda_render).  Returns (rgb8 (H,W,3) u8, accum (H,W,4) f32 or None)."""
+        cm = _ccam(Camera.of(cam))
+        if rgb8 is None:
+            rgb8 = np.zeros((height, width, 3), np.uint8)
+        accum = np.zeros((height, width, 4), np.float32) if want_accum else None
+        p = self._params(width, height, depth, pass_cap, sample_begin, sample_begin + spp, seed, variant, flags)
+        self._check(self.L.spt_cuda_render(self.h, C.byref(cm), C.byref(p), _seg(seg, width, height), rgb8.ctypes.data,
+                                           accum.ctypes.data if accum is not None else None))
+        return rgb8, accum
+
+    def accumulate(self, cam, width, height, sample_begin, sample_end, depth, d_accum, pass_cap=0, seed=1, seg=None,
+                   variant=MEGAKERNEL, flags=0):
+        """Adds samples [sample_begin, sample_end) into a DEVICE float4 accumulator (async)."""
+        cm = _ccam(Camera.of(cam))
+        p = self._params(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags)
+        self._check(self.L.spt_cuda_accumulate(self.h, C.byref(cm), C.byref(p), _seg(seg, width, height), C.c_void_p(_devptr(d_accum))))
+
+    def resolve(self, d_accum, width, height, d_rgb8, seg=None):
+        self._check(self.L.spt_cuda_resolve(self.h, C.c_void_p(_devptr(d_accum)), width, height, _seg(seg, width, height),
+                                            C.c_void_p(_devptr(d_rgb8))))
+
+    def synchronize(self):
+        self._check(self.L.spt_cuda_synchronize(self.h))
+
+    def first_hit(self, cam, width, height, seg=None, flags=0):
+        cm = _ccam(Camera.of(cam))
+        s = _seg(seg, width, height)
+        npx = (s.yEnd - s.yBegin) * (s.xEnd - s.xBegin)
+        idx = np.empty(npx, np.uint32)
+        t = np.empty(npx, np.float32)
+        nrm = np.empty((npx, 3), np.float32)
+        self._check(self.L.spt_cuda_first_hit(self.h, C.byref(cm), width, height, s, flags, idx.ctypes.data, t.ctypes.data, nrm.ctypes.data))
+        return idx, t, nrm
+
+    def closest_hit(self, dirs: Sequence, orgs: Sequence, flags=0):
+        dirs = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+        orgs = np.ascontiguousarray(orgs, np.float32).reshape(-1, 3)
+        idx = np.empty(dirs.shape[0], np.uint32)
+        self._check(self.L.spt_cuda_closest_hit(self.h, dirs.shape[0], dirs.ctypes.data, orgs.ctypes.data, flags, idx.ctypes.data))
+        return idx
+
+    def counters(self) -> dict:
+        c = Counters()
+        self._check(self.L.spt_cuda_get_counters(self.h, C.byref(c)))
+        return c.asdict()
+
+    def reset_counters(self):
+        self._check(self.L.spt_cuda_reset_counters(self.h))
+
+    def timing(self) -> dict:
+        t = Timing()
+        self._check(self.L.spt_cuda_get_timing(self.h, C.byref(t)))
+        return {"trace_ms": float(t.trace_ms), "resolve_ms": float(t.resolve_ms), "launches": int(t.launches)}
+
+    def measure_fp32_peak(self):
+        a, b = C.c_float(), C.c_float()
+        self._check(self.L.spt_cuda_measure_fp32_peak(self.h, C.byref(a), C.byref(b)))
+        return float(a.value), float(b.value)

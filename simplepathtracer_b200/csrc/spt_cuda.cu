@@ -1,0 +1,550 @@
+// spt_cuda.cu -- C ABI (include/spt_cuda.h) over the sm_100a kernels.  No CPU fallback exists:
+// every entry point returns an error when CUDA is unusable.
+#include "../../include/spt_cuda.h"
+#include "spt_kernels.cuh"
+
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+namespace
+{
+thread_local std::string g_lastError;
+
+int fail(int code, const char *what, cudaError_t ce = cudaSuccess)
+{
+    char buf[512];
+    if (ce != cudaSuccess)
+        snprintf(buf, sizeof(buf), "%s: %s (%s)", what, cudaGetErrorString(ce), cudaGetErrorName(ce));
+    else
+        snprintf(buf, sizeof(buf), "%s", what);
+    g_lastError = buf;
+    return code;
+}
+
+#define SPT_CUDA_CHECK(call)                                      \
+    do                                                            \
+    {                                                             \
+        cudaError_t const ce_ = (call);                           \
+        if (ce_ != cudaSuccess)                                   \
+            return fail(SPT_ERR_CUDA, #call, ce_);                \
+    } while (0)
+} // namespace
+
+struct SptContext
+{
+    int device = 0;
+    cudaDeviceProp prop{};
+    cudaStream_t ownStream = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    std::mutex lock; // the reference calls its tracers from several host threads (Renderer.hpp:282-290)
+
+    uint32_t n = 0;
+    float4 *dGeom = nullptr;
+    float4 *dShade = nullptr;
+    uint8_t *dMat = nullptr;
+
+    unsigned long long *dCounters = nullptr;
+    SptTiming timing{};
+
+    // scratch for the host-buffer entry points
+    float4 *dAccum = nullptr;
+    uint8_t *dRgb = nullptr;
+    size_t accumPixels = 0;
+    void *dProbe = nullptr;
+    size_t probeBytes = 0;
+    size_t maxSmemOptin = 0;
+};
+
+namespace
+{
+int ensure_scratch(SptContext *c, size_t pixels)
+{
+    if (pixels <= c->accumPixels)
+        return SPT_OK;
+    if (c->dAccum)
+        cudaFree(c->dAccum);
+    if (c->dRgb)
+        cudaFree(c->dRgb);
+    c->dAccum = nullptr;
+    c->dRgb = nullptr;
+    c->accumPixels = 0;
+    SPT_CUDA_CHECK(cudaMalloc(&c->dAccum, pixels * sizeof(float4)));
+    SPT_CUDA_CHECK(cudaMalloc(&c->dRgb, pixels * 3));
+    c->accumPixels = pixels;
+    return SPT_OK;
+}
+
+int ensure_probe(SptContext *c, size_t bytes)
+{
+    if (bytes <= c->probeBytes)
+        return SPT_OK;
+    if (c->dProbe)
+        cudaFree(c->dProbe);
+    c->dProbe = nullptr;
+    c->probeBytes = 0;
+    SPT_CUDA_CHECK(cudaMalloc(&c->dProbe, bytes));
+    c->probeBytes = bytes;
+    return SPT_OK;
+}
+
+int check_camera(const SptCamera *cam)
+{
+    if (!cam)
+        return fail(SPT_ERR_INVALID, "camera is null");
+    if (cam->view[12] != 0.f || cam->view[13] != 0.f || cam->view[14] != 0.f || cam->view[15] != 0.f || cam->view[3] != 0.f ||
+        cam->view[7] != 0.f || cam->view[11] != 0.f || cam->eye[3] != 0.f)
+        return fail(SPT_ERR_INVALID, "camera: view row 3 / column 3 and eye.w must be 0 (as Renderer.hpp:321 produces)");
+    return SPT_OK;
+}
+
+void fill_camera(spt::CameraConst &d, const SptCamera *cam)
+{
+    for (int r = 0; r < 3; ++r)
+        for (int k = 0; k < 4; ++k)
+            d.view[4 * r + k] = cam->view[4 * r + k];
+    for (int k = 0; k < 3; ++k)
+    {
+        d.eye[k] = cam->eye[k];
+        d.sky[k] = cam->sky[k];
+    }
+}
+
+int check_segment(uint32_t width, uint32_t height, SptSegment s)
+{
+    if (width == 0 || height == 0 || uint64_t(width) * height * 3u > 0xFFFFFFFFull)
+        return fail(SPT_ERR_INVALID, "image size out of range");
+    if (s.xBegin > s.xEnd || s.yBegin > s.yEnd || s.xEnd > width || s.yEnd > height)
+        return fail(SPT_ERR_INVALID, "segment outside the image");
+    return SPT_OK;
+}
+
+int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptSegment seg, float4 *dAccum)
+{
+    if (c->n == 0 || !c->dGeom)
+        return fail(SPT_ERR_NO_SCENE, "spt_cuda_set_scene has not been called");
+    if (prm->variant != SPT_VARIANT_MEGAKERNEL)
+        return fail(SPT_ERR_INVALID, "unknown variant");
+    c->timing.trace_ms = 0.f;
+    c->timing.launches = 0;
+    uint32_t const segW = seg.xEnd - seg.xBegin, segH = seg.yEnd - seg.yBegin;
+    if (segW == 0 || segH == 0 || prm->sample_end <= prm->sample_begin)
+        return SPT_OK;
+
+    spt::TraceParams p{};
+    fill_camera(p.cam, cam);
+    p.width = prm->width;
+    p.height = prm->height;
+    p.yBegin = seg.yBegin;
+    p.yEnd = seg.yEnd;
+    p.xBegin = seg.xBegin;
+    p.xEnd = seg.xEnd;
+    p.sampleBegin = prm->sample_begin;
+    p.sampleEnd = prm->sample_end;
+    p.depth = prm->depth;
+    p.passCap = prm->pass_cap;
+    p.seed = prm->seed;
+    p.n = c->n;
+    p.geom = c->dGeom;
+    p.shade = c->dShade;
+    p.mat = c->dMat;
+    p.accum = dAccum;
+    p.counters = (prm->flags & SPT_FLAG_COUNTERS) ? c->dCounters : nullptr;
+
+    dim3 const grid((segW + spt::kTileW - 1) / spt::kTileW, (segH + spt::kTileH - 1) / spt::kTileH);
+    dim3 const block(spt::kBlockThreads);
+    size_t const geomBytes = size_t(c->n) * sizeof(float4);
+    bool const inSmem = geomBytes + 1024 <= c->maxSmemOptin;
+
+    SPT_CUDA_CHECK(cudaEventRecord(c->ev[0], c->stream));
+    if (inSmem)
+    {
+        auto kernel = spt::trace_megakernel<true, true>;
+        SPT_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(geomBytes)));
+        kernel<<<grid, block, geomBytes, c->stream>>>(p);
+    }
+    else
+    {
+        auto kernel = spt::trace_megakernel<false, true>;
+        kernel<<<grid, block, 0, c->stream>>>(p);
+    }
+    SPT_CUDA_CHECK(cudaGetLastError());
+    SPT_CUDA_CHECK(cudaEventRecord(c->ev[1], c->stream));
+    c->timing.launches += 1;
+    return SPT_OK;
+}
+
+int launch_resolve(SptContext *c, const float4 *dAccum, uint32_t width, uint32_t height, SptSegment seg, uint8_t *dRgb)
+{
+    uint32_t const segW = seg.xEnd - seg.xBegin, segH = seg.yEnd - seg.yBegin;
+    c->timing.resolve_ms = 0.f;
+    if (segW == 0 || segH == 0)
+        return SPT_OK;
+    dim3 const block(128);
+    dim3 const grid((segW + block.x - 1) / block.x, segH);
+    SPT_CUDA_CHECK(cudaEventRecord(c->ev[2], c->stream));
+    spt::resolve_kernel<<<grid, block, 0, c->stream>>>(dAccum, width, height, seg.yBegin, seg.yEnd, seg.xBegin, seg.xEnd, dRgb);
+    SPT_CUDA_CHECK(cudaGetLastError());
+    SPT_CUDA_CHECK(cudaEventRecord(c->ev[3], c->stream));
+    c->timing.launches += 1;
+    return SPT_OK;
+}
+} // namespace
+
+extern "C"
+{
+
+const char *spt_cuda_last_error(void) { return g_lastError.c_str(); }
+const char *spt_cuda_version(void) { return "simplepathtracer_b200 0.1 (sm_100a)"; }
+
+int spt_cuda_create(SptContext **out, int device)
+{
+    if (!out)
+        return fail(SPT_ERR_INVALID, "out is null");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t ce = cudaGetDeviceCount(&count);
+    if (ce != cudaSuccess || count <= 0)
+        return fail(SPT_ERR_NO_DEVICE, "no CUDA device is usable; this library has no CPU path", ce);
+    if (device < 0 || device >= count)
+        return fail(SPT_ERR_INVALID, "device ordinal out of range");
+    SPT_CUDA_CHECK(cudaSetDevice(device));
+    SptContext *c = new SptContext();
+    c->device = device;
+    ce = cudaGetDeviceProperties(&c->prop, device);
+    if (ce == cudaSuccess)
+        ce = cudaStreamCreateWithFlags(&c->ownStream, cudaStreamNonBlocking);
+    for (int i = 0; i < 4 && ce == cudaSuccess; ++i)
+        ce = cudaEventCreate(&c->ev[i]);
+    if (ce == cudaSuccess)
+        ce = cudaMalloc(&c->dCounters, 8 * sizeof(unsigned long long));
+    if (ce == cudaSuccess)
+        ce = cudaMemset(c->dCounters, 0, 8 * sizeof(unsigned long long));
+    if (ce != cudaSuccess)
+    {
+        delete c;
+        return fail(SPT_ERR_CUDA, "context creation", ce);
+    }
+    c->stream = c->ownStream;
+    c->maxSmemOptin = c->prop.sharedMemPerBlockOptin;
+    *out = c;
+    return SPT_OK;
+}
+
+void spt_cuda_destroy(SptContext *c)
+{
+    if (!c)
+        return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    cudaFree(c->dGeom);
+    cudaFree(c->dShade);
+    cudaFree(c->dMat);
+    cudaFree(c->dCounters);
+    cudaFree(c->dAccum);
+    cudaFree(c->dRgb);
+    cudaFree(c->dProbe);
+    for (auto &e : c->ev)
+        if (e)
+            cudaEventDestroy(e);
+    if (c->ownStream)
+        cudaStreamDestroy(c->ownStream);
+    delete c;
+}
+
+int spt_cuda_set_stream(SptContext *c, void *cuda_stream)
+{
+    if (!c)
+        return fail(SPT_ERR_INVALID, "context is null");
+    std::lock_guard<std::mutex> g(c->lock);
+    c->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : c->ownStream;
+    return SPT_OK;
+}
+
+int spt_cuda_device_info(SptContext *c, SptDeviceInfo *out)
+{
+    if (!c || !out)
+        return fail(SPT_ERR_INVALID, "null argument");
+    memset(out, 0, sizeof(*out));
+    strncpy(out->name, c->prop.name, sizeof(out->name) - 1);
+    out->sm_count = c->prop.multiProcessorCount;
+    out->cc_major = c->prop.major;
+    out->cc_minor = c->prop.minor;
+    int khz = 0;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, c->device);
+    out->clock_khz = khz;
+    out->smem_per_block_optin = c->prop.sharedMemPerBlockOptin;
+    out->global_mem = c->prop.totalGlobalMem;
+    return SPT_OK;
+}
+
+int spt_cuda_set_scene(SptContext *c, const SptScene *s)
+{
+    if (!c || !s)
+        return fail(SPT_ERR_INVALID, "null argument");
+    if (s->n == 0 || !s->centers4 || !s->radii || !s->materials || !s->colors4 || !s->fuzz)
+        return fail(SPT_ERR_INVALID, "scene arrays must be non-null and n > 0");
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    std::vector<float4> geom(s->n), shade(s->n);
+    for (uint32_t i = 0; i < s->n; ++i)
+    {
+        if (s->centers4[4 * i + 3] != 0.f)
+            return fail(SPT_ERR_INVALID, "sphere centre w must be 0 (Vec4{x,y,z} initialisers, SceneGenerators.hpp)");
+        geom[i] = make_float4(s->centers4[4 * i], s->centers4[4 * i + 1], s->centers4[4 * i + 2], s->radii[i]);
+        shade[i] = make_float4(s->colors4[4 * i], s->colors4[4 * i + 1], s->colors4[4 * i + 2], s->fuzz[i]);
+    }
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    cudaFree(c->dGeom);
+    cudaFree(c->dShade);
+    cudaFree(c->dMat);
+    c->dGeom = c->dShade = nullptr;
+    c->dMat = nullptr;
+    c->n = 0;
+    SPT_CUDA_CHECK(cudaMalloc(&c->dGeom, s->n * sizeof(float4)));
+    SPT_CUDA_CHECK(cudaMalloc(&c->dShade, s->n * sizeof(float4)));
+    SPT_CUDA_CHECK(cudaMalloc(&c->dMat, s->n));
+    SPT_CUDA_CHECK(cudaMemcpy(c->dGeom, geom.data(), s->n * sizeof(float4), cudaMemcpyHostToDevice));
+    SPT_CUDA_CHECK(cudaMemcpy(c->dShade, shade.data(), s->n * sizeof(float4), cudaMemcpyHostToDevice));
+    SPT_CUDA_CHECK(cudaMemcpy(c->dMat, s->materials, s->n, cudaMemcpyHostToDevice));
+    c->n = s->n;
+    return SPT_OK;
+}
+
+int spt_cuda_accumulate(SptContext *c, const SptCamera *cam, const SptParams *prm, SptSegment seg, float *d_accum4)
+{
+    if (!c || !prm || !d_accum4)
+        return fail(SPT_ERR_INVALID, "null argument");
+    int rc = check_camera(cam);
+    if (rc)
+        return rc;
+    rc = check_segment(prm->width, prm->height, seg);
+    if (rc)
+        return rc;
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    return launch_trace(c, cam, prm, seg, reinterpret_cast<float4 *>(d_accum4));
+}
+
+int spt_cuda_resolve(SptContext *c, const float *d_accum4, uint32_t width, uint32_t height, SptSegment seg, uint8_t *d_rgb8)
+{
+    if (!c || !d_accum4 || !d_rgb8)
+        return fail(SPT_ERR_INVALID, "null argument");
+    int const rc = check_segment(width, height, seg);
+    if (rc)
+        return rc;
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    return launch_resolve(c, reinterpret_cast<const float4 *>(d_accum4), width, height, seg, d_rgb8);
+}
+
+int spt_cuda_synchronize(SptContext *c)
+{
+    if (!c)
+        return fail(SPT_ERR_INVALID, "context is null");
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    return SPT_OK;
+}
+
+int spt_cuda_render(SptContext *c, const SptCamera *cam, const SptParams *prm, SptSegment seg, uint8_t *rgb8, float *accum4)
+{
+    if (!c || !prm || !rgb8)
+        return fail(SPT_ERR_INVALID, "null argument");
+    int rc = check_camera(cam);
+    if (rc)
+        return rc;
+    rc = check_segment(prm->width, prm->height, seg);
+    if (rc)
+        return rc;
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    uint32_t const W = prm->width, H = prm->height;
+    uint32_t const segW = seg.xEnd - seg.xBegin, segH = seg.yEnd - seg.yBegin;
+    if (segW == 0 || segH == 0)
+        return SPT_OK;
+    rc = ensure_scratch(c, size_t(W) * H);
+    if (rc)
+        return rc;
+    // zero the accumulator rows of the segment
+    SPT_CUDA_CHECK(cudaMemset2DAsync(c->dAccum + size_t(seg.yBegin) * W + seg.xBegin, size_t(W) * sizeof(float4), 0,
+                                     size_t(segW) * sizeof(float4), segH, c->stream));
+    rc = launch_trace(c, cam, prm, seg, c->dAccum);
+    if (rc)
+        return rc;
+    uint32_t const traceLaunches = c->timing.launches;
+    rc = launch_resolve(c, c->dAccum, W, H, seg, c->dRgb);
+    if (rc)
+        return rc;
+    c->timing.launches += traceLaunches;
+    // pixel (x,y) lives in byte row H-1-y: copy the segment's rows back into the caller's g_data
+    uint32_t const rowTop = H - seg.yEnd; // flipped
+    SPT_CUDA_CHECK(cudaMemcpy2DAsync(rgb8 + (size_t(rowTop) * W + seg.xBegin) * 3, size_t(W) * 3,
+                                     c->dRgb + (size_t(rowTop) * W + seg.xBegin) * 3, size_t(W) * 3, size_t(segW) * 3, segH,
+                                     cudaMemcpyDeviceToHost, c->stream));
+    if (accum4)
+        SPT_CUDA_CHECK(cudaMemcpy2DAsync(accum4 + (size_t(seg.yBegin) * W + seg.xBegin) * 4, size_t(W) * sizeof(float4),
+                                         c->dAccum + size_t(seg.yBegin) * W + seg.xBegin, size_t(W) * sizeof(float4),
+                                         size_t(segW) * sizeof(float4), segH, cudaMemcpyDeviceToHost, c->stream));
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    return SPT_OK;
+}
+
+int spt_cuda_first_hit(SptContext *c, const SptCamera *cam, uint32_t width, uint32_t height, SptSegment seg, uint32_t flags,
+                       uint32_t *idx, float *t, float *normal3)
+{
+    (void)flags;
+    if (!c || !idx || !t || !normal3)
+        return fail(SPT_ERR_INVALID, "null argument");
+    int rc = check_camera(cam);
+    if (rc)
+        return rc;
+    rc = check_segment(width, height, seg);
+    if (rc)
+        return rc;
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    if (c->n == 0)
+        return fail(SPT_ERR_NO_SCENE, "spt_cuda_set_scene has not been called");
+    size_t const count = size_t(seg.xEnd - seg.xBegin) * (seg.yEnd - seg.yBegin);
+    if (count == 0)
+        return SPT_OK;
+    rc = ensure_probe(c, count * 20);
+    if (rc)
+        return rc;
+    spt::FirstHitParams p{};
+    fill_camera(p.cam, cam);
+    p.width = width;
+    p.height = height;
+    p.yBegin = seg.yBegin;
+    p.yEnd = seg.yEnd;
+    p.xBegin = seg.xBegin;
+    p.xEnd = seg.xEnd;
+    p.n = c->n;
+    p.geom = c->dGeom;
+    p.idx = static_cast<uint32_t *>(c->dProbe);
+    p.t = reinterpret_cast<float *>(p.idx + count);
+    p.normal3 = p.t + count;
+    spt::first_hit_kernel<<<unsigned((count + 255) / 256), 256, 0, c->stream>>>(p);
+    SPT_CUDA_CHECK(cudaGetLastError());
+    SPT_CUDA_CHECK(cudaMemcpyAsync(idx, p.idx, count * 4, cudaMemcpyDeviceToHost, c->stream));
+    SPT_CUDA_CHECK(cudaMemcpyAsync(t, p.t, count * 4, cudaMemcpyDeviceToHost, c->stream));
+    SPT_CUDA_CHECK(cudaMemcpyAsync(normal3, p.normal3, count * 12, cudaMemcpyDeviceToHost, c->stream));
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    return SPT_OK;
+}
+
+int spt_cuda_closest_hit(SptContext *c, uint32_t count, const float *dir3, const float *org3, uint32_t flags, uint32_t *idx)
+{
+    (void)flags;
+    if (!c || !dir3 || !org3 || !idx)
+        return fail(SPT_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    if (c->n == 0)
+        return fail(SPT_ERR_NO_SCENE, "spt_cuda_set_scene has not been called");
+    if (count == 0)
+        return SPT_OK;
+    int rc = ensure_probe(c, size_t(count) * 28);
+    if (rc)
+        return rc;
+    float *dDir = static_cast<float *>(c->dProbe);
+    float *dOrg = dDir + size_t(count) * 3;
+    uint32_t *dIdx = reinterpret_cast<uint32_t *>(dOrg + size_t(count) * 3);
+    SPT_CUDA_CHECK(cudaMemcpyAsync(dDir, dir3, size_t(count) * 12, cudaMemcpyHostToDevice, c->stream));
+    SPT_CUDA_CHECK(cudaMemcpyAsync(dOrg, org3, size_t(count) * 12, cudaMemcpyHostToDevice, c->stream));
+    spt::closest_hit_kernel<<<(count + 255) / 256, 256, 0, c->stream>>>(c->dGeom, c->n, count, dDir, dOrg, dIdx);
+    SPT_CUDA_CHECK(cudaGetLastError());
+    SPT_CUDA_CHECK(cudaMemcpyAsync(idx, dIdx, size_t(count) * 4, cudaMemcpyDeviceToHost, c->stream));
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    return SPT_OK;
+}
+
+int spt_cuda_get_counters(SptContext *c, SptCounters *out)
+{
+    if (!c || !out)
+        return fail(SPT_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    unsigned long long h[8];
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    SPT_CUDA_CHECK(cudaMemcpy(h, c->dCounters, sizeof(h), cudaMemcpyDeviceToHost));
+    out->segments = h[0];
+    out->tests = h[0] * c->n;
+    out->samples = h[1];
+    out->dropped = h[2];
+    out->exact = h[3];
+    return SPT_OK;
+}
+
+int spt_cuda_reset_counters(SptContext *c)
+{
+    if (!c)
+        return fail(SPT_ERR_INVALID, "context is null");
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    SPT_CUDA_CHECK(cudaMemsetAsync(c->dCounters, 0, 8 * sizeof(unsigned long long), c->stream));
+    return SPT_OK;
+}
+
+int spt_cuda_get_timing(SptContext *c, SptTiming *out)
+{
+    if (!c || !out)
+        return fail(SPT_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]) == cudaSuccess)
+        c->timing.trace_ms = ms;
+    if (cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]) == cudaSuccess)
+        c->timing.resolve_ms = ms;
+    cudaGetLastError(); // events never recorded: not an error of the caller
+    *out = c->timing;
+    return SPT_OK;
+}
+
+int spt_cuda_measure_fp32_peak(SptContext *c, float *tflops_scalar, float *tflops_packed)
+{
+    if (!c)
+        return fail(SPT_ERR_INVALID, "context is null");
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    int rc = ensure_probe(c, 256);
+    if (rc)
+        return rc;
+    float *dOut = static_cast<float *>(c->dProbe);
+    int const blocks = c->prop.multiProcessorCount * 8, threads = 256;
+    uint32_t const iters = 1u << 16;
+    double const flopScalar = double(blocks) * threads * double(iters) * 8 * 2;
+    float best[2] = {0.f, 0.f};
+    for (int variant = 0; variant < 2; ++variant)
+    {
+        for (int rep = 0; rep < 4; ++rep)
+        {
+            SPT_CUDA_CHECK(cudaEventRecord(c->ev[0], c->stream));
+            if (variant == 0)
+                spt::fp32_peak_scalar<<<blocks, threads, 0, c->stream>>>(dOut, iters, 1.0000001f, 1e-9f);
+            else
+                spt::fp32_peak_packed<<<blocks, threads, 0, c->stream>>>(dOut, iters, 1.0000001f, 1e-9f);
+            SPT_CUDA_CHECK(cudaGetLastError());
+            SPT_CUDA_CHECK(cudaEventRecord(c->ev[1], c->stream));
+            SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+            float ms = 0.f;
+            SPT_CUDA_CHECK(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
+            float const tf = float(flopScalar * (variant ? 2.0 : 1.0) / (double(ms) * 1e-3) / 1e12);
+            if (rep > 0 && tf > best[variant])
+                best[variant] = tf;
+        }
+    }
+    if (tflops_scalar)
+        *tflops_scalar = best[0];
+    if (tflops_packed)
+        *tflops_packed = best[1];
+    return SPT_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,436 @@
+// spt_kernels.cuh -- kernels of the path-tracing hot path (sm_100a only).
+//
+//   trace_megakernel   camera rays + closest-hit + scatter + bounce loop + per-pixel accumulation
+//                      (RenderSegment / RenderSegmentTask semantics, SingleThreadPathTracer.hpp:94-137,
+//                      TaskBasedPathTracer.hpp:54-206) as ONE kernel; one lane = one pixel, the sample
+//                      loop and the bounce loop are flattened into a single state machine so that
+//                      every iteration of the warp is one closest-hit over the sphere list.
+//   first_hit_kernel   deterministic pinhole rays -> index / t / normal (parity probe)
+//   closest_hit_kernel caller-supplied rays -> index (parity probe)
+//   resolve_kernel     (sum, count) -> normalise, gamma 2, round, flip, pack RGB8 (IOHelpers.hpp:17-22)
+#pragma once
+
+#include "spt_device.cuh"
+
+namespace spt
+{
+
+// Block = 8 warps; a warp covers an 8x4 pixel tile (coherent rays), the block a 32x8 tile.
+constexpr int kWarpW = 8, kWarpH = 4;
+constexpr int kBlockWarpsX = 4, kBlockWarpsY = 2;
+constexpr int kTileW = kWarpW * kBlockWarpsX; // 32
+constexpr int kTileH = kWarpH * kBlockWarpsY; // 8
+constexpr int kBlockThreads = kTileW * kTileH; // 256
+
+struct TraceParams
+{
+    CameraConst cam;
+    uint32_t width, height;
+    uint32_t yBegin, yEnd, xBegin, xEnd;
+    uint32_t sampleBegin, sampleEnd;
+    uint32_t depth, passCap;
+    uint64_t seed;
+    uint32_t n;
+    const float4 *geom;  // (cx, cy, cz, r)
+    const float4 *shade; // (colour r, g, b, fuzz)
+    const uint8_t *mat;
+    float4 *accum;       // width*height (sum r, sum g, sum b, count), row y*width + x (not flipped)
+    unsigned long long *counters; // [0] segments [1] samples [2] dropped [3] exact evaluations (may be null)
+};
+
+constexpr uint32_t kSpecularSafetyCap = 65536u; // the reference would overflow its stack long before
+
+// ---- TMA: one bulk copy of the whole sphere list into shared memory ---------------------------
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void stage_geometry_tma(float4 *smemGeom, const float4 *gmemGeom, uint32_t n, uint64_t *mbar)
+{
+    uint32_t const bytes = n * uint32_t(sizeof(float4));
+    uint32_t const bar = smem_addr(mbar);
+    if (threadIdx.x == 0)
+    {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         smem_addr(smemGeom)),
+                     "l"(gmemGeom), "r"(bytes), "r"(bar)
+                     : "memory");
+    }
+    // every thread waits for phase 0 of the barrier (the bytes have landed)
+    uint32_t done = 0;
+    while (!done)
+    {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done)
+                     : "r"(bar)
+                     : "memory");
+    }
+}
+
+// ---- shading (a6-a9 of SURVEY 8a) ---------------------------------------------------------------
+// SampleColorSkybox (SingleThreadPathTracer.hpp:11-19): (initColor * (d.y + 1)) * 0.5
+__device__ __forceinline__ V3 sample_sky(const CameraConst &cam, V3 dir)
+{
+    float const k = fadd(dir.y, 1.f);
+    return vscale(vscale(v3(cam.sky[0], cam.sky[1], cam.sky[2]), k), 0.5f);
+}
+
+// SampleColorReflective (SingleThreadPathTracer.hpp:39-46; TaskBasedPathTracer.hpp:108-122)
+__device__ __forceinline__ void scatter_reflective(float4 sphere, float fuzz, V3 &dir, V3 &org, Rng &rng)
+{
+    org = contact_point(sphere, org, dir, false);
+    V3 const normal = contact_normal(org, sphere);
+    rng.open_event();
+    V3 const sh = rng.shell(); // drawn even when fuzz == 0
+    dir = vnormalize(vadd(vreflect(dir, normal), vscale(sh, fuzz)));
+}
+
+// SampleColorRefractive (SingleThreadPathTracer.hpp:48-92; TaskBasedPathTracer.hpp:124-180)
+__device__ __forceinline__ void scatter_refractive(float4 sphere, V3 &dir, V3 &org, Rng &rng)
+{
+    float const nAir = 1.0f, nGlass = 1.5f;
+    org = contact_point(sphere, org, dir, false);
+    V3 n = contact_normal(org, sphere);
+    rng.open_event();
+
+    float c = vdot(vneg(n), dir);
+    float r = fdiv(nAir, nGlass);
+    float const q1 = fdiv(fsub(nAir, nGlass), fadd(nAir, nGlass));
+    float rSq = fmul(q1, q1); // pow(q, 2.f)
+    float schlick = fadd(rSq, fmul(fsub(1.f, rSq), pow5(fsub(1.f, c))));
+
+    if (rng.uniform(0.f, 1.f) < schlick)
+    {
+        dir = vreflect(dir, n);
+    }
+    else if (fmul(r, fsqrt(fsub(1.f, fmul(c, c)))) < 1.f)
+    {
+        float const k = fsub(fmul(r, c), fsqrt(fsub(1.f, fmul(fmul(r, r), fsub(1.f, fmul(c, c))))));
+        dir = vnormalize(vadd(vscale(dir, r), vscale(n, k)));
+        org = contact_point(sphere, org, dir, true); // straight to the far side of the SAME sphere (quirk Q9)
+        n = vneg(contact_normal(org, sphere));
+
+        c = vdot(vneg(n), dir);
+        r = fdiv(nGlass, nAir);
+        float const q2 = fdiv(fsub(nGlass, nAir), fadd(nGlass, nAir));
+        rSq = fmul(q2, q2);
+        schlick = fadd(rSq, fmul(fsub(1.f, rSq), pow5(fsub(1.f, c))));
+
+        if (rng.uniform(0.f, 1.f) < schlick)
+        {
+            dir = vreflect(dir, n);
+        }
+        else if (fmul(r, fsqrt(fsub(1.f, fmul(c, c)))) < 1.f)
+        {
+            float const k2 = fsub(fmul(r, c), fsqrt(fsub(1.f, fmul(fmul(r, r), fsub(1.f, fmul(c, c))))));
+            dir = vnormalize(vadd(vscale(dir, r), vscale(n, k2)));
+        }
+        else
+        {
+            dir = vreflect(dir, n);
+        }
+    }
+    else
+    {
+        dir = vreflect(dir, n);
+    }
+}
+
+enum : uint32_t
+{
+    MODE_NEW = 0,    // lane needs its next camera sample
+    MODE_TRACE = 1,  // primary / specular segment: material dispatch follows (TraceAndSampleColor)
+    MODE_DIFFUSE = 2 // inside SampleColorDiffuse's terminal chain
+};
+
+// Lane state of the flattened (sample x bounce) loop
+struct Lane
+{
+    V3 org, dir;
+    V3 chain;   // SampleColorDiffuse's sampleColor
+    V3 sum;     // pixelColor (SingleThreadPathTracer.hpp:121) / colors[ci] (TaskBasedPathTracer.hpp:58)
+    float count; // samples[ci] (TaskBasedPathTracer.hpp:59)
+    Rng rng;
+    uint32_t mode, bounce, specular, sample;
+};
+
+// After the closest-hit of the current segment returned `idx`: shade, and either finish the sample or set up
+// the next segment.  `geom` may live in shared or global memory.
+template <typename GeomPtr>
+__device__ __forceinline__ void shade_step(const TraceParams &p, GeomPtr geom, Lane &L, uint32_t idx, uint32_t &dropped)
+{
+    if (L.mode == MODE_DIFFUSE)
+    {
+        // while (--bounceCount && sphereIndex < g_sphereNumber) (SingleThreadPathTracer.hpp:28-34)
+        if (--L.bounce && idx < p.n)
+        {
+            L.chain = vscale(L.chain, 0.5f);
+            float4 const s = geom[idx];
+            L.org = contact_point(s, L.org, L.dir, false);
+            L.rng.open_event();
+            // Normalize(origin + normal + shell): the origin really is added in (quirk Q6)
+            L.dir = vnormalize(vadd(vadd(L.org, contact_normal(L.org, s)), L.rng.shell()));
+        }
+        else
+        {
+            L.sum = vadd(L.sum, L.chain);
+            L.count = fadd(L.count, 1.f);
+            L.mode = MODE_NEW;
+        }
+        return;
+    }
+    // TraceAndSampleColor (SingleThreadPathTracer.hpp:94-112)
+    uint32_t const m = idx < p.n ? uint32_t(__ldg(p.mat + idx)) : 0u;
+    if (m == 3u) // Material::DIFFUSE -> SampleColorDiffuse (SingleThreadPathTracer.hpp:21-27)
+    {
+        float4 const s = geom[idx];
+        float4 const col = __ldg(p.shade + idx);
+        L.chain = vscale(v3(col.x, col.y, col.z), 0.5f);
+        L.org = contact_point(s, L.org, L.dir, false);
+        L.rng.open_event();
+        L.dir = vnormalize(vadd(contact_normal(L.org, s), L.rng.shell()));
+        L.bounce = p.depth;
+        L.mode = MODE_DIFFUSE;
+        return;
+    }
+    if (m == 1u || m == 2u)
+    {
+        float4 const s = geom[idx];
+        if (m == 1u)
+            scatter_reflective(s, __ldg(p.shade + idx).w, L.dir, L.org, L.rng);
+        else
+            scatter_refractive(s, L.dir, L.org, L.rng);
+        ++L.specular;
+        if (p.passCap && L.specular >= p.passCap)
+        {
+            ++dropped; // the task tracer's pass loop ends: path dropped, sample not counted
+            L.mode = MODE_NEW;
+        }
+        else if (L.specular >= kSpecularSafetyCap)
+        {
+            L.count = fadd(L.count, 1.f);
+            L.mode = MODE_NEW;
+        }
+        return;
+    }
+    // miss, or Material::SKYBOX on a sphere (falls out of the switch): SampleColorSkybox
+    L.sum = vadd(L.sum, sample_sky(p.cam, L.dir));
+    L.count = fadd(L.count, 1.f);
+    L.mode = MODE_NEW;
+}
+
+__device__ __forceinline__ void warp_counter_add(unsigned long long *ctr, unsigned long long v)
+{
+    for (int o = 16; o > 0; o >>= 1)
+        v += __shfl_down_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0 && v)
+        atomicAdd(ctr, v);
+}
+
+// pixel of this lane inside the segment: warps tile 8x4, blocks 32x8
+__device__ __forceinline__ void lane_pixel(const TraceParams &p, uint32_t &x, uint32_t &y, bool &inside)
+{
+    uint32_t const lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t const lx = (lane & (kWarpW - 1)) + (warp % kBlockWarpsX) * kWarpW;
+    uint32_t const ly = (lane / kWarpW) + (warp / kBlockWarpsX) * kWarpH;
+    x = p.xBegin + blockIdx.x * kTileW + lx;
+    y = p.yBegin + blockIdx.y * kTileH + ly;
+    inside = x < p.xEnd && y < p.yEnd;
+}
+
+// GEOM_SMEM: the whole sphere list is staged into shared memory by one TMA bulk copy and every lane of a
+// warp reads the same float4 (a broadcast).  Otherwise (list larger than shared memory) it is read through
+// the read-only path with warp-uniform addresses.
+template <bool GEOM_SMEM, bool STRICT>
+__global__ void __launch_bounds__(kBlockThreads) trace_megakernel(const __grid_constant__ TraceParams p)
+{
+    extern __shared__ __align__(16) unsigned char smemRaw[];
+    float4 *smemGeom = reinterpret_cast<float4 *>(smemRaw);
+    __shared__ __align__(8) uint64_t mbar;
+    if (GEOM_SMEM)
+        stage_geometry_tma(smemGeom, p.geom, p.n, &mbar);
+    const float4 *geom = GEOM_SMEM ? smemGeom : p.geom;
+
+    uint32_t x, y;
+    bool inside;
+    lane_pixel(p, x, y, inside);
+    uint32_t const pixel = y * p.width + x;
+    float const widthF = __uint2float_rn(p.width), heightF = __uint2float_rn(p.height);
+
+    Lane L;
+    L.sum = v3(0.f, 0.f, 0.f);
+    L.count = 0.f;
+    L.mode = MODE_NEW;
+    L.sample = p.sampleBegin;
+    uint32_t segments = 0, dropped = 0;
+
+    if (inside)
+    {
+        for (;;)
+        {
+            if (L.mode == MODE_NEW)
+            {
+                if (L.sample >= p.sampleEnd)
+                    break;
+                // next camera sample (SingleThreadPathTracer.hpp:123-128)
+                L.rng.key = stream_key(p.seed, pixel, L.sample);
+                L.rng.event = 0;
+                L.rng.open_event();
+                float const xiU = L.rng.uniform(-1.f, 1.f);
+                float const xiV = L.rng.uniform(-1.f, 1.f);
+                L.dir = primary_direction(p.cam, widthF, heightF, x, y, xiU, xiV);
+                L.org = v3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
+                L.specular = 0;
+                L.mode = MODE_TRACE;
+                ++L.sample;
+            }
+            uint32_t const idx = closest_hit_strict(geom, p.n, L.dir, L.org);
+            ++segments;
+            shade_step(p, geom, L, idx, dropped);
+        }
+        // one lane owns one pixel for the whole launch: plain read-modify-write, no atomics
+        float4 a = p.accum[pixel];
+        a.x = fadd(a.x, L.sum.x);
+        a.y = fadd(a.y, L.sum.y);
+        a.z = fadd(a.z, L.sum.z);
+        a.w = fadd(a.w, L.count);
+        p.accum[pixel] = a;
+    }
+    if (p.counters)
+    {
+        __syncwarp();
+        warp_counter_add(p.counters + 0, segments);
+        warp_counter_add(p.counters + 1, inside ? (p.sampleEnd - p.sampleBegin) : 0u);
+        warp_counter_add(p.counters + 2, dropped);
+    }
+}
+
+// ---- parity probes ------------------------------------------------------------------------------
+struct FirstHitParams
+{
+    CameraConst cam;
+    uint32_t width, height;
+    uint32_t yBegin, yEnd, xBegin, xEnd;
+    uint32_t n;
+    const float4 *geom;
+    uint32_t *idx;
+    float *t;
+    float *normal3;
+};
+
+// jitter-free pinhole rays exactly as SingleThreadPathTracer.hpp:125-128 with xi = 0
+__global__ void first_hit_kernel(const __grid_constant__ FirstHitParams p)
+{
+    uint32_t const segW = p.xEnd - p.xBegin, segH = p.yEnd - p.yBegin;
+    uint32_t const k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= segW * segH)
+        return;
+    uint32_t const x = p.xBegin + k % segW, y = p.yBegin + k / segW;
+    V3 const o = v3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
+    V3 const d = primary_direction(p.cam, __uint2float_rn(p.width), __uint2float_rn(p.height), x, y, 0.f, 0.f);
+    uint32_t const i = closest_hit_strict(p.geom, p.n, d, o);
+    p.idx[k] = i;
+    float t = 0.f;
+    V3 nrm = v3(0.f, 0.f, 0.f);
+    if (i < p.n)
+    {
+        float4 const s = p.geom[i];
+        t = ray_sphere_t(vsub(v3(s.x, s.y, s.z), o), s.w, d, false);
+        nrm = contact_normal(contact_point(s, o, d, false), s);
+    }
+    p.t[k] = t;
+    p.normal3[3 * k + 0] = nrm.x;
+    p.normal3[3 * k + 1] = nrm.y;
+    p.normal3[3 * k + 2] = nrm.z;
+}
+
+__global__ void closest_hit_kernel(const float4 *geom, uint32_t n, uint32_t count, const float *dir3, const float *org3,
+                                   uint32_t *idx)
+{
+    uint32_t const k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= count)
+        return;
+    V3 const d = v3(dir3[3 * k], dir3[3 * k + 1], dir3[3 * k + 2]);
+    V3 const o = v3(org3[3 * k], org3[3 * k + 1], org3[3 * k + 2]);
+    idx[k] = closest_hit_strict(geom, n, d, o);
+}
+
+// ---- resolve ------------------------------------------------------------------------------------
+// colors[i] *= 1.f / samples[i]; io::WritePixel at g_size - ((g_width - x)*3 + y*g_width*3)
+// (TaskBasedPathTracer.hpp:196-205, SingleThreadPathTracer.hpp:120,133-134, IOHelpers.hpp:17-22)
+__global__ void resolve_kernel(const float4 *accum, uint32_t width, uint32_t height, uint32_t yBegin, uint32_t yEnd,
+                               uint32_t xBegin, uint32_t xEnd, uint8_t *rgb8)
+{
+    uint32_t const x = xBegin + blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t const y = yBegin + blockIdx.y;
+    if (x >= xEnd || y >= yEnd)
+        return;
+    float4 const a = accum[size_t(y) * width + x];
+    float const inv = fdiv(1.f, a.w);
+    uint32_t const size = width * height * 3u;
+    uint32_t const index = size - ((width - x) * 3u + y * width * 3u);
+    rgb8[index + 0] = encode_channel(fmul(a.x, inv));
+    rgb8[index + 1] = encode_channel(fmul(a.y, inv));
+    rgb8[index + 2] = encode_channel(fmul(a.z, inv));
+}
+
+// ---- FP32 peak microbenchmark ---------------------------------------------------------------------
+// 8 independent dependent-FMA chains per thread; scalar fma.rn.f32 and packed fma.rn.f32x2.
+__global__ void __launch_bounds__(256) fp32_peak_scalar(float *out, uint32_t iters, float b, float c)
+{
+    float a[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+        a[k] = float(threadIdx.x + k);
+    for (uint32_t i = 0; i < iters; ++i)
+    {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            a[k] = __fmaf_rn(a[k], b, c);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+        s += a[k];
+    if (s == 123.456f)
+        out[0] = s;
+}
+
+__global__ void __launch_bounds__(256) fp32_peak_packed(float *out, uint32_t iters, float b, float c)
+{
+    unsigned long long a[8];
+    unsigned long long bb, cc;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(bb) : "f"(b));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(cc) : "f"(c));
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+    {
+        float const v = float(threadIdx.x + k);
+        asm("mov.b64 %0, {%1, %1};" : "=l"(a[k]) : "f"(v));
+    }
+    for (uint32_t i = 0; i < iters; ++i)
+    {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(a[k]) : "l"(bb), "l"(cc));
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+    {
+        float lo, hi;
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a[k]));
+        s += lo + hi;
+    }
+    if (s == 123.456f)
+        out[0] = s;
+}
+
+} // namespace spt

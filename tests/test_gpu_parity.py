@@ -1,0 +1,206 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the CPU oracle on the same inputs.
+
+Bars (BASELINE.json north_star): first-hit sphere index bit-exact, t / normal within 4 ulp
+(we require and get 0 ulp); renders within RMSE <= 1e-3 / PSNR >= 45 dB of the reference.
+Because the CUDA path spells every rounded operation in the reference's order and shares the
+counter-based RNG definition with the oracle, the float accumulators are compared for EQUALITY.
+"""
+import numpy as np
+import pytest
+
+import simplepathtracer_b200 as spt
+
+pytestmark = pytest.mark.gpu
+
+
+def ulp_diff(a, b):
+    a = np.ascontiguousarray(a, np.float32).view(np.int32).astype(np.int64)
+    b = np.ascontiguousarray(b, np.float32).view(np.int32).astype(np.int64)
+    a = np.where(a < 0, -(a & 0x7FFFFFFF), a)
+    b = np.where(b < 0, -(b & 0x7FFFFFFF), b)
+    return np.abs(a - b)
+
+
+def assert_accum_equal(gpu, cpu):
+    assert gpu.shape == cpu.shape
+    same = (gpu == cpu) | (np.isnan(gpu) & np.isnan(cpu))
+    if not same.all():
+        bad = np.argwhere(~same)
+        raise AssertionError(f"{len(bad)} accumulator words differ; first at {bad[0]}: gpu={gpu[tuple(bad[0])]} cpu={cpu[tuple(bad[0])]}")
+
+
+# ----------------------------------------------------------------------------- first hit
+@pytest.mark.parametrize("which", ["init", "random"])
+@pytest.mark.parametrize("size", [(640, 360), (256, 256)])
+def test_first_hit_bit_exact(tracer, oracle, cam, scene_init, scene_random, which, size):
+    scene = scene_init if which == "init" else scene_random
+    w, h = size
+    tracer.set_scene(scene)
+    gi, gt, gn = tracer.first_hit(cam, w, h)
+    oi, ot, on, _ = oracle.first_hit(scene, cam, w, h)
+    assert np.array_equal(gi, oi)  # index: bit-exact
+    assert ulp_diff(gt, ot).max() == 0  # t: north star allows 4 ulp
+    assert ulp_diff(gn, on).max() == 0  # normal: north star allows 4 ulp
+    assert len(np.unique(oi)) > 3
+
+
+def test_first_hit_config2_full_resolution(tracer, oracle, cam):
+    """BASELINE config 2: single diffuse sphere + ground sphere, 1920x1080, all 2.07 M pinhole rays."""
+    scene = spt.Scene(
+        centers=np.array([[0, -1000.5, 0, 0], [0, 1, 0, 0]], np.float32),
+        radii=np.array([1000.0, 0.5], np.float32),
+        materials=np.array([spt.DIFFUSE, spt.DIFFUSE], np.uint8),
+        colors=np.array([[30, 144, 255, 0], [255, 100, 230, 0]], np.float32),
+        fuzz=np.zeros(2, np.float32),
+    )
+    tracer.set_scene(scene)
+    gi, gt, gn = tracer.first_hit(cam, 1920, 1080)
+    oi, ot, on, _ = oracle.first_hit(scene, cam, 1920, 1080)
+    assert np.array_equal(gi, oi)
+    assert ulp_diff(gt, ot).max() == 0
+    assert ulp_diff(gn, on).max() == 0
+    assert set(np.unique(oi)) == {0, 1, 2}
+
+
+def test_first_hit_segment(tracer, oracle, cam, scene_random):
+    tracer.set_scene(scene_random)
+    seg = (40, 120, 100, 300)  # yBegin, yEnd, xBegin, xEnd
+    gi, gt, gn = tracer.first_hit(cam, 640, 360, seg=seg)
+    oi, ot, on, _ = oracle.first_hit(scene_random, cam, 640, 360, seg=seg)
+    assert np.array_equal(gi, oi) and np.array_equal(gt, ot) and np.array_equal(gn, on)
+
+
+def test_closest_hit_random_rays(tracer, oracle, scene_random):
+    """Secondary-ray-like inputs: origins on and around spheres, arbitrary directions."""
+    rng = np.random.default_rng(7)
+    n = 200_000
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True).astype(np.float32)
+    pick = rng.integers(1, scene_random.n, n)
+    surf = rng.normal(size=(n, 3)).astype(np.float32)
+    surf /= np.linalg.norm(surf, axis=1, keepdims=True).astype(np.float32)
+    o = (scene_random.centers[pick, :3] + surf * scene_random.radii[pick, None]).astype(np.float32)
+    o[: n // 4] = rng.uniform(-20, 20, size=(n // 4, 3)).astype(np.float32)
+    tracer.set_scene(scene_random)
+    assert np.array_equal(tracer.closest_hit(d, o), oracle.closest_hit_many(scene_random, d, o))
+
+
+# ----------------------------------------------------------------------------- renders
+@pytest.mark.parametrize("which", ["init", "random"])
+@pytest.mark.parametrize("pass_cap", [0, 10])
+def test_render_accumulators_bit_exact(tracer, oracle, cam, scene_init, scene_random, which, pass_cap):
+    scene = scene_init if which == "init" else scene_random
+    w, h, spp, depth = 96, 64, 8, 8
+    tracer.set_scene(scene)
+    rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=pass_cap, seed=42, want_accum=True)
+    oacc, octr = oracle.render_accum(scene, cam, w, h, spp, depth, pass_cap=pass_cap, seed=42)
+    assert_accum_equal(acc, oacc)
+    assert np.array_equal(rgb, oracle.resolve(oacc))
+    assert acc[..., 3].max() == spp
+
+
+def test_render_pass_cap_drops_samples(tracer, oracle, cam, scene_init):
+    """With a tiny pass cap the task tracer's drop rule shows up as count < spp, identically on both sides."""
+    w, h, spp, depth = 64, 64, 8, 8
+    tracer.set_scene(scene_init)
+    _, acc = tracer.render(cam, w, h, spp, depth, pass_cap=1, seed=3, want_accum=True)
+    oacc, octr = oracle.render_accum(scene_init, cam, w, h, spp, depth, pass_cap=1, seed=3)
+    assert_accum_equal(acc, oacc)
+    assert octr["dropped"] > 0 and acc[..., 3].min() < spp
+
+
+def test_render_counters_match_oracle(tracer, oracle, cam, scene_random):
+    w, h, spp, depth = 64, 48, 4, 8
+    tracer.set_scene(scene_random)
+    tracer.reset_counters()
+    tracer.render(cam, w, h, spp, depth, seed=9, flags=spt.FLAG_COUNTERS)
+    c = tracer.counters()
+    _, o = oracle.render_accum(scene_random, cam, w, h, spp, depth, seed=9)
+    assert c["segments"] == o["segments"]
+    assert c["tests"] == o["tests"] == o["segments"] * scene_random.n
+    assert c["samples"] == o["samples"] == w * h * spp
+
+
+def test_render_segment_and_ragged_sizes(tracer, oracle, cam, scene_random):
+    """Segments that do not align with the 32x8 block tile, odd image sizes, 1-pixel segments, empty segments."""
+    w, h, spp, depth = 70, 45, 3, 5
+    tracer.set_scene(scene_random)
+    for seg in [(0, 45, 0, 70), (3, 29, 11, 58), (44, 45, 69, 70), (10, 10, 5, 20)]:
+        rgb0 = np.full((h, w, 3), 7, np.uint8)
+        rgb, acc = tracer.render(cam, w, h, spp, depth, seed=5, seg=seg, rgb8=rgb0.copy(), want_accum=True)
+        oacc, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, seed=5, seg=seg)
+        assert_accum_equal(acc, oacc)
+        y0, y1, x0, x1 = seg
+        want = rgb0.copy()
+        if y1 > y0 and x1 > x0:
+            full = oracle.resolve(oacc, seg=seg)
+            want[h - y1 : h - y0, x0:x1] = full[h - y1 : h - y0, x0:x1]
+        assert np.array_equal(rgb, want)  # bytes outside the segment are untouched
+
+
+def test_sample_ranges_compose(tracer, oracle, cam, scene_init):
+    """sample_begin/sample_end shards (the multi-GPU split) reproduce the same per-sample radiance."""
+    import torch
+
+    w, h, depth = 48, 32, 6
+    tracer.set_scene(scene_init)
+    acc = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+    parts = []
+    for s0, s1 in [(0, 5), (5, 6), (6, 16)]:
+        part = torch.zeros_like(acc)
+        tracer.accumulate(cam, w, h, s0, s1, depth, part, seed=11)
+        tracer.synchronize()
+        o, _ = oracle.render_accum(scene_init, cam, w, h, s1 - s0, depth, seed=11, sample_begin=s0)
+        assert_accum_equal(part.cpu().numpy(), o)
+        parts.append(o)
+    # accumulating ranges one after another into ONE buffer == oracle doing the same
+    for s0, s1 in [(0, 5), (5, 6), (6, 16)]:
+        tracer.accumulate(cam, w, h, s0, s1, depth, acc, seed=11)
+    tracer.synchronize()
+    want = np.zeros((h, w, 4), np.float32)
+    for s0, s1 in [(0, 5), (5, 6), (6, 16)]:
+        oracle.render_accum(scene_init, cam, w, h, s1 - s0, depth, seed=11, sample_begin=s0, accum=want)
+    assert_accum_equal(acc.cpu().numpy(), want)
+
+
+def test_resolve_device(tracer, oracle):
+    import torch
+
+    rng = np.random.default_rng(0)
+    w, h = 37, 19
+    acc = rng.uniform(0, 255 * 9, size=(h, w, 4)).astype(np.float32)
+    acc[..., 3] = rng.integers(1, 12, size=(h, w)).astype(np.float32)
+    acc[0, 0] = [0, 0, 0, 0]  # count 0 -> NaN colour -> byte 0 (TaskBasedPathTracer.hpp:198)
+    d_acc = torch.from_numpy(acc).cuda()
+    d_rgb = torch.zeros((h, w, 3), dtype=torch.uint8, device="cuda")
+    tracer.resolve(d_acc, w, h, d_rgb)
+    tracer.synchronize()
+    assert np.array_equal(d_rgb.cpu().numpy(), oracle.resolve(acc))
+
+
+def test_config1_full_size(tracer, oracle, cam, scene_random):
+    """BASELINE config 1 at full size: random-spheres scene, 640x360, 16 spp, depth 8, task-tracer semantics."""
+    w, h, spp, depth = 640, 360, 16, 8
+    tracer.set_scene(scene_random)
+    rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=1, want_accum=True)
+    oacc, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, pass_cap=10, seed=1)
+    assert_accum_equal(acc, oacc)
+    assert np.array_equal(rgb, oracle.resolve(oacc))
+
+
+def test_determinism(tracer, cam, scene_random):
+    tracer.set_scene(scene_random)
+    a = tracer.render(cam, 128, 72, 8, 8, seed=77, want_accum=True)[1]
+    b = tracer.render(cam, 128, 72, 8, 8, seed=77, want_accum=True)[1]
+    c = tracer.render(cam, 128, 72, 8, 8, seed=78, want_accum=True)[1]
+    assert np.array_equal(a, b) and not np.array_equal(a, c)
+
+
+def test_errors(tracer, cam, scene_init):
+    tracer.set_scene(scene_init)
+    with pytest.raises(spt.SptError):
+        tracer.render(cam, 64, 64, 1, 4, seg=(0, 65, 0, 64))  # segment outside the image
+    bad = spt.Camera.of(cam)
+    bad.eye = np.array([0, 1, -3, 1], np.float32)
+    with pytest.raises(spt.SptError):
+        tracer.render(bad, 64, 64, 1, 4)

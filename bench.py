@@ -142,16 +142,18 @@ def run_reference_arm(args, wl):
     if rank != 0:
         return
     rates, sample = [], None
+    t_steps = []
     for i in range(args.warmup + args.steps):
+        t0 = time.time()
         r = cpu_reference_rate(wl, budget_s=4.0)
         if i >= args.warmup:
             rates.append(r["value"])
+            t_steps.append(time.time() - t0)
         sample = r
     value = float(np.mean(rates))
-    samples_per_step = None
     line = {
         "impl": "reference", "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "warmup": args.warmup, "ms_per_step": float(np.mean(t_steps)) * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {wl['desc']} (bounded sample per step: {sample['sample']})"},
         "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": sample["cores"], "kind": sample["kind"], "sample": sample["sample"]},
@@ -188,7 +190,10 @@ def run_native_arm(args, wl):
     s0, s1 = rank * spp // world, (rank + 1) * spp // world
 
     pt = spt.PathTracer(local)
-    pt.set_stream(torch.cuda.current_stream().cuda_stream)
+    # one explicit stream for torch fills, our kernels and the timing events
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    pt.set_stream(stream.cuda_stream)
     pt.set_scene(scene)
     info = pt.device_info()
     accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
@@ -266,6 +271,7 @@ def run_native_arm(args, wl):
     roofline = {
         "bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
         "traffic": None,
+        "exact_evals_per_segment": ctr["exact"] / max(ctr["segments"], 1),
         "kernel": "trace_megakernel", "kernel_ms": kernel_ms, "kernel_share_of_step": kernel_ms / ms_step,
         "algorithmic": f"{FLOP_PER_TEST} flop x {tests_per_launch:.4g} ray-sphere tests per launch "
                        f"({ctr['segments'] / args.steps:.4g} ray segments x {scene.n} spheres; {ctr['segments'] / max(ctr['samples'], 1):.3f} segments/sample)",

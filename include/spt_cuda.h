@@ -70,7 +70,8 @@ enum { SPT_VARIANT_MEGAKERNEL = 0, SPT_VARIANT_WAVEFRONT = 1 };
 enum {
     SPT_FLAG_STRICT_LOOP = 1u, /* closest-hit evaluates every sphere with the reference's exact op sequence
                                   (no conservative pre-filter); results are identical either way */
-    SPT_FLAG_COUNTERS = 2u     /* maintain SptCounters (cheap: per-thread registers, one atomic per warp) */
+    SPT_FLAG_COUNTERS = 2u,    /* maintain SptCounters (cheap: per-thread registers, one atomic per warp) */
+    SPT_FLAG_CROSS_CHECK = 4u  /* spt_cuda_closest_hit only: run pre-filter AND strict loop, report 0xFFFFFFFF on disagreement */
 };
 
 typedef struct SptParams {
@@ -114,8 +115,9 @@ typedef struct SptContext SptContext;
 /* lifetime.  `device` is a CUDA ordinal.  The context owns a stream, the device copy of the scene and scratch. */
 int spt_cuda_create(SptContext **out, int device);
 void spt_cuda_destroy(SptContext *ctx);
-/* run on a caller stream (cudaStream_t passed as void*) instead of the context's own; NULL restores it */
-int spt_cuda_set_stream(SptContext *ctx, void *cuda_stream);
+/* run on a caller stream (cudaStream_t passed as void*; NULL is the legacy default stream) instead of
+ * the context's own non-blocking stream; use_own != 0 restores the context's stream */
+int spt_cuda_set_stream(SptContext *ctx, void *cuda_stream, int use_own);
 int spt_cuda_device_info(SptContext *ctx, SptDeviceInfo *out);
 
 /* upload the scene (copied; no host pointer is retained) */
@@ -139,8 +141,9 @@ int spt_cuda_synchronize(SptContext *ctx);
 /* Parity probes (host buffers, blocking).  Outputs are indexed (x-xBegin) + (y-yBegin)*(xEnd-xBegin). */
 int spt_cuda_first_hit(SptContext *ctx, const SptCamera *cam, uint32_t width, uint32_t height, SptSegment seg,
                        uint32_t flags, uint32_t *idx, float *t, float *normal3);
+/* exact_evals (optional, count entries): spheres per ray that went through the exact sequence */
 int spt_cuda_closest_hit(SptContext *ctx, uint32_t count, const float *dir3, const float *org3, uint32_t flags,
-                         uint32_t *idx);
+                         uint32_t *idx, uint32_t *exact_evals);
 
 int spt_cuda_get_counters(SptContext *ctx, SptCounters *out); /* accumulated since the last reset */
 int spt_cuda_reset_counters(SptContext *ctx);

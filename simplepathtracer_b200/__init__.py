@@ -21,6 +21,7 @@ from .binding import (  # noqa: F401
     WAVEFRONT,
     FLAG_STRICT_LOOP,
     FLAG_COUNTERS,
+    FLAG_CROSS_CHECK,
     DIFFUSE,
     REFLECTIVE,
     REFRACTIVE,

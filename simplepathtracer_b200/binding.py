@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_NAME = "libspt_cuda.so"
 
 MEGAKERNEL, WAVEFRONT = 0, 1
-FLAG_STRICT_LOOP, FLAG_COUNTERS = 1, 2
+FLAG_STRICT_LOOP, FLAG_COUNTERS, FLAG_CROSS_CHECK = 1, 2, 4
 SKYBOX, REFLECTIVE, REFRACTIVE, DIFFUSE = 0, 1, 2, 3  # include/Definitions.hpp:7-13
 
 f32p = C.POINTER(C.c_float)
@@ -187,7 +187,7 @@ def load_library():
     L.spt_cuda_create.argtypes = [C.POINTER(C.c_void_p), C.c_int]
     L.spt_cuda_destroy.argtypes = [C.c_void_p]
     L.spt_cuda_destroy.restype = None
-    L.spt_cuda_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+    L.spt_cuda_set_stream.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
     L.spt_cuda_device_info.argtypes = [C.c_void_p, C.POINTER(DeviceInfo)]
     L.spt_cuda_set_scene.argtypes = [C.c_void_p, C.POINTER(_CScene)]
     L.spt_cuda_render.argtypes = [C.c_void_p, C.POINTER(_CCamera), C.POINTER(_CParams), Segment, C.c_void_p, C.c_void_p]
@@ -196,7 +196,7 @@ def load_library():
     L.spt_cuda_synchronize.argtypes = [C.c_void_p]
     L.spt_cuda_first_hit.argtypes = [C.c_void_p, C.POINTER(_CCamera), C.c_uint32, C.c_uint32, Segment, C.c_uint32, C.c_void_p,
                                      C.c_void_p, C.c_void_p]
-    L.spt_cuda_closest_hit.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+    L.spt_cuda_closest_hit.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
     L.spt_cuda_get_counters.argtypes = [C.c_void_p, C.POINTER(Counters)]
     L.spt_cuda_reset_counters.argtypes = [C.c_void_p]
     L.spt_cuda_get_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
@@ -265,8 +265,12 @@ class PathTracer:
         return {"name": d.name.decode(), "sm_count": d.sm_count, "cc": (d.cc_major, d.cc_minor), "clock_khz": d.clock_khz,
                 "smem_per_block_optin": d.smem_per_block_optin, "global_mem": d.global_mem}
 
-    def set_stream(self, cuda_stream: int):
-        self._check(self.L.spt_cuda_set_stream(self.h, C.c_void_p(cuda_stream)))
+    def set_stream(self, cuda_stream: Optional[int]):
+        """Launch on the given cudaStream_t (0 = legacy default stream); None restores the context's own stream."""
+        if cuda_stream is None:
+            self._check(self.L.spt_cuda_set_stream(self.h, None, 1))
+        else:
+            self._check(self.L.spt_cuda_set_stream(self.h, C.c_void_p(cuda_stream), 0))
 
     def set_scene(self, scene) -> None:
         sc = Scene.of(scene)
@@ -314,12 +318,14 @@ class PathTracer:
         self._check(self.L.spt_cuda_first_hit(self.h, C.byref(cm), width, height, s, flags, idx.ctypes.data, t.ctypes.data, nrm.ctypes.data))
         return idx, t, nrm
 
-    def closest_hit(self, dirs: Sequence, orgs: Sequence, flags=0):
+    def closest_hit(self, dirs: Sequence, orgs: Sequence, flags=0, want_evals=False):
         dirs = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
         orgs = np.ascontiguousarray(orgs, np.float32).reshape(-1, 3)
         idx = np.empty(dirs.shape[0], np.uint32)
-        self._check(self.L.spt_cuda_closest_hit(self.h, dirs.shape[0], dirs.ctypes.data, orgs.ctypes.data, flags, idx.ctypes.data))
-        return idx
+        ev = np.empty(dirs.shape[0], np.uint32) if want_evals else None
+        self._check(self.L.spt_cuda_closest_hit(self.h, dirs.shape[0], dirs.ctypes.data, orgs.ctypes.data, flags, idx.ctypes.data,
+                                                ev.ctypes.data if want_evals else None))
+        return (idx, ev) if want_evals else idx
 
     def counters(self) -> dict:
         c = Counters()

@@ -3,6 +3,7 @@
 #include "../../include/spt_cuda.h"
 #include "spt_kernels.cuh"
 
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -46,6 +47,9 @@ struct SptContext
     float4 *dGeom = nullptr;
     float4 *dShade = nullptr;
     uint8_t *dMat = nullptr;
+    spt::FilterPair *dPairs = nullptr; // pre-filter records
+    uint32_t *dBigIdx = nullptr;
+    spt::FilterScene filter{};
 
     unsigned long long *dCounters = nullptr;
     SptTiming timing{};
@@ -89,6 +93,50 @@ int ensure_probe(SptContext *c, size_t bytes)
     SPT_CUDA_CHECK(cudaMalloc(&c->dProbe, bytes));
     c->probeBytes = bytes;
     return SPT_OK;
+}
+
+float round_up_to_float(double d)
+{
+    float f = float(d);
+    if (double(f) < d)
+        f = std::nextafterf(f, INFINITY);
+    return f;
+}
+
+// Pre-filter records (spt_filter.cuh): per sphere (cx, cy, cz, nk) with
+//   nk = -(|C|^2 - r^2) + S_i - 1e-3f,  S_i = 96 u (|C|^2 + r^2),  evaluated in binary64 and rounded UP.
+// Spheres that are too large for the filter to say anything useful, and the padding up to a whole mask
+// word, get a record that can never pass; the large ones are listed in bigIdx and always evaluated exactly.
+void build_filter(const SptScene *s, std::vector<spt::FilterPair> &pairs, std::vector<uint32_t> &big, float &amax)
+{
+    uint32_t const nWords = (s->n + spt::kWordSpheres - 1) / spt::kWordSpheres;
+    pairs.assign(size_t(nWords) * (spt::kWordSpheres / 2), spt::FilterPair{});
+    big.clear();
+    double amaxD = 0.0;
+    for (uint32_t i = 0; i < nWords * spt::kWordSpheres; ++i)
+    {
+        spt::FilterPair &rec = pairs[i / 2];
+        int const h = int(i & 1);
+        rec.cx[h] = rec.cy[h] = rec.cz[h] = 0.f;
+        rec.nk[h] = -1e30f; // never a candidate
+        if (i >= s->n)
+            continue;
+        double const cx = s->centers4[4 * i], cy = s->centers4[4 * i + 1], cz = s->centers4[4 * i + 2], r = s->radii[i];
+        double const a2 = cx * cx + cy * cy + cz * cz;
+        bool const finite = std::isfinite(a2) && std::isfinite(r);
+        if (!finite || std::fabs(r) > spt::kBigRadius || std::sqrt(a2) > spt::kBigCentre)
+        {
+            big.push_back(i);
+            continue;
+        }
+        double const slack = spt::kSlackU * (a2 + r * r);
+        rec.cx[h] = float(cx);
+        rec.cy[h] = float(cy);
+        rec.cz[h] = float(cz);
+        rec.nk[h] = round_up_to_float(-(a2 - r * r) + slack - double(1e-3f));
+        amaxD = std::max(amaxD, std::sqrt(a2));
+    }
+    amax = round_up_to_float(amaxD);
 }
 
 int check_camera(const SptCamera *cam)
@@ -151,26 +199,42 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
     p.geom = c->dGeom;
     p.shade = c->dShade;
     p.mat = c->dMat;
+    p.filter = c->filter;
     p.accum = dAccum;
     p.counters = (prm->flags & SPT_FLAG_COUNTERS) ? c->dCounters : nullptr;
 
     dim3 const grid((segW + spt::kTileW - 1) / spt::kTileW, (segH + spt::kTileH - 1) / spt::kTileH);
     dim3 const block(spt::kBlockThreads);
     size_t const geomBytes = size_t(c->n) * sizeof(float4);
-    bool const inSmem = geomBytes + 1024 <= c->maxSmemOptin;
+    size_t const pairBytes = size_t(c->filter.nWords) * (spt::kWordSpheres / 2) * sizeof(spt::FilterPair);
+    size_t const budget = c->maxSmemOptin > 2048 ? c->maxSmemOptin - 2048 : 0;
+    bool const strict = (prm->flags & SPT_FLAG_STRICT_LOOP) != 0;
 
     SPT_CUDA_CHECK(cudaEventRecord(c->ev[0], c->stream));
-    if (inSmem)
+#define SPT_LAUNCH(STAGE, STRICT, SMEM)                                                                              \
+    do                                                                                                               \
+    {                                                                                                                \
+        auto kernel = spt::trace_megakernel<STAGE, STRICT>;                                                          \
+        SPT_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(SMEM)));        \
+        kernel<<<grid, block, (SMEM), c->stream>>>(p);                                                               \
+    } while (0)
+    if (strict)
     {
-        auto kernel = spt::trace_megakernel<true, true>;
-        SPT_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(geomBytes)));
-        kernel<<<grid, block, geomBytes, c->stream>>>(p);
+        if (geomBytes <= budget)
+            SPT_LAUNCH(1, true, geomBytes);
+        else
+            SPT_LAUNCH(0, true, 0);
     }
     else
     {
-        auto kernel = spt::trace_megakernel<false, true>;
-        kernel<<<grid, block, 0, c->stream>>>(p);
+        if (geomBytes + pairBytes <= budget)
+            SPT_LAUNCH(2, false, geomBytes + pairBytes);
+        else if (pairBytes <= budget)
+            SPT_LAUNCH(1, false, pairBytes);
+        else
+            SPT_LAUNCH(0, false, 0);
     }
+#undef SPT_LAUNCH
     SPT_CUDA_CHECK(cudaGetLastError());
     SPT_CUDA_CHECK(cudaEventRecord(c->ev[1], c->stream));
     c->timing.launches += 1;
@@ -243,6 +307,8 @@ void spt_cuda_destroy(SptContext *c)
     cudaFree(c->dGeom);
     cudaFree(c->dShade);
     cudaFree(c->dMat);
+    cudaFree(c->dPairs);
+    cudaFree(c->dBigIdx);
     cudaFree(c->dCounters);
     cudaFree(c->dAccum);
     cudaFree(c->dRgb);
@@ -255,12 +321,13 @@ void spt_cuda_destroy(SptContext *c)
     delete c;
 }
 
-int spt_cuda_set_stream(SptContext *c, void *cuda_stream)
+int spt_cuda_set_stream(SptContext *c, void *cuda_stream, int use_own)
 {
     if (!c)
         return fail(SPT_ERR_INVALID, "context is null");
     std::lock_guard<std::mutex> g(c->lock);
-    c->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : c->ownStream;
+    // a null handle is a real stream (the legacy default stream), so "own" is a separate switch
+    c->stream = use_own ? c->ownStream : static_cast<cudaStream_t>(cuda_stream);
     return SPT_OK;
 }
 
@@ -297,13 +364,31 @@ int spt_cuda_set_scene(SptContext *c, const SptScene *s)
         geom[i] = make_float4(s->centers4[4 * i], s->centers4[4 * i + 1], s->centers4[4 * i + 2], s->radii[i]);
         shade[i] = make_float4(s->colors4[4 * i], s->colors4[4 * i + 1], s->colors4[4 * i + 2], s->fuzz[i]);
     }
+    std::vector<spt::FilterPair> pairs;
+    std::vector<uint32_t> big;
+    float amax = 0.f;
+    build_filter(s, pairs, big, amax);
     SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     cudaFree(c->dGeom);
     cudaFree(c->dShade);
     cudaFree(c->dMat);
+    cudaFree(c->dPairs);
+    cudaFree(c->dBigIdx);
     c->dGeom = c->dShade = nullptr;
     c->dMat = nullptr;
+    c->dPairs = nullptr;
+    c->dBigIdx = nullptr;
     c->n = 0;
+    SPT_CUDA_CHECK(cudaMalloc(&c->dPairs, pairs.size() * sizeof(spt::FilterPair)));
+    SPT_CUDA_CHECK(cudaMalloc(&c->dBigIdx, (big.size() + 1) * sizeof(uint32_t)));
+    SPT_CUDA_CHECK(cudaMemcpy(c->dPairs, pairs.data(), pairs.size() * sizeof(spt::FilterPair), cudaMemcpyHostToDevice));
+    if (!big.empty())
+        SPT_CUDA_CHECK(cudaMemcpy(c->dBigIdx, big.data(), big.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    c->filter.pairs = c->dPairs;
+    c->filter.nWords = uint32_t(pairs.size() / (spt::kWordSpheres / 2));
+    c->filter.bigIdx = c->dBigIdx;
+    c->filter.nBig = uint32_t(big.size());
+    c->filter.amax = amax;
     SPT_CUDA_CHECK(cudaMalloc(&c->dGeom, s->n * sizeof(float4)));
     SPT_CUDA_CHECK(cudaMalloc(&c->dShade, s->n * sizeof(float4)));
     SPT_CUDA_CHECK(cudaMalloc(&c->dMat, s->n));
@@ -396,7 +481,6 @@ int spt_cuda_render(SptContext *c, const SptCamera *cam, const SptParams *prm, S
 int spt_cuda_first_hit(SptContext *c, const SptCamera *cam, uint32_t width, uint32_t height, SptSegment seg, uint32_t flags,
                        uint32_t *idx, float *t, float *normal3)
 {
-    (void)flags;
     if (!c || !idx || !t || !normal3)
         return fail(SPT_ERR_INVALID, "null argument");
     int rc = check_camera(cam);
@@ -425,6 +509,8 @@ int spt_cuda_first_hit(SptContext *c, const SptCamera *cam, uint32_t width, uint
     p.xEnd = seg.xEnd;
     p.n = c->n;
     p.geom = c->dGeom;
+    p.filter = c->filter;
+    p.strict = (flags & SPT_FLAG_STRICT_LOOP) ? 1u : 0u;
     p.idx = static_cast<uint32_t *>(c->dProbe);
     p.t = reinterpret_cast<float *>(p.idx + count);
     p.normal3 = p.t + count;
@@ -437,9 +523,9 @@ int spt_cuda_first_hit(SptContext *c, const SptCamera *cam, uint32_t width, uint
     return SPT_OK;
 }
 
-int spt_cuda_closest_hit(SptContext *c, uint32_t count, const float *dir3, const float *org3, uint32_t flags, uint32_t *idx)
+int spt_cuda_closest_hit(SptContext *c, uint32_t count, const float *dir3, const float *org3, uint32_t flags, uint32_t *idx,
+                         uint32_t *exact_evals)
 {
-    (void)flags;
     if (!c || !dir3 || !org3 || !idx)
         return fail(SPT_ERR_INVALID, "null argument");
     std::lock_guard<std::mutex> g(c->lock);
@@ -448,17 +534,22 @@ int spt_cuda_closest_hit(SptContext *c, uint32_t count, const float *dir3, const
         return fail(SPT_ERR_NO_SCENE, "spt_cuda_set_scene has not been called");
     if (count == 0)
         return SPT_OK;
-    int rc = ensure_probe(c, size_t(count) * 28);
+    int rc = ensure_probe(c, size_t(count) * 32);
     if (rc)
         return rc;
     float *dDir = static_cast<float *>(c->dProbe);
     float *dOrg = dDir + size_t(count) * 3;
     uint32_t *dIdx = reinterpret_cast<uint32_t *>(dOrg + size_t(count) * 3);
+    uint32_t *dEvals = dIdx + count;
+    uint32_t const mode = (flags & SPT_FLAG_STRICT_LOOP) ? 1u : ((flags & SPT_FLAG_CROSS_CHECK) ? 2u : 0u);
     SPT_CUDA_CHECK(cudaMemcpyAsync(dDir, dir3, size_t(count) * 12, cudaMemcpyHostToDevice, c->stream));
     SPT_CUDA_CHECK(cudaMemcpyAsync(dOrg, org3, size_t(count) * 12, cudaMemcpyHostToDevice, c->stream));
-    spt::closest_hit_kernel<<<(count + 255) / 256, 256, 0, c->stream>>>(c->dGeom, c->n, count, dDir, dOrg, dIdx);
+    spt::closest_hit_kernel<<<(count + 255) / 256, 256, 0, c->stream>>>(c->dGeom, c->n, c->filter, mode, count, dDir, dOrg, dIdx,
+                                                                          dEvals);
     SPT_CUDA_CHECK(cudaGetLastError());
     SPT_CUDA_CHECK(cudaMemcpyAsync(idx, dIdx, size_t(count) * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (exact_evals)
+        SPT_CUDA_CHECK(cudaMemcpyAsync(exact_evals, dEvals, size_t(count) * 4, cudaMemcpyDeviceToHost, c->stream));
     SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     return SPT_OK;
 }

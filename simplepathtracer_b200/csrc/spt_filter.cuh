@@ -1,0 +1,194 @@
+// spt_filter.cuh -- the closest-hit loop as the B200 runs it: a conservative FMA pre-filter over the
+// whole sphere list in packed f32x2 arithmetic, then the reference's exact sequence on the few survivors.
+//
+// Why: cd::RaySphereIntersection (Collision.hpp:9-17) is 17 separately rounded flops per (ray, sphere).
+// Spelled that way it costs ~23 issue slots per test and, having no FMA, can never pass 50 % of the FP32
+// roofline.  But only ~2 of N spheres pass per ray, and only those decide the result.  So every sphere first
+// goes through a cheaper test that is PROVABLY implied by the exact one (no false negatives), and only
+// spheres that pass it are evaluated with the exact, separately rounded sequence (exact_sphere<>), which
+// alone decides index, t and normal.  Results are therefore bit-identical to the strict loop.
+//
+// The pre-filter, per (ray, sphere), with C = centre, O = origin, D = direction:
+//     tC = C.D - O.D (+ epsT)                           3 FMA   chain seeded with a per-ray constant
+//     na = -(|C|^2 - r^2) + 2 C.O  (+ S_i - 1e-3)       3 FMA   chain seeded with a per-sphere constant
+//     v  = tC*tC + na  - |O|^2 (+ S_ray)                1 FMA + 1 ADD
+//     candidate  <=>  min(v, tC) >= 0                    i.e.  r^2 - d^2 > 1e-3 - slack  and  tC > -epsT
+// v is the discriminant r^2 - (|C-O|^2 - tC^2) of Collision.hpp:14-16 expanded about the world origin so that
+// nothing of the form (C - O) has to be formed per test.  Two spheres are tested per instruction
+// (fma.rn.f32x2 / add.rn.f32x2: one issue slot, two lanes of the FP32 pipe), the sign of min(v, tC) is shifted
+// into a per-lane bit mask (one FMNMX + one SHF per test), and nothing branches inside the loop.
+//
+// Slack (u = 2^-24; A = |C_i|, B = |O|, |D| <= 1 + 2^-20).  Worst-case rounding analysis of both sides
+// ("pre-filter bound"):  |disc_exact_sequence - disc_real| <= u(33.4(A^2+B^2) + 2r^2),
+// |v - (disc_real - 1e-3 + S_i + S_ray)| <= u(37.8A^2 + 41.9B^2 + 6r^2), so S_i = 96u(A^2 + r^2) and
+// S_ray = 96u B^2 cover the sum with margin.  For tC the exact sequence errs by <= 4.2u(A+B) and the chain
+// by <= 6.2u(A+B): with A + B <= 1024 a strict pass (tC_exact > 1e-3) implies tC_chain > 0, so epsT = 0;
+// beyond that epsT = 2^-20 (Amax + B) is seeded into the chain and S_ray grows by 2^-18 (Amax + B)^2.
+// Spheres too large for this to be useful (r > kBigRadius or |C| > kBigCentre: the ground sphere) are kept
+// out of the filter and always evaluated exactly.
+#pragma once
+
+#include "spt_device.cuh"
+
+namespace spt
+{
+
+constexpr float kBigRadius = 64.f;
+constexpr float kBigCentre = 4096.f;
+constexpr uint32_t kWordSpheres = 32;                // one mask word
+constexpr uint32_t kSuperWords = 4;                  // words per candidate-resolution round
+constexpr double kSlackU = 96.0 / 16777216.0;        // 96 u
+
+// One record = TWO spheres, component-interleaved so that each 64-bit half is an f32x2 operand:
+//   a = (cx0, cx1, cy0, cy1)   b = (cz0, cz1, nk0, nk1),   nk = -(|C|^2 - r^2) + S_i - 1e-3 (rounded up)
+struct __align__(16) FilterPair
+{
+    float cx[2], cy[2], cz[2], nk[2];
+};
+
+struct FilterScene
+{
+    const FilterPair *pairs; // nWords * 16 records (padded with never-pass spheres); big spheres are never-pass here
+    uint32_t nWords;
+    const uint32_t *bigIdx;  // spheres always evaluated exactly
+    uint32_t nBig;
+    float amax;              // max |C_i| over filtered spheres
+};
+
+// ---- packed f32x2 helpers (sm_100a: FFMA2 / FADD2) -------------------------------------------------
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi)
+{
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(unsigned long long v, float &lo, float &hi)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c)
+{
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ unsigned long long add2(unsigned long long a, unsigned long long b)
+{
+    unsigned long long d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+// Per-ray constants of the pre-filter, each rounded in the direction that can only ADD candidates.
+struct FilterRay
+{
+    unsigned long long dx, dy, dz;    // direction, broadcast to both halves
+    unsigned long long ox2, oy2, oz2; // 2 * origin
+    unsigned long long nod;           // -(O.D) + epsT
+    unsigned long long noo;           // -|O|^2 + S_ray
+};
+
+__device__ __forceinline__ FilterRay make_filter_ray(V3 dir, V3 org, float od, float amax)
+{
+    float const oo = __fmaf_ru(org.z, org.z, __fmaf_ru(org.y, org.y, __fmul_ru(org.x, org.x))); // >= |O|^2
+    float sRay = __fmul_ru(oo, float(kSlackU) * 1.0001f);
+    float epsT = 0.f;
+    float const b = __fsqrt_ru(oo);
+    float const m = __fadd_ru(amax, b);
+    if (m > 1024.f)
+    { // far-away origin: widen the tC test, and pay for shifting tC in the square
+        epsT = __fmul_ru(m, 9.5367431640625e-7f);                   // 2^-20 (Amax + B)
+        sRay = __fadd_ru(sRay, __fmul_ru(__fmul_ru(m, m), 3.8146973e-6f)); // + 2^-18 (Amax + B)^2
+    }
+    float const oolo = __fmaf_rd(org.z, org.z, __fmaf_rd(org.y, org.y, __fmul_rd(org.x, org.x))); // <= |O|^2
+    float const nod = __fadd_ru(-od, epsT); // od is the exact sequence's Dot(O,D): its <= 3.1u B error is in the bound
+    float const noo = __fadd_ru(-oolo, sRay);
+    FilterRay r;
+    r.dx = pack2(dir.x, dir.x);
+    r.dy = pack2(dir.y, dir.y);
+    r.dz = pack2(dir.z, dir.z);
+    r.ox2 = pack2(org.x + org.x, org.x + org.x);
+    r.oy2 = pack2(org.y + org.y, org.y + org.y);
+    r.oz2 = pack2(org.z + org.z, org.z + org.z);
+    r.nod = pack2(nod, nod);
+    r.noo = pack2(noo, noo);
+    return r;
+}
+
+// one record (two spheres): shifts two FAIL bits into `mask` (sign of min(v, tC))
+__device__ __forceinline__ void filter_pair(const FilterPair *__restrict__ rec, const FilterRay &r, uint32_t &mask)
+{
+    ulonglong2 const a = *reinterpret_cast<const ulonglong2 *>(rec->cx); // (cx0,cx1) (cy0,cy1)
+    ulonglong2 const b = *reinterpret_cast<const ulonglong2 *>(rec->cz); // (cz0,cz1) (nk0,nk1)
+    unsigned long long const tc = fma2(b.x, r.dz, fma2(a.y, r.dy, fma2(a.x, r.dx, r.nod)));
+    unsigned long long const na = fma2(b.x, r.oz2, fma2(a.y, r.oy2, fma2(a.x, r.ox2, b.y)));
+    unsigned long long const v = add2(fma2(tc, tc, na), r.noo);
+    float t0, t1, v0, v1;
+    unpack2(tc, t0, t1);
+    unpack2(v, v0, v1);
+    mask = __funnelshift_l(__float_as_uint(fminf(v0, t0)), mask, 1);
+    mask = __funnelshift_l(__float_as_uint(fminf(v1, t1)), mask, 1);
+}
+
+// FindClosestIntersectionSphere (Collision.hpp:87-109): pre-filter + exact evaluation of the candidates.
+// Returns exactly what closest_hit_strict returns.  `exactEvals` counts exact_sphere calls (instrumentation).
+template <typename GeomPtr>
+__device__ __forceinline__ uint32_t closest_hit_filtered(const FilterScene &fs, GeomPtr geom, uint32_t n, V3 dir, V3 org,
+                                                         uint32_t &exactEvals)
+{
+    uint32_t minIndex = n;
+    float minDistanceSq = FLT_MAX;
+    float const od = vdot(org, dir);
+
+    for (uint32_t b = 0; b < fs.nBig; ++b)
+    {
+        uint32_t const i = fs.bigIdx[b];
+        exact_sphere<false>(geom[i], i, dir, org, od, minIndex, minDistanceSq);
+        ++exactEvals;
+    }
+
+    FilterRay const fr = make_filter_ray(dir, org, od, fs.amax);
+    const FilterPair *rec = fs.pairs;
+    for (uint32_t w0 = 0; w0 < fs.nWords; w0 += kSuperWords)
+    {
+        uint32_t cand[kSuperWords];
+#pragma unroll
+        for (uint32_t w = 0; w < kSuperWords; ++w)
+        {
+            uint32_t mask = 0xFFFFFFFFu; // all "fail"
+            if (w0 + w < fs.nWords)      // warp-uniform
+            {
+#pragma unroll
+                for (uint32_t pp = 0; pp < kWordSpheres / 2; ++pp)
+                    filter_pair(rec + pp, fr, mask);
+                rec += kWordSpheres / 2;
+            }
+            cand[w] = ~mask; // bit (31 - j) set <=> sphere j of the word is a candidate
+        }
+        // exact sequence on this lane's candidates; lanes without any idle here (the only divergent part)
+        for (;;)
+        {
+            uint32_t w, bits;
+            if (cand[0]) { w = 0; bits = cand[0]; }
+            else if (cand[1]) { w = 1; bits = cand[1]; }
+            else if (cand[2]) { w = 2; bits = cand[2]; }
+            else if (cand[3]) { w = 3; bits = cand[3]; }
+            else break;
+            uint32_t const j = __clz(bits);
+            uint32_t const cleared = bits & ~(0x80000000u >> j);
+            if (w == 0) cand[0] = cleared;
+            else if (w == 1) cand[1] = cleared;
+            else if (w == 2) cand[2] = cleared;
+            else cand[3] = cleared;
+            uint32_t const i = (w0 + w) * kWordSpheres + j;
+            if (i < n) // padding records can only show up for NaN rays
+            {
+                exact_sphere<false>(geom[i], i, dir, org, od, minIndex, minDistanceSq);
+                ++exactEvals;
+            }
+        }
+    }
+    return minIndex;
+}
+
+} // namespace spt

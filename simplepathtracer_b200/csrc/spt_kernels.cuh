@@ -11,6 +11,7 @@
 #pragma once
 
 #include "spt_device.cuh"
+#include "spt_filter.cuh"
 
 namespace spt
 {
@@ -34,6 +35,7 @@ struct TraceParams
     const float4 *geom;  // (cx, cy, cz, r)
     const float4 *shade; // (colour r, g, b, fuzz)
     const uint8_t *mat;
+    FilterScene filter;  // pre-filter records (global memory copies)
     float4 *accum;       // width*height (sum r, sum g, sum b, count), row y*width + x (not flipped)
     unsigned long long *counters; // [0] segments [1] samples [2] dropped [3] exact evaluations (may be null)
 };
@@ -43,9 +45,11 @@ constexpr uint32_t kSpecularSafetyCap = 65536u; // the reference would overflow 
 // ---- TMA: one bulk copy of the whole sphere list into shared memory ---------------------------
 __device__ __forceinline__ uint32_t smem_addr(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
 
-__device__ __forceinline__ void stage_geometry_tma(float4 *smemGeom, const float4 *gmemGeom, uint32_t n, uint64_t *mbar)
+// dstA/srcA/bytesA and dstB/srcB/bytesB: up to two regions (bytes multiple of 16; 0 = skip)
+__device__ __forceinline__ void stage_scene_tma(void *dstA, const void *srcA, uint32_t bytesA, void *dstB, const void *srcB,
+                                                uint32_t bytesB, uint64_t *mbar)
 {
-    uint32_t const bytes = n * uint32_t(sizeof(float4));
+    uint32_t const bytes = bytesA + bytesB;
     uint32_t const bar = smem_addr(mbar);
     if (threadIdx.x == 0)
     {
@@ -56,10 +60,16 @@ __device__ __forceinline__ void stage_geometry_tma(float4 *smemGeom, const float
     if (threadIdx.x == 0)
     {
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                         smem_addr(smemGeom)),
-                     "l"(gmemGeom), "r"(bytes), "r"(bar)
-                     : "memory");
+        if (bytesA)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                             smem_addr(dstA)),
+                         "l"(srcA), "r"(bytesA), "r"(bar)
+                         : "memory");
+        if (bytesB)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                             smem_addr(dstB)),
+                         "l"(srcB), "r"(bytesB), "r"(bar)
+                         : "memory");
     }
     // every thread waits for phase 0 of the barrier (the bytes have landed)
     uint32_t done = 0;
@@ -245,18 +255,38 @@ __device__ __forceinline__ void lane_pixel(const TraceParams &p, uint32_t &x, ui
     inside = x < p.xEnd && y < p.yEnd;
 }
 
-// GEOM_SMEM: the whole sphere list is staged into shared memory by one TMA bulk copy and every lane of a
-// warp reads the same float4 (a broadcast).  Otherwise (list larger than shared memory) it is read through
-// the read-only path with warp-uniform addresses.
-template <bool GEOM_SMEM, bool STRICT>
+// STAGE: what is staged into shared memory by TMA bulk copies at kernel start (every lane of a warp then
+// reads the same address: a broadcast).  2 = exact geometry + pre-filter records, 1 = pre-filter records only
+// (strict: geometry only), 0 = nothing (lists larger than shared memory are read through L1/L2 with
+// warp-uniform addresses).  STRICT: no pre-filter, every sphere through the exact sequence.
+template <int STAGE, bool STRICT>
 __global__ void __launch_bounds__(kBlockThreads) trace_megakernel(const __grid_constant__ TraceParams p)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
-    float4 *smemGeom = reinterpret_cast<float4 *>(smemRaw);
     __shared__ __align__(8) uint64_t mbar;
-    if (GEOM_SMEM)
-        stage_geometry_tma(smemGeom, p.geom, p.n, &mbar);
-    const float4 *geom = GEOM_SMEM ? smemGeom : p.geom;
+    uint32_t const geomBytes = p.n * uint32_t(sizeof(float4));
+    uint32_t const pairBytes = STRICT ? 0u : p.filter.nWords * (kWordSpheres / 2) * uint32_t(sizeof(FilterPair));
+    const float4 *geom = p.geom;
+    FilterScene fs = p.filter;
+    if (STAGE == 2)
+    {
+        stage_scene_tma(smemRaw, p.geom, geomBytes, smemRaw + geomBytes, p.filter.pairs, pairBytes, &mbar);
+        geom = reinterpret_cast<const float4 *>(smemRaw);
+        fs.pairs = reinterpret_cast<const FilterPair *>(smemRaw + geomBytes);
+    }
+    else if (STAGE == 1)
+    {
+        if (STRICT)
+        {
+            stage_scene_tma(smemRaw, p.geom, geomBytes, nullptr, nullptr, 0, &mbar);
+            geom = reinterpret_cast<const float4 *>(smemRaw);
+        }
+        else
+        {
+            stage_scene_tma(smemRaw, p.filter.pairs, pairBytes, nullptr, nullptr, 0, &mbar);
+            fs.pairs = reinterpret_cast<const FilterPair *>(smemRaw);
+        }
+    }
 
     uint32_t x, y;
     bool inside;
@@ -269,7 +299,7 @@ __global__ void __launch_bounds__(kBlockThreads) trace_megakernel(const __grid_c
     L.count = 0.f;
     L.mode = MODE_NEW;
     L.sample = p.sampleBegin;
-    uint32_t segments = 0, dropped = 0;
+    uint32_t segments = 0, dropped = 0, exactEvals = 0;
 
     if (inside)
     {
@@ -291,7 +321,8 @@ __global__ void __launch_bounds__(kBlockThreads) trace_megakernel(const __grid_c
                 L.mode = MODE_TRACE;
                 ++L.sample;
             }
-            uint32_t const idx = closest_hit_strict(geom, p.n, L.dir, L.org);
+            uint32_t const idx = STRICT ? closest_hit_strict(geom, p.n, L.dir, L.org)
+                                        : closest_hit_filtered(fs, geom, p.n, L.dir, L.org, exactEvals);
             ++segments;
             shade_step(p, geom, L, idx, dropped);
         }
@@ -309,6 +340,7 @@ __global__ void __launch_bounds__(kBlockThreads) trace_megakernel(const __grid_c
         warp_counter_add(p.counters + 0, segments);
         warp_counter_add(p.counters + 1, inside ? (p.sampleEnd - p.sampleBegin) : 0u);
         warp_counter_add(p.counters + 2, dropped);
+        warp_counter_add(p.counters + 3, STRICT ? segments * (unsigned long long)(p.n) : exactEvals);
     }
 }
 
@@ -320,6 +352,8 @@ struct FirstHitParams
     uint32_t yBegin, yEnd, xBegin, xEnd;
     uint32_t n;
     const float4 *geom;
+    FilterScene filter;
+    uint32_t strict;
     uint32_t *idx;
     float *t;
     float *normal3;
@@ -335,7 +369,8 @@ __global__ void first_hit_kernel(const __grid_constant__ FirstHitParams p)
     uint32_t const x = p.xBegin + k % segW, y = p.yBegin + k / segW;
     V3 const o = v3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
     V3 const d = primary_direction(p.cam, __uint2float_rn(p.width), __uint2float_rn(p.height), x, y, 0.f, 0.f);
-    uint32_t const i = closest_hit_strict(p.geom, p.n, d, o);
+    uint32_t exactEvals = 0;
+    uint32_t const i = p.strict ? closest_hit_strict(p.geom, p.n, d, o) : closest_hit_filtered(p.filter, p.geom, p.n, d, o, exactEvals);
     p.idx[k] = i;
     float t = 0.f;
     V3 nrm = v3(0.f, 0.f, 0.f);
@@ -351,15 +386,29 @@ __global__ void first_hit_kernel(const __grid_constant__ FirstHitParams p)
     p.normal3[3 * k + 2] = nrm.z;
 }
 
-__global__ void closest_hit_kernel(const float4 *geom, uint32_t n, uint32_t count, const float *dir3, const float *org3,
-                                   uint32_t *idx)
+// mode 0: pre-filter + exact candidates (the product path); 1: strict loop; 2: both, and idx gets 0xFFFFFFFF
+// where they disagree (must never happen).  evals (optional) receives the number of exact evaluations.
+__global__ void closest_hit_kernel(const float4 *geom, uint32_t n, FilterScene filter, uint32_t mode, uint32_t count,
+                                   const float *dir3, const float *org3, uint32_t *idx, uint32_t *evals)
 {
     uint32_t const k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= count)
         return;
     V3 const d = v3(dir3[3 * k], dir3[3 * k + 1], dir3[3 * k + 2]);
     V3 const o = v3(org3[3 * k], org3[3 * k + 1], org3[3 * k + 2]);
-    idx[k] = closest_hit_strict(geom, n, d, o);
+    uint32_t exactEvals = 0;
+    uint32_t r;
+    if (mode == 1)
+        r = closest_hit_strict(geom, n, d, o);
+    else
+    {
+        r = closest_hit_filtered(filter, geom, n, d, o, exactEvals);
+        if (mode == 2 && r != closest_hit_strict(geom, n, d, o))
+            r = 0xFFFFFFFFu;
+    }
+    idx[k] = r;
+    if (evals)
+        evals[k] = exactEvals;
 }
 
 // ---- resolve ------------------------------------------------------------------------------------

@@ -32,11 +32,12 @@ def assert_accum_equal(gpu, cpu):
 # ----------------------------------------------------------------------------- first hit
 @pytest.mark.parametrize("which", ["init", "random"])
 @pytest.mark.parametrize("size", [(640, 360), (256, 256)])
-def test_first_hit_bit_exact(tracer, oracle, cam, scene_init, scene_random, which, size):
+@pytest.mark.parametrize("flags", [0, spt.FLAG_STRICT_LOOP])
+def test_first_hit_bit_exact(tracer, oracle, cam, scene_init, scene_random, which, size, flags):
     scene = scene_init if which == "init" else scene_random
     w, h = size
     tracer.set_scene(scene)
-    gi, gt, gn = tracer.first_hit(cam, w, h)
+    gi, gt, gn = tracer.first_hit(cam, w, h, flags=flags)
     oi, ot, on, _ = oracle.first_hit(scene, cam, w, h)
     assert np.array_equal(gi, oi)  # index: bit-exact
     assert ulp_diff(gt, ot).max() == 0  # t: north star allows 4 ulp
@@ -70,29 +71,70 @@ def test_first_hit_segment(tracer, oracle, cam, scene_random):
     assert np.array_equal(gi, oi) and np.array_equal(gt, ot) and np.array_equal(gn, on)
 
 
-def test_closest_hit_random_rays(tracer, oracle, scene_random):
-    """Secondary-ray-like inputs: origins on and around spheres, arbitrary directions."""
-    rng = np.random.default_rng(7)
-    n = 200_000
+def secondary_like_rays(scene, n, seed):
+    """Origins on sphere surfaces (and some anywhere, some far away), arbitrary unit directions,
+    a share of them aimed to graze a sphere's silhouette (the pre-filter's hard case)."""
+    rng = np.random.default_rng(seed)
     d = rng.normal(size=(n, 3)).astype(np.float32)
     d /= np.linalg.norm(d, axis=1, keepdims=True).astype(np.float32)
-    pick = rng.integers(1, scene_random.n, n)
+    pick = rng.integers(0, scene.n, n)
     surf = rng.normal(size=(n, 3)).astype(np.float32)
     surf /= np.linalg.norm(surf, axis=1, keepdims=True).astype(np.float32)
-    o = (scene_random.centers[pick, :3] + surf * scene_random.radii[pick, None]).astype(np.float32)
-    o[: n // 4] = rng.uniform(-20, 20, size=(n // 4, 3)).astype(np.float32)
-    tracer.set_scene(scene_random)
-    assert np.array_equal(tracer.closest_hit(d, o), oracle.closest_hit_many(scene_random, d, o))
+    o = (scene.centers[pick, :3].astype(np.float64) + surf * scene.radii[pick, None].astype(np.float64)).astype(np.float32)
+    q = n // 8
+    o[:q] = rng.uniform(-20, 20, size=(q, 3)).astype(np.float32)
+    o[q : q + q // 4] = rng.uniform(-3000, 3000, size=(q // 4, 3)).astype(np.float32)  # far origins: widened tC test
+    # grazing rays: aim at a point on the silhouette circle of another sphere, +- a hair
+    k = slice(2 * q, 5 * q)
+    m = k.stop - k.start
+    tgt = rng.integers(0, scene.n, m)
+    c = scene.centers[tgt, :3].astype(np.float64)
+    r = scene.radii[tgt].astype(np.float64)
+    to = c - o[k].astype(np.float64)
+    dist = np.linalg.norm(to, axis=1, keepdims=True)
+    axis = to / np.maximum(dist, 1e-9)
+    perp = np.cross(axis, rng.normal(size=(m, 3)))
+    perp /= np.maximum(np.linalg.norm(perp, axis=1, keepdims=True), 1e-9)
+    scale = (1.0 + rng.normal(scale=3e-5, size=(m, 1))) * r[:, None]
+    aim = c + perp * scale - o[k]
+    aim /= np.maximum(np.linalg.norm(aim, axis=1, keepdims=True), 1e-9)
+    d[k] = aim.astype(np.float32)
+    return d, o
+
+
+@pytest.mark.parametrize("which", ["init", "random"])
+def test_closest_hit_random_rays(tracer, oracle, scene_init, scene_random, which):
+    scene = scene_init if which == "init" else scene_random
+    d, o = secondary_like_rays(scene, 200_000, 7)
+    tracer.set_scene(scene)
+    want = oracle.closest_hit_many(scene, d, o)
+    got, evals = tracer.closest_hit(d, o, want_evals=True)  # product path: pre-filter + exact candidates
+    assert np.array_equal(got, want)
+    assert np.array_equal(tracer.closest_hit(d, o, flags=spt.FLAG_STRICT_LOOP), want)
+    assert (want < scene.n).mean() > 0.3
+    assert evals.mean() < 0.25 * scene.n + 4  # the pre-filter really filters
+
+
+def test_prefilter_never_rejects_a_true_hit(tracer, scene_random, scene_init):
+    """Property at scale: pre-filter + exact candidates == strict loop on millions of rays (device-side
+    cross-check; 0xFFFFFFFF marks a disagreement)."""
+    for scene, seed in ((scene_random, 11), (scene_init, 12)):
+        tracer.set_scene(scene)
+        for rep in range(3):
+            d, o = secondary_like_rays(scene, 1_000_000, seed + 100 * rep)
+            got = tracer.closest_hit(d, o, flags=spt.FLAG_CROSS_CHECK)
+            assert not (got == 0xFFFFFFFF).any()
 
 
 # ----------------------------------------------------------------------------- renders
 @pytest.mark.parametrize("which", ["init", "random"])
 @pytest.mark.parametrize("pass_cap", [0, 10])
-def test_render_accumulators_bit_exact(tracer, oracle, cam, scene_init, scene_random, which, pass_cap):
+@pytest.mark.parametrize("flags", [0, spt.FLAG_STRICT_LOOP])
+def test_render_accumulators_bit_exact(tracer, oracle, cam, scene_init, scene_random, which, pass_cap, flags):
     scene = scene_init if which == "init" else scene_random
     w, h, spp, depth = 96, 64, 8, 8
     tracer.set_scene(scene)
-    rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=pass_cap, seed=42, want_accum=True)
+    rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=pass_cap, seed=42, want_accum=True, flags=flags)
     oacc, octr = oracle.render_accum(scene, cam, w, h, spp, depth, pass_cap=pass_cap, seed=42)
     assert_accum_equal(acc, oacc)
     assert np.array_equal(rgb, oracle.resolve(oacc))
@@ -144,6 +186,7 @@ def test_sample_ranges_compose(tracer, oracle, cam, scene_init):
 
     w, h, depth = 48, 32, 6
     tracer.set_scene(scene_init)
+    tracer.set_stream(torch.cuda.current_stream().cuda_stream)  # same stream as the torch fills below
     acc = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
     parts = []
     for s0, s1 in [(0, 5), (5, 6), (6, 16)]:
@@ -161,6 +204,7 @@ def test_sample_ranges_compose(tracer, oracle, cam, scene_init):
     for s0, s1 in [(0, 5), (5, 6), (6, 16)]:
         oracle.render_accum(scene_init, cam, w, h, s1 - s0, depth, seed=11, sample_begin=s0, accum=want)
     assert_accum_equal(acc.cpu().numpy(), want)
+    tracer.set_stream(None)
 
 
 def test_resolve_device(tracer, oracle):
@@ -171,10 +215,12 @@ def test_resolve_device(tracer, oracle):
     acc = rng.uniform(0, 255 * 9, size=(h, w, 4)).astype(np.float32)
     acc[..., 3] = rng.integers(1, 12, size=(h, w)).astype(np.float32)
     acc[0, 0] = [0, 0, 0, 0]  # count 0 -> NaN colour -> byte 0 (TaskBasedPathTracer.hpp:198)
+    tracer.set_stream(torch.cuda.current_stream().cuda_stream)
     d_acc = torch.from_numpy(acc).cuda()
     d_rgb = torch.zeros((h, w, 3), dtype=torch.uint8, device="cuda")
     tracer.resolve(d_acc, w, h, d_rgb)
     tracer.synchronize()
+    tracer.set_stream(None)
     assert np.array_equal(d_rgb.cpu().numpy(), oracle.resolve(acc))
 
 

@@ -92,24 +92,12 @@ __device__ __forceinline__ V3 sample_sky(const CameraConst &cam, V3 dir)
     return vscale(vscale(v3(cam.sky[0], cam.sky[1], cam.sky[2]), k), 0.5f);
 }
 
-// SampleColorReflective (SingleThreadPathTracer.hpp:39-46; TaskBasedPathTracer.hpp:108-122)
-__device__ __forceinline__ void scatter_reflective(float4 sphere, float fuzz, V3 &dir, V3 &org, Rng &rng)
-{
-    org = contact_point(sphere, org, dir, false);
-    V3 const normal = contact_normal(org, sphere);
-    rng.open_event();
-    V3 const sh = rng.shell(); // drawn even when fuzz == 0
-    dir = vnormalize(vadd(vreflect(dir, normal), vscale(sh, fuzz)));
-}
-
-// SampleColorRefractive (SingleThreadPathTracer.hpp:48-92; TaskBasedPathTracer.hpp:124-180)
-__device__ __forceinline__ void scatter_refractive(float4 sphere, V3 &dir, V3 &org, Rng &rng)
+// SampleColorRefractive after its contact point / normal (SingleThreadPathTracer.hpp:54-91;
+// TaskBasedPathTracer.hpp:135-174): Schlick, refract in, jump to the far side of the SAME sphere (quirk Q9),
+// Schlick again, refract out or reflect.  `org` is the near contact point on entry.
+__device__ __forceinline__ void refract_through(float4 sphere, V3 n, V3 &dir, V3 &org, Rng &rng)
 {
     float const nAir = 1.0f, nGlass = 1.5f;
-    org = contact_point(sphere, org, dir, false);
-    V3 n = contact_normal(org, sphere);
-    rng.open_event();
-
     float c = vdot(vneg(n), dir);
     float r = fdiv(nAir, nGlass);
     float const q1 = fdiv(fsub(nAir, nGlass), fadd(nAir, nGlass));
@@ -124,7 +112,7 @@ __device__ __forceinline__ void scatter_refractive(float4 sphere, V3 &dir, V3 &o
     {
         float const k = fsub(fmul(r, c), fsqrt(fsub(1.f, fmul(fmul(r, r), fsub(1.f, fmul(c, c))))));
         dir = vnormalize(vadd(vscale(dir, r), vscale(n, k)));
-        org = contact_point(sphere, org, dir, true); // straight to the far side of the SAME sphere (quirk Q9)
+        org = contact_point(sphere, org, dir, true);
         n = vneg(contact_normal(org, sphere));
 
         c = vdot(vneg(n), dir);
@@ -173,54 +161,87 @@ struct Lane
 
 // After the closest-hit of the current segment returned `idx`: shade, and either finish the sample or set up
 // the next segment.  `geom` may live in shared or global memory.
+//
+// The reference has four handlers (sky / diffuse / reflective / refractive) plus the diffuse chain; lanes of a
+// warp are in different ones at the same time.  To keep the warp converged the work they share is hoisted
+// into single sites that every lane needing it executes together: ONE contact point + normal
+// (Collision.hpp:49-71), ONE rejection-sampled shell vector (Random.hpp:115-127; the loop whose trip count
+// varies most) and ONE final Normalize.  Only the few instructions that differ sit in per-material branches.
+// The arithmetic per lane is exactly the reference's.
 template <typename GeomPtr>
 __device__ __forceinline__ void shade_step(const TraceParams &p, GeomPtr geom, Lane &L, uint32_t idx, uint32_t &dropped)
 {
-    if (L.mode == MODE_DIFFUSE)
+    bool const hit = idx < p.n;
+    bool const inChain = L.mode == MODE_DIFFUSE;
+    uint32_t const m = (hit && !inChain) ? uint32_t(__ldg(p.mat + idx)) : 0u;
+    // while (--bounceCount && sphereIndex < g_sphereNumber) (SingleThreadPathTracer.hpp:28): the decrement
+    // happens whether or not the sphere test is reached
+    bool chainGoes = false;
+    if (inChain)
     {
-        // while (--bounceCount && sphereIndex < g_sphereNumber) (SingleThreadPathTracer.hpp:28-34)
-        if (--L.bounce && idx < p.n)
+        --L.bounce;
+        chainGoes = L.bounce != 0u && hit;
+    }
+    bool const isDiffuse = !inChain && m == 3u, isMirror = !inChain && m == 1u, isGlass = !inChain && m == 2u;
+    bool const surface = chainGoes || isDiffuse || isMirror || isGlass;
+
+    if (!surface)
+    {
+        // terminal: end of SampleColorDiffuse's chain, or SampleColorSkybox (miss / Material::SKYBOX sphere)
+        V3 const add = inChain ? L.chain : sample_sky(p.cam, L.dir);
+        L.sum = vadd(L.sum, add);
+        L.count = fadd(L.count, 1.f);
+        L.mode = MODE_NEW;
+        return;
+    }
+
+    // ---- shared site 1: contact point and normal (every handler starts with these two calls) ----
+    float4 const s = geom[idx];
+    V3 const pnt = contact_point(s, L.org, L.dir, false);
+    V3 const nrm = contact_normal(pnt, s);
+    L.rng.open_event();
+
+    if (isGlass)
+    {
+        L.org = pnt;
+        refract_through(s, nrm, L.dir, L.org, L.rng);
+    }
+    else
+    {
+        // ---- shared site 2: the shell vector (drawn even by a mirror with fuzz 0) ----
+        V3 const sh = L.rng.shell();
+        V3 v;
+        if (chainGoes)
         {
+            // sampleColor * 0.5; Normalize(origin + normal + shell): the origin really is added (quirk Q6)
             L.chain = vscale(L.chain, 0.5f);
-            float4 const s = geom[idx];
-            L.org = contact_point(s, L.org, L.dir, false);
-            L.rng.open_event();
-            // Normalize(origin + normal + shell): the origin really is added in (quirk Q6)
-            L.dir = vnormalize(vadd(vadd(L.org, contact_normal(L.org, s)), L.rng.shell()));
+            v = vadd(vadd(pnt, nrm), sh);
+        }
+        else if (isDiffuse)
+        {
+            // SampleColorDiffuse's head (SingleThreadPathTracer.hpp:23-26)
+            float4 const col = __ldg(p.shade + idx);
+            L.chain = vscale(v3(col.x, col.y, col.z), 0.5f);
+            v = vadd(nrm, sh);
+            L.bounce = p.depth;
+            L.mode = MODE_DIFFUSE;
         }
         else
         {
-            L.sum = vadd(L.sum, L.chain);
-            L.count = fadd(L.count, 1.f);
-            L.mode = MODE_NEW;
+            // SampleColorReflective (SingleThreadPathTracer.hpp:39-46): Reflect + shell * g_diffuses[idx]
+            v = vadd(vreflect(L.dir, nrm), vscale(sh, __ldg(p.shade + idx).w));
         }
-        return;
+        // ---- shared site 3: the final Normalize ----
+        L.dir = vnormalize(v);
+        L.org = pnt;
     }
-    // TraceAndSampleColor (SingleThreadPathTracer.hpp:94-112)
-    uint32_t const m = idx < p.n ? uint32_t(__ldg(p.mat + idx)) : 0u;
-    if (m == 3u) // Material::DIFFUSE -> SampleColorDiffuse (SingleThreadPathTracer.hpp:21-27)
+
+    if (isMirror || isGlass)
     {
-        float4 const s = geom[idx];
-        float4 const col = __ldg(p.shade + idx);
-        L.chain = vscale(v3(col.x, col.y, col.z), 0.5f);
-        L.org = contact_point(s, L.org, L.dir, false);
-        L.rng.open_event();
-        L.dir = vnormalize(vadd(contact_normal(L.org, s), L.rng.shell()));
-        L.bounce = p.depth;
-        L.mode = MODE_DIFFUSE;
-        return;
-    }
-    if (m == 1u || m == 2u)
-    {
-        float4 const s = geom[idx];
-        if (m == 1u)
-            scatter_reflective(s, __ldg(p.shade + idx).w, L.dir, L.org, L.rng);
-        else
-            scatter_refractive(s, L.dir, L.org, L.rng);
         ++L.specular;
         if (p.passCap && L.specular >= p.passCap)
         {
-            ++dropped; // the task tracer's pass loop ends: path dropped, sample not counted
+            ++dropped; // the task tracer's pass loop ends (TaskBasedPathTracer.hpp:81): dropped, not counted
             L.mode = MODE_NEW;
         }
         else if (L.specular >= kSpecularSafetyCap)
@@ -228,12 +249,7 @@ __device__ __forceinline__ void shade_step(const TraceParams &p, GeomPtr geom, L
             L.count = fadd(L.count, 1.f);
             L.mode = MODE_NEW;
         }
-        return;
     }
-    // miss, or Material::SKYBOX on a sphere (falls out of the switch): SampleColorSkybox
-    L.sum = vadd(L.sum, sample_sky(p.cam, L.dir));
-    L.count = fadd(L.count, 1.f);
-    L.mode = MODE_NEW;
 }
 
 __device__ __forceinline__ void warp_counter_add(unsigned long long *ctr, unsigned long long v)

@@ -162,7 +162,8 @@ static void rng_open_event(rng_t *r)
     }
 }
 
-/* GenerateUniformRealDist (Random.hpp:86-93): u(rand) = canonical * (max - min) + min */
+/* GenerateUniformRealDist (Random.hpp:86-93): u(rand) = canonical * (max - min) + min.
+ * One engine step per draw with the reference's output function -- the REFSEQ front end. */
 static float rng_uniform(rng_t *r, float lo, float hi)
 {
     uint32_t const d = spo_splitmix_next(&r->state);
@@ -171,16 +172,60 @@ static float rng_uniform(rng_t *r, float lo, float hi)
     return spo_u32_to_unit(d) * (hi - lo) + lo;
 }
 
+/* COUNTER front end: the same engine step (Random.hpp:37-39), but BOTH 32-bit halves of the mixed word
+ * z ^ (z >> 31) are used as draws (the reference keeps bits 31..62 only).  Halves the integer work per
+ * draw on the GPU; each half is a full-quality 32-bit output of splitmix64. */
+void spo_splitmix_pair(uint64_t *state, uint32_t *hi, uint32_t *lo)
+{
+    uint64_t z = (*state += SPO_GOLDEN);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    z = z ^ (z >> 31);
+    *hi = (uint32_t)(z >> 32);
+    *lo = (uint32_t)z;
+}
+
+static float map_uniform(uint32_t d, float lo, float hi) { return spo_u32_to_unit(d) * (hi - lo) + lo; }
+
+/* one draw; counter mode: one engine step, high half (low half unused) */
+static float rng_uniform1(rng_t *r, float lo, float hi)
+{
+    if (!r->counter_mode)
+        return rng_uniform(r, lo, hi);
+    uint32_t a, b;
+    spo_splitmix_pair(&r->state, &a, &b);
+    if (r->ctr)
+        r->ctr->rng_draws++;
+    return map_uniform(a, lo, hi);
+}
+
+/* two draws in call order; counter mode: one engine step (high half first) */
+static void rng_uniform2(rng_t *r, float lo, float hi, float *u0, float *u1)
+{
+    if (!r->counter_mode) {
+        *u0 = rng_uniform(r, lo, hi);
+        *u1 = rng_uniform(r, lo, hi);
+        return;
+    }
+    uint32_t a, b;
+    spo_splitmix_pair(&r->state, &a, &b);
+    if (r->ctr)
+        r->ctr->rng_draws += 2;
+    *u0 = map_uniform(a, lo, hi);
+    *u1 = map_uniform(b, lo, hi);
+}
+
 /* GenerateUniformDistInsideSphereVector == GenerateNormalDistInsideSphereVector (Random.hpp:115-141):
- * redraw while Length < radius, i.e. KEEP points of the +-0.5 cube that lie OUTSIDE the 0.5 ball. */
+ * redraw while Length < radius, i.e. KEEP points of the +-0.5 cube that lie OUTSIDE the 0.5 ball.
+ * Counter mode: attempt k takes engine steps 2k (x, y) and 2k+1 (z): any attempt is addressable. */
 static v4 rng_shell(rng_t *r)
 {
     float const radius = 0.5f;
     v4 res;
     do {
-        float const x = rng_uniform(r, -radius, radius);
-        float const y = rng_uniform(r, -radius, radius);
-        float const z = rng_uniform(r, -radius, radius);
+        float x, y, z;
+        rng_uniform2(r, -radius, radius, &x, &y);
+        z = rng_uniform1(r, -radius, radius);
         res = v3(x, y, z);
     } while (vlen(res) < radius);
     return res;
@@ -398,7 +443,7 @@ static void scatter_refractive(const trace_ctx *c, v4 *pdir, v4 *porg, uint32_t 
     float rSq = q1 * q1; /* pow(q, 2.f): exactly one rounded product (checked against powf in tests) */
     float schlick = rSq + (1.f - rSq) * spo_pow5(1.f - cc, c->pow_mode);
 
-    if (rng_uniform(rng, 0.f, 1.f) < schlick) {
+    if (rng_uniform1(rng, 0.f, 1.f) < schlick) {
         dir = vreflect(dir, n);
     } else if (r * sqrtf(1.f - cc * cc) < 1.f) {
         dir = vnormalize(vadd(vscale(dir, r), vscale(n, r * cc - sqrtf(1.f - r * r * (1.f - cc * cc)))));
@@ -411,7 +456,7 @@ static void scatter_refractive(const trace_ctx *c, v4 *pdir, v4 *porg, uint32_t 
         rSq = q2 * q2;
         schlick = rSq + (1.f - rSq) * spo_pow5(1.f - cc, c->pow_mode);
 
-        if (rng_uniform(rng, 0.f, 1.f) < schlick) {
+        if (rng_uniform1(rng, 0.f, 1.f) < schlick) {
             dir = vreflect(dir, n);
         } else if (r * sqrtf(1.f - cc * cc) < 1.f) {
             dir = vnormalize(vadd(vscale(dir, r), vscale(n, r * cc - sqrtf(1.f - r * r * (1.f - cc * cc)))));
@@ -471,8 +516,8 @@ int spo_sample_radiance(const spo_scene *sc, const spo_camera *cam, const spo_pa
     trace_ctx const c = {sc, cam, p->depth, p->pass_cap, p->pow_mode, ctr};
     rng_t rng = {0, spo_stream_key(p->seed, y * p->width + x, sample), 0, 1, ctr};
     rng_open_event(&rng);
-    float const xiU = rng_uniform(&rng, -1.f, 1.f);
-    float const xiV = rng_uniform(&rng, -1.f, 1.f);
+    float xiU, xiV;
+    rng_uniform2(&rng, -1.f, 1.f, &xiU, &xiV);
     v4 const d = primary_direction(cam, p->width, p->height, x, y, xiU, xiV);
     v4 out = v3(0.f, 0.f, 0.f);
     if (ctr)

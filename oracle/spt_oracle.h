@@ -70,6 +70,7 @@ typedef struct spo_counters {
 
 /* ---- RNG (include/Random.hpp:11-46, :86-93, :115-127) ---- */
 uint32_t spo_splitmix_next(uint64_t *state);
+void spo_splitmix_pair(uint64_t *state, uint32_t *hi, uint32_t *lo); /* counter front end: both halves */
 uint64_t spo_splitmix_seed(uint32_t seed32);             /* seed << 31 | seed  (Random.hpp:20) */
 float spo_u32_to_unit(uint32_t draw);                    /* libstdc++ generate_canonical<float,24> */
 uint64_t spo_stream_key(uint64_t seed, uint32_t pixel, uint32_t sample);

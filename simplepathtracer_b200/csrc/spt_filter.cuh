@@ -132,19 +132,24 @@ __device__ __forceinline__ void filter_pair(const FilterPair *__restrict__ rec, 
 
 // FindClosestIntersectionSphere (Collision.hpp:87-109): pre-filter + exact evaluation of the candidates.
 // Returns exactly what closest_hit_strict returns.  `exactEvals` counts exact_sphere calls (instrumentation).
+// `live` = false marks a lane that only keeps its warp company (finished pixel): it runs the convergent
+// filter loop with the rest of the warp but never enters the exact path.
 template <typename GeomPtr>
 __device__ __forceinline__ uint32_t closest_hit_filtered(const FilterScene &fs, GeomPtr geom, uint32_t n, V3 dir, V3 org,
-                                                         uint32_t &exactEvals)
+                                                         uint32_t &exactEvals, bool live = true)
 {
     uint32_t minIndex = n;
     float minDistanceSq = FLT_MAX;
     float const od = vdot(org, dir);
 
-    for (uint32_t b = 0; b < fs.nBig; ++b)
+    if (live)
     {
-        uint32_t const i = fs.bigIdx[b];
-        exact_sphere<false>(geom[i], i, dir, org, od, minIndex, minDistanceSq);
-        ++exactEvals;
+        for (uint32_t b = 0; b < fs.nBig; ++b)
+        {
+            uint32_t const i = fs.bigIdx[b];
+            exact_sphere<false>(geom[i], i, dir, org, od, minIndex, minDistanceSq);
+            ++exactEvals;
+        }
     }
 
     FilterRay const fr = make_filter_ray(dir, org, od, fs.amax);
@@ -163,7 +168,7 @@ __device__ __forceinline__ uint32_t closest_hit_filtered(const FilterScene &fs, 
                     filter_pair(rec + pp, fr, mask);
                 rec += kWordSpheres / 2;
             }
-            cand[w] = ~mask; // bit (31 - j) set <=> sphere j of the word is a candidate
+            cand[w] = live ? ~mask : 0u; // bit (31 - j) set <=> sphere j of the word is a candidate
         }
         // exact sequence on this lane's candidates; lanes without any idle here (the only divergent part)
         for (;;)

@@ -104,7 +104,7 @@ __device__ __forceinline__ void refract_through(float4 sphere, V3 n, V3 &dir, V3
     float rSq = fmul(q1, q1); // pow(q, 2.f)
     float schlick = fadd(rSq, fmul(fsub(1.f, rSq), pow5(fsub(1.f, c))));
 
-    if (rng.uniform(0.f, 1.f) < schlick)
+    if (rng.uniform1(0.f, 1.f) < schlick)
     {
         dir = vreflect(dir, n);
     }
@@ -121,7 +121,7 @@ __device__ __forceinline__ void refract_through(float4 sphere, V3 n, V3 &dir, V3
         rSq = fmul(q2, q2);
         schlick = fadd(rSq, fmul(fsub(1.f, rSq), pow5(fsub(1.f, c))));
 
-        if (rng.uniform(0.f, 1.f) < schlick)
+        if (rng.uniform1(0.f, 1.f) < schlick)
         {
             dir = vreflect(dir, n);
         }
@@ -159,6 +159,73 @@ struct Lane
     uint32_t mode, bounce, specular, sample;
 };
 
+// Warp-cooperative rejection sampling of the shell vector (Random.hpp:115-141).
+//
+// Each lane that needs a vector owns a counter-addressable stream (state0): attempt t is a pure function of
+// (state0, t) (shell_attempt).  Run lane-by-lane the do/while costs the warp max-over-lanes trips (about 6 for
+// an acceptance of 0.476) with most lanes idle.  Here the `m` lanes still pending are given per = 2^k <= 32/m
+// helper lanes each; in one round helper a of pending lane r evaluates attempt base_r + a, a ballot collects
+// the verdicts, and every pending lane takes the FIRST accepted attempt (lowest t) -- exactly the vector the
+// sequential loop would have produced -- or moves its base on by `per`.  Two rounds almost always finish.
+// Must be called by all 32 lanes of the warp (need = false for lanes that want nothing).
+struct ShellSlots
+{
+    unsigned long long st[32];
+    uint32_t base[32];
+};
+
+__device__ __forceinline__ V3 coop_shell(bool need, unsigned long long state0, ShellSlots &slot)
+{
+    uint32_t const lane = threadIdx.x & 31u;
+    V3 sh = v3(0.f, 0.f, 0.f);
+    uint32_t base = 0;
+    uint32_t pending = __ballot_sync(0xffffffffu, need);
+    while (pending) // warp-uniform
+    {
+        uint32_t const m = __popc(pending);
+        uint32_t const lg = m <= 1u ? 5u : uint32_t(__clz(int(m - 1u))) - 27u; // per = largest 2^k with m * 2^k <= 32
+        uint32_t const per = 1u << lg;
+        uint32_t const r = __popc(pending & ((1u << lane) - 1u)); // my rank among the pending lanes
+        if (need)
+        {
+            slot.st[r] = state0;
+            slot.base[r] = base;
+        }
+        __syncwarp();
+        uint32_t const g = lane >> lg, a = lane & (per - 1u);
+        bool const valid = g < m;
+        unsigned long long const s0 = slot.st[valid ? g : 0u];
+        uint32_t const b0 = slot.base[valid ? g : 0u];
+        __syncwarp();
+        V3 cand;
+        bool const ok = shell_attempt(s0, b0 + a, cand) && valid;
+        uint32_t const verdict = __ballot_sync(0xffffffffu, ok);
+        uint32_t src = lane;
+        bool got = false;
+        if (need)
+        {
+            uint32_t const field = per == 32u ? verdict : ((verdict >> (r << lg)) & ((1u << per) - 1u));
+            if (field)
+            {
+                src = (r << lg) + uint32_t(__ffs(int(field)) - 1);
+                got = true;
+            }
+            else
+                base += per;
+        }
+        float const sx = __shfl_sync(0xffffffffu, cand.x, src);
+        float const sy = __shfl_sync(0xffffffffu, cand.y, src);
+        float const sz = __shfl_sync(0xffffffffu, cand.z, src);
+        if (got)
+        {
+            sh = v3(sx, sy, sz);
+            need = false;
+        }
+        pending = __ballot_sync(0xffffffffu, need);
+    }
+    return sh;
+}
+
 // After the closest-hit of the current segment returned `idx`: shade, and either finish the sample or set up
 // the next segment.  `geom` may live in shared or global memory.
 //
@@ -169,47 +236,56 @@ struct Lane
 // varies most) and ONE final Normalize.  Only the few instructions that differ sit in per-material branches.
 // The arithmetic per lane is exactly the reference's.
 template <typename GeomPtr>
-__device__ __forceinline__ void shade_step(const TraceParams &p, GeomPtr geom, Lane &L, uint32_t idx, uint32_t &dropped)
+__device__ __forceinline__ void shade_step(const TraceParams &p, GeomPtr geom, Lane &L, uint32_t idx, uint32_t &dropped,
+                                           bool live, ShellSlots &slots)
 {
     bool const hit = idx < p.n;
     bool const inChain = L.mode == MODE_DIFFUSE;
-    uint32_t const m = (hit && !inChain) ? uint32_t(__ldg(p.mat + idx)) : 0u;
+    uint32_t const m = (live && hit && !inChain) ? uint32_t(__ldg(p.mat + idx)) : 0u;
     // while (--bounceCount && sphereIndex < g_sphereNumber) (SingleThreadPathTracer.hpp:28): the decrement
     // happens whether or not the sphere test is reached
     bool chainGoes = false;
-    if (inChain)
+    if (live && inChain)
     {
         --L.bounce;
         chainGoes = L.bounce != 0u && hit;
     }
-    bool const isDiffuse = !inChain && m == 3u, isMirror = !inChain && m == 1u, isGlass = !inChain && m == 2u;
+    bool const isDiffuse = live && !inChain && m == 3u, isMirror = live && !inChain && m == 1u,
+               isGlass = live && !inChain && m == 2u;
     bool const surface = chainGoes || isDiffuse || isMirror || isGlass;
 
-    if (!surface)
+    if (live && !surface)
     {
         // terminal: end of SampleColorDiffuse's chain, or SampleColorSkybox (miss / Material::SKYBOX sphere)
         V3 const add = inChain ? L.chain : sample_sky(p.cam, L.dir);
         L.sum = vadd(L.sum, add);
         L.count = fadd(L.count, 1.f);
         L.mode = MODE_NEW;
-        return;
     }
 
     // ---- shared site 1: contact point and normal (every handler starts with these two calls) ----
-    float4 const s = geom[idx];
-    V3 const pnt = contact_point(s, L.org, L.dir, false);
-    V3 const nrm = contact_normal(pnt, s);
-    L.rng.open_event();
+    float4 s = make_float4(0.f, 0.f, 0.f, 1.f);
+    V3 pnt = v3(0.f, 0.f, 0.f), nrm = v3(0.f, 0.f, 0.f);
+    if (surface)
+    {
+        s = geom[idx];
+        pnt = contact_point(s, L.org, L.dir, false);
+        nrm = contact_normal(pnt, s);
+        L.rng.open_event();
+    }
 
     if (isGlass)
     {
         L.org = pnt;
         refract_through(s, nrm, L.dir, L.org, L.rng);
     }
-    else
+
+    // ---- shared site 2: the shell vector (drawn even by a mirror with fuzz 0), sampled by the whole warp ----
+    bool const needShell = surface && !isGlass;
+    V3 const sh = coop_shell(needShell, L.rng.state, slots);
+
+    if (needShell)
     {
-        // ---- shared site 2: the shell vector (drawn even by a mirror with fuzz 0) ----
-        V3 const sh = L.rng.shell();
         V3 v;
         if (chainGoes)
         {
@@ -310,38 +386,64 @@ __global__ void __launch_bounds__(kBlockThreads) trace_megakernel(const __grid_c
     uint32_t const pixel = y * p.width + x;
     float const widthF = __uint2float_rn(p.width), heightF = __uint2float_rn(p.height);
 
+    __shared__ ShellSlots shellSlots[kBlockThreads / 32];
+    ShellSlots &slots = shellSlots[threadIdx.x >> 5];
+
     Lane L;
     L.sum = v3(0.f, 0.f, 0.f);
     L.count = 0.f;
     L.mode = MODE_NEW;
     L.sample = p.sampleBegin;
+    L.dir = v3(0.f, 0.f, 1.f);
+    L.org = v3(0.f, 0.f, 0.f);
+    L.chain = v3(0.f, 0.f, 0.f);
+    L.rng.state = 0;
+    L.rng.key = 0;
+    L.rng.event = 0;
+    L.rng.word = 0;
+    L.bounce = 0;
+    L.specular = 0;
     uint32_t segments = 0, dropped = 0, exactEvals = 0;
+    uint64_t const pixKey = pixel_key(p.seed, pixel);
 
-    if (inside)
+    // All 32 lanes stay in the loop until the whole warp is finished (the shell sampler is a warp
+    // collective); a lane whose pixel is complete is carried along with live = false.
+    bool live = inside;
+    for (;;)
     {
-        for (;;)
+        if (live && L.mode == MODE_NEW)
         {
-            if (L.mode == MODE_NEW)
+            if (L.sample >= p.sampleEnd)
             {
-                if (L.sample >= p.sampleEnd)
-                    break;
+                live = false;
+            }
+            else
+            {
                 // next camera sample (SingleThreadPathTracer.hpp:123-128)
-                L.rng.key = stream_key(p.seed, pixel, L.sample);
+                L.rng.key = stream_key(pixKey, L.sample);
                 L.rng.event = 0;
                 L.rng.open_event();
-                float const xiU = L.rng.uniform(-1.f, 1.f);
-                float const xiV = L.rng.uniform(-1.f, 1.f);
+                float xiU, xiV;
+                L.rng.uniform2(-1.f, 1.f, xiU, xiV);
                 L.dir = primary_direction(p.cam, widthF, heightF, x, y, xiU, xiV);
                 L.org = v3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
                 L.specular = 0;
                 L.mode = MODE_TRACE;
                 ++L.sample;
             }
-            uint32_t const idx = STRICT ? closest_hit_strict(geom, p.n, L.dir, L.org)
-                                        : closest_hit_filtered(fs, geom, p.n, L.dir, L.org, exactEvals);
-            ++segments;
-            shade_step(p, geom, L, idx, dropped);
         }
+        if (!__any_sync(0xffffffffu, live))
+            break;
+        uint32_t idx;
+        if (STRICT)
+            idx = live ? closest_hit_strict(geom, p.n, L.dir, L.org) : p.n;
+        else
+            idx = closest_hit_filtered(fs, geom, p.n, L.dir, L.org, exactEvals, live);
+        segments += live ? 1u : 0u;
+        shade_step(p, geom, L, idx, dropped, live, slots);
+    }
+    if (inside)
+    {
         // one lane owns one pixel for the whole launch: plain read-modify-write, no atomics
         float4 a = p.accum[pixel];
         a.x = fadd(a.x, L.sum.x);

@@ -143,3 +143,17 @@ def test_restatement_independent_of_pass_cap_when_paths_are_short(oracle):
     a, ca = oracle.render_accum(scene, cam, 32, 32, 4, 8, pass_cap=0, seed=2)
     b, cb = oracle.render_accum(scene, cam, 32, 32, 4, 8, pass_cap=1000, seed=2)
     assert np.array_equal(a, b) and cb["dropped"] == 0
+
+
+def test_shell_acceptance_needs_no_square_root():
+    """The CUDA path tests lensq < 0.25f where Random.hpp:124 tests sqrtf(lensq) < 0.5f.  They agree for
+    EVERY float: sqrt is monotone, so it is enough to look at both sides of the boundary."""
+    q = np.float32(0.25)
+    around = q.view(np.uint32).astype(np.int64) + np.arange(-100000, 100001)
+    xs = around.astype(np.uint32).view(np.float32)
+    assert np.array_equal(np.sqrt(xs) < np.float32(0.5), xs < q)
+    below, at = np.nextafter(q, np.float32(0)), q
+    assert np.sqrt(below) < np.float32(0.5) and not (np.sqrt(at) < np.float32(0.5))
+    rng = np.random.default_rng(0)
+    xs = rng.uniform(0, 0.75, 2_000_000).astype(np.float32)
+    assert np.array_equal(np.sqrt(xs) < np.float32(0.5), xs < q)

@@ -29,7 +29,7 @@ class SptError(RuntimeError):
 
 
 def library_path() -> str:
-    return os.path.join(HERE, LIB_NAME)
+    return os.environ.get("SPT_CUDA_LIB") or os.path.join(HERE, LIB_NAME)
 
 
 NVCC_FLAGS = [

@@ -22,6 +22,9 @@ constexpr int kBlockWarpsX = 4, kBlockWarpsY = 2;
 constexpr int kTileW = kWarpW * kBlockWarpsX; // 32
 constexpr int kTileH = kWarpH * kBlockWarpsY; // 8
 constexpr int kBlockThreads = kTileW * kTileH; // 256
+#ifndef SPT_MIN_BLOCKS
+#define SPT_MIN_BLOCKS 4 // resident blocks per SM the register allocation aims at
+#endif
 
 struct TraceParams
 {
@@ -352,7 +355,7 @@ __device__ __forceinline__ void lane_pixel(const TraceParams &p, uint32_t &x, ui
 // (strict: geometry only), 0 = nothing (lists larger than shared memory are read through L1/L2 with
 // warp-uniform addresses).  STRICT: no pre-filter, every sphere through the exact sequence.
 template <int STAGE, bool STRICT>
-__global__ void __launch_bounds__(kBlockThreads) trace_megakernel(const __grid_constant__ TraceParams p)
+__global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_megakernel(const __grid_constant__ TraceParams p)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     __shared__ __align__(8) uint64_t mbar;

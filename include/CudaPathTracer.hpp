@@ -1,0 +1,135 @@
+// CudaPathTracer.hpp -- the drop-in: RenderSegmentCuda / RenderSegmentCudaWavefront next to the reference's
+//
+//     void RenderSegment(RenderSegmentData)       /root/reference/include/SingleThreadPathTracer.hpp:114
+//     void RenderSegmentTask(RenderSegmentData)   /root/reference/include/TaskBasedPathTracer.hpp:54
+//
+// Same signature, same implicit inputs (the scene / camera / config globals of Globals.hpp) and the same
+// output (8-bit gamma-encoded RGB written in place into g_data at the reference's flipped pixel slots), so it
+// slots into RenderJob (Renderer.hpp:242-255) or RenderImage (Renderer.hpp:304-308) by changing one call.
+//
+// Include it AFTER either
+//   * the reference's own headers (Definitions.hpp, Globals.hpp, ...)  -> see INTEGRATION.md, or
+//   * this repo's mirror "spt_host/Scene.hpp"                          -> headless builds.
+// Both provide: RenderSegmentData, Material, math::Vec4 (.xyzw), math::Mat4 (.array), g_spheres, g_radii,
+// g_materials, g_colors, g_diffuses, g_sphereNumber, viewMatrix, eyePos, initColor, g_width, g_height,
+// g_samples, g_bounces, g_data.
+//
+// Link with libspt_cuda.so (include/spt_cuda.h).  There is no CPU fallback: any failure throws.
+#pragma once
+
+#include "spt_cuda.h"
+
+#include <cstdint>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace spt_cuda
+{
+struct State
+{
+    SptContext *ctx = nullptr;
+    std::mutex lock;
+    bool sceneUploaded = false;
+    int device = 0;
+    uint64_t seed = 1;   // counter-RNG seed (the reference seeds from the clock, Random.hpp:88-89)
+    uint32_t flags = 0;  // SPT_FLAG_*
+};
+
+inline State &GetState()
+{
+    static State s;
+    return s;
+}
+
+inline void Check(int rc, char const *what)
+{
+    if (rc != SPT_OK)
+        throw std::runtime_error(std::string("CudaPathTracer: ") + what + ": " + spt_cuda_last_error());
+}
+
+// Call after the scene globals change (InitSpheres / GenerateSpheres); the first render uploads lazily.
+inline void InvalidateScene()
+{
+    State &s = GetState();
+    std::lock_guard<std::mutex> g(s.lock);
+    s.sceneUploaded = false;
+}
+
+inline void SetDevice(int device) { GetState().device = device; }
+inline void SetSeed(uint64_t seed) { GetState().seed = seed; }
+
+inline SptContext *Acquire()
+{
+    State &s = GetState();
+    std::lock_guard<std::mutex> g(s.lock);
+    if (!s.ctx)
+        Check(spt_cuda_create(&s.ctx, s.device), "spt_cuda_create");
+    if (!s.sceneUploaded)
+    {
+        std::vector<uint8_t> mats(g_sphereNumber);
+        for (uint32_t i = 0; i < g_sphereNumber; ++i)
+            mats[i] = static_cast<uint8_t>(g_materials[i]);
+        SptScene sc{};
+        sc.n = g_sphereNumber;
+        sc.centers4 = g_spheres[0].xyzw;
+        sc.radii = g_radii.data();
+        sc.materials = mats.data();
+        sc.colors4 = g_colors[0].xyzw;
+        sc.fuzz = g_diffuses.data();
+        Check(spt_cuda_set_scene(s.ctx, &sc), "spt_cuda_set_scene");
+        s.sceneUploaded = true;
+    }
+    return s.ctx;
+}
+
+inline void Shutdown()
+{
+    State &s = GetState();
+    std::lock_guard<std::mutex> g(s.lock);
+    if (s.ctx)
+        spt_cuda_destroy(s.ctx);
+    s.ctx = nullptr;
+    s.sceneUploaded = false;
+}
+
+inline void Render(RenderSegmentData segment, uint32_t passCap, uint32_t variant)
+{
+    static_assert(sizeof(math::Vec4) == 16, "Vec4 must be 4 packed floats (Math.hpp:9-14)");
+    SptContext *ctx = Acquire();
+    SptCamera cam{};
+    for (int k = 0; k < 16; ++k)
+        cam.view[k] = viewMatrix.array[k];
+    // the tracers only ever multiply the matrix with a w = 0 vector and read lanes 0..2 of the result, so row 3
+    // and column 3 never reach a pixel; the reference's identity initialiser has a 1 there, its camera basis a 0
+    cam.view[3] = cam.view[7] = cam.view[11] = cam.view[12] = cam.view[13] = cam.view[14] = cam.view[15] = 0.f;
+    for (int k = 0; k < 3; ++k)
+    {
+        cam.eye[k] = eyePos.xyzw[k];
+        cam.sky[k] = initColor.xyzw[k];
+    }
+    SptParams p{};
+    p.width = g_width;
+    p.height = g_height;
+    p.depth = g_bounces;
+    p.pass_cap = passCap;
+    p.sample_begin = 0;
+    p.sample_end = g_samples;
+    p.seed = GetState().seed;
+    p.variant = variant;
+    p.flags = GetState().flags;
+    SptSegment const seg{segment.yBegin, segment.yEnd, segment.xBegin, segment.xEnd};
+    Check(spt_cuda_render(ctx, &cam, &p, seg, g_data, nullptr), "spt_cuda_render");
+}
+} // namespace spt_cuda
+
+// RenderSegment on the GPU: recursive-tracer semantics (specular recursion unbounded), megakernel.
+inline void RenderSegmentCuda(RenderSegmentData segment) { spt_cuda::Render(segment, 0u, SPT_VARIANT_MEGAKERNEL); }
+
+// RenderSegmentTask on the GPU: queue-tracer semantics (10 passes, drop + per-pixel count,
+// TaskBasedPathTracer.hpp:81,196-198), wavefront variant.
+inline void RenderSegmentCudaWavefront(RenderSegmentData segment) { spt_cuda::Render(segment, 10u, SPT_VARIANT_WAVEFRONT); }
+
+// RenderSegmentTask semantics on the megakernel (what bench.py times)
+inline void RenderSegmentTaskCuda(RenderSegmentData segment) { spt_cuda::Render(segment, 10u, SPT_VARIANT_MEGAKERNEL); }

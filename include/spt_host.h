@@ -1,0 +1,37 @@
+/*
+ * spt_host.h -- C exports of the host-side mirror (include/spt_host/*.hpp) for bindings and tools:
+ * the reference's scene generators with an injectable seed, its camera basis, and its BMP output.
+ *
+ *   spt_host_init_spheres      InitSpheres()      /root/reference/include/SceneGenerators.hpp:68-133
+ *   spt_host_generate_spheres  GenerateSpheres()  /root/reference/include/SceneGenerators.hpp:6-66
+ *   spt_host_generate_metal_glass / _lattice       BASELINE.json configs 4 / 5 (no reference counterpart)
+ *   spt_host_camera_basis      Transpose(CreateCameraBasisMatrix(...))  include/Math.hpp:198-231, Renderer.hpp:321
+ *   spt_host_save_bmp          stbi_write_bmp as called by io::SaveImage  include/IOHelpers.hpp:24-27
+ *
+ * Generators return the sphere count; arrays are filled when cap >= count (call with cap = 0 to size).
+ * Layout = the reference's SoA globals (include/Globals.hpp:31-37).
+ */
+#ifndef SPT_HOST_H
+#define SPT_HOST_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+uint32_t spt_host_init_spheres(uint32_t seed, uint32_t cap, float *centers4, float *radii, uint8_t *materials,
+                               float *colors4, float *fuzz);
+uint32_t spt_host_generate_spheres(uint32_t seed, uint32_t cap, float *centers4, float *radii, uint8_t *materials,
+                                   float *colors4, float *fuzz);
+uint32_t spt_host_generate_metal_glass(uint32_t seed, uint32_t count, uint32_t cap, float *centers4, float *radii,
+                                       uint8_t *materials, float *colors4, float *fuzz);
+uint32_t spt_host_generate_lattice(uint32_t seed, uint32_t side, uint32_t cap, float *centers4, float *radii,
+                                   uint8_t *materials, float *colors4, float *fuzz);
+void spt_host_camera_basis(const float eye[3], const float look[3], const float up[3], float view16[16]);
+int spt_host_save_bmp(const char *path, uint32_t width, uint32_t height, const uint8_t *rgb8);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPT_HOST_H */

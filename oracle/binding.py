@@ -103,6 +103,8 @@ def build_oracle(ref: bool = True) -> None:
     targets = ["all"]
     if ref and os.path.isdir(os.path.join(REF_ROOT, "include")):
         targets.append("ref")
+        if os.path.exists(os.path.join(os.path.dirname(HERE), "simplepathtracer_b200", "libspt_cuda.so")):
+            targets.append("integration")  # the drop-in shown inside the reference's own translation unit
     subprocess.run(["make", "-s", "-C", HERE] + targets, check=True)
 
 

@@ -26,6 +26,12 @@ from .binding import (  # noqa: F401
     REFLECTIVE,
     REFRACTIVE,
     SKYBOX,
+    init_spheres,
+    generate_spheres,
+    generate_metal_glass,
+    generate_lattice,
+    make_camera,
+    save_bmp,
 )
 
 __version__ = "0.1.0"

@@ -36,7 +36,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
     "--fmad=false",  # belt and braces: every rounded op is spelled out with __f*_rn as well
-    "-Xcompiler", "-fPIC", "-shared",
+    "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-shared",
 ]
 
 
@@ -168,6 +168,10 @@ EXPORTS = [
     "spt_cuda_closest_hit", "spt_cuda_get_counters", "spt_cuda_reset_counters", "spt_cuda_get_timing",
     "spt_cuda_measure_fp32_peak", "spt_cuda_last_error", "spt_cuda_version",
 ]
+HOST_EXPORTS = [
+    "spt_host_init_spheres", "spt_host_generate_spheres", "spt_host_generate_metal_glass", "spt_host_generate_lattice",
+    "spt_host_camera_basis", "spt_host_save_bmp",
+]
 
 _LIB = None
 
@@ -201,6 +205,16 @@ def load_library():
     L.spt_cuda_reset_counters.argtypes = [C.c_void_p]
     L.spt_cuda_get_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
     L.spt_cuda_measure_fp32_peak.argtypes = [C.c_void_p, f32p, f32p]
+    gen = [C.c_uint32, C.c_uint32, f32p, f32p, u8p, f32p, f32p]
+    L.spt_host_init_spheres.argtypes = gen
+    L.spt_host_generate_spheres.argtypes = gen
+    L.spt_host_generate_metal_glass.argtypes = [C.c_uint32] + gen
+    L.spt_host_generate_lattice.argtypes = [C.c_uint32] + gen
+    for f in (L.spt_host_init_spheres, L.spt_host_generate_spheres, L.spt_host_generate_metal_glass, L.spt_host_generate_lattice):
+        f.restype = C.c_uint32
+    L.spt_host_camera_basis.argtypes = [f32p, f32p, f32p, f32p]
+    L.spt_host_camera_basis.restype = None
+    L.spt_host_save_bmp.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, u8p]
     _LIB = L
     return L
 
@@ -344,3 +358,50 @@ class PathTracer:
         a, b = C.c_float(), C.c_float()
         self._check(self.L.spt_cuda_measure_fp32_peak(self.h, C.byref(a), C.byref(b)))
         return float(a.value), float(b.value)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# host mirror (include/spt_host.h): the reference's scene generators / camera / BMP output, no GPU needed
+def _generate(fn, *head) -> Scene:
+    n = fn(*head, 0, None, None, None, None, None)
+    sc = Scene(np.zeros((n, 4), np.float32), np.zeros(n, np.float32), np.zeros(n, np.uint8), np.zeros((n, 4), np.float32),
+               np.zeros(n, np.float32))
+    got = fn(*head, n, sc.centers.ctypes.data_as(f32p), sc.radii.ctypes.data_as(f32p), sc.materials.ctypes.data_as(u8p),
+             sc.colors.ctypes.data_as(f32p), sc.fuzz.ctypes.data_as(f32p))
+    assert got == n
+    return sc
+
+
+def init_spheres(seed: int = 1) -> Scene:
+    """InitSpheres() (SceneGenerators.hpp:68-133) with the RNG seeded by `seed`."""
+    return _generate(load_library().spt_host_init_spheres, seed)
+
+
+def generate_spheres(seed: int = 1) -> Scene:
+    """GenerateSpheres() (SceneGenerators.hpp:6-66) with the RNG seeded by `seed`."""
+    return _generate(load_library().spt_host_generate_spheres, seed)
+
+
+def generate_metal_glass(seed: int = 4, count: int = 500) -> Scene:
+    """BASELINE config 4: ground + `count` mirror / glass spheres."""
+    return _generate(load_library().spt_host_generate_metal_glass, seed, count)
+
+
+def generate_lattice(seed: int = 5, side: int = 128) -> Scene:
+    """BASELINE config 5: ground + side*side - 1 spheres on a jittered lattice."""
+    return _generate(load_library().spt_host_generate_lattice, seed, side)
+
+
+def make_camera(eye=(0, 1, -3), look=(0, 1, 0), up=(0, 1, 0), sky=(137, 207, 240)) -> Camera:
+    """viewMatrix = Transpose(CreateCameraBasisMatrix(eyePos, lookAt, upDir)) (Renderer.hpp:321)."""
+    view = np.zeros(16, np.float32)
+    load_library().spt_host_camera_basis((C.c_float * 3)(*eye), (C.c_float * 3)(*look), (C.c_float * 3)(*up), view.ctypes.data_as(f32p))
+    return Camera(view.reshape(4, 4), np.array([*eye, 0], np.float32), np.array([*sky, 0], np.float32))
+
+
+def save_bmp(path: str, rgb8: np.ndarray) -> None:
+    """io::SaveImage's serialiser (stbi_write_bmp-compatible)."""
+    rgb8 = np.ascontiguousarray(rgb8, np.uint8)
+    h, w = rgb8.shape[:2]
+    if not load_library().spt_host_save_bmp(path.encode(), w, h, rgb8.ctypes.data_as(u8p)):
+        raise SptError("cannot write " + path)

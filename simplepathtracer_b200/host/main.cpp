@@ -1,0 +1,82 @@
+// spt_headless -- the reference's TracePaths() without a window: scene -> viewMatrix -> RenderSegmentCuda over the
+// whole image -> io::SaveImage (BMP).  Stands in for Main.cpp:3-6 + Renderer.hpp:316-357 (MainLoop) with the
+// GL/GLFW parts left out (no graphics stack on this box) and the compile-time constants of Globals.hpp:8-18
+// turned into flags.
+//
+//   spt_headless [--scene reference|random|metalglass|lattice] [--seed S] [--width W] [--height H]
+//                [--spp N] [--depth D] [--tracer recursive|task|wavefront] [--tiles T] [--out file.bmp]
+#include "../../include/spt_host/Scene.hpp"
+#include "../../include/spt_host/SceneGenerators.hpp"
+#include "../../include/spt_host/Image.hpp"
+#include "../../include/CudaPathTracer.hpp"
+
+#include <chrono>
+#include <cstring>
+#include <iostream>
+#include <string>
+#include <thread>
+
+int main(int argc, char **argv)
+{
+    std::string scene = "reference", tracer = "recursive", out;
+    uint32_t seed = 1, width = 1440, height = 1440, spp = 100, depth = 10, tiles = 1;
+    for (int i = 1; i + 1 < argc; i += 2)
+    {
+        std::string const k = argv[i], v = argv[i + 1];
+        if (k == "--scene") scene = v;
+        else if (k == "--seed") seed = uint32_t(std::stoul(v));
+        else if (k == "--width") width = uint32_t(std::stoul(v));
+        else if (k == "--height") height = uint32_t(std::stoul(v));
+        else if (k == "--spp") spp = uint32_t(std::stoul(v));
+        else if (k == "--depth") depth = uint32_t(std::stoul(v));
+        else if (k == "--tracer") tracer = v;
+        else if (k == "--tiles") tiles = uint32_t(std::stoul(v));
+        else if (k == "--out") out = v;
+        else { std::cerr << "unknown flag " << k << "\n"; return 2; }
+    }
+    SetRenderConfig(width, height, spp, depth);
+    UpdateViewMatrix(); // Renderer.hpp:321
+    if (scene == "reference") InitSpheres(seed);            // eSceneGenerator::REFERENCE
+    else if (scene == "random") GenerateSpheres(seed);      // eSceneGenerator::RANDOM
+    else if (scene == "metalglass") GenerateMetalGlassSpheres(seed);
+    else if (scene == "lattice") GenerateLatticeSpheres(seed);
+    else { std::cerr << "unknown scene " << scene << "\n"; return 2; }
+    spt_cuda::SetSeed(seed);
+    spt_cuda::InvalidateScene();
+
+    auto const t0 = std::chrono::high_resolution_clock::now();
+    try
+    {
+        // tiles == 1: RenderImage's single {0, H, 0, W} call (Renderer.hpp:304-308); tiles > 1: the
+        // threadCount x threadCount grid of RenderImageParallelMain (Renderer.hpp:264-274), one call per tile
+        uint32_t const sw = (g_width + tiles - 1) / tiles, sh = (g_height + tiles - 1) / tiles;
+        uint32_t done = 0;
+        for (uint32_t j = 0; j < tiles; ++j)
+            for (uint32_t i = 0; i < tiles; ++i)
+            {
+                RenderSegmentData const seg{sh * j, std::min(sh * (j + 1), g_height), sw * i, std::min(sw * (i + 1), g_width)};
+                if (tiles > 1)
+                    std::cout << ++done << "/" << tiles * tiles << std::endl; // Renderer.hpp:285
+                if (tracer == "recursive") RenderSegmentCuda(seg);
+                else if (tracer == "task") RenderSegmentTaskCuda(seg);
+                else if (tracer == "wavefront") RenderSegmentCudaWavefront(seg);
+                else { std::cerr << "unknown tracer " << tracer << "\n"; return 2; }
+            }
+    }
+    catch (std::exception const &e)
+    {
+        std::cerr << e.what() << "\n";
+        return 1;
+    }
+    auto const dt = std::chrono::high_resolution_clock::now() - t0;
+    std::cout << "Duration: " << std::chrono::duration_cast<std::chrono::milliseconds>(dt).count() << " ms\n"; // Renderer.hpp:297
+    double const sec = std::chrono::duration<double>(dt).count();
+    std::cout << "Spheres: " << g_sphereNumber << "  Msamples/s: " << double(width) * height * spp / sec / 1e6 << "\n";
+    if (!io::SaveImage(out.empty() ? nullptr : out.c_str()))
+    {
+        std::cerr << "cannot write image\n";
+        return 1;
+    }
+    spt_cuda::Shutdown();
+    return 0;
+}

@@ -1,0 +1,56 @@
+"""The C++ host side on a GPU: the headless program over include/CudaPathTracer.hpp + the spt_host mirror, and
+the drop-in compiled INSIDE the reference's own translation unit (oracle/_ref/ref_integration, built in the
+container where /root/reference exists; only the binary travels)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def read_bmp(path):
+    raw = open(path, "rb").read()
+    assert raw[:2] == b"BM"
+    off = int.from_bytes(raw[10:14], "little")
+    w = int.from_bytes(raw[18:22], "little")
+    h = int.from_bytes(raw[22:26], "little")
+    stride = (w * 3 + 3) // 4 * 4
+    rows = np.frombuffer(raw, np.uint8, offset=off).reshape(h, stride)[:, : w * 3].reshape(h, w, 3)
+    return rows[::-1, :, ::-1].copy()  # top-down RGB
+
+
+@pytest.mark.parametrize("tracer,pass_cap", [("recursive", 0), ("task", 10)])
+def test_headless_program_matches_c_abi(tmp_path, tracer, pass_cap, oracle):
+    """spt_headless == RenderSegmentCuda over the host mirror's globals: its BMP equals the oracle's bytes."""
+    exe = os.path.join(ROOT, "simplepathtracer_b200", "host", "spt_headless")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-s", "-C", os.path.dirname(exe)], check=True)
+    out = str(tmp_path / "img.bmp")
+    w, h, spp, depth, seed = 96, 64, 8, 6, 3
+    r = subprocess.run([exe, "--scene", "random", "--seed", str(seed), "--width", str(w), "--height", str(h), "--spp", str(spp),
+                        "--depth", str(depth), "--tracer", tracer, "--tiles", "2", "--out", out], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "Duration:" in r.stdout and "4/4" in r.stdout
+    scene = oracle.generate_spheres(seed)
+    acc, _ = oracle.render_accum(scene, oracle.camera(), w, h, spp, depth, pass_cap=pass_cap, seed=seed)
+    assert np.array_equal(read_bmp(out), oracle.resolve(acc))
+
+
+@pytest.mark.parametrize("scene", [0, 1])
+def test_drop_in_inside_the_reference_translation_unit(tmp_path, scene):
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_integration")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/ref_integration not built (needs /root/reference at build time)")
+    prefix = str(tmp_path / "ri")
+    r = subprocess.run([exe, str(scene), "160", "90", "512", "8", prefix], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    psnr = float(r.stdout.split("psnr8bit")[1].split()[0])
+    cpu, gpu = read_bmp(prefix + "_cpu.bmp"), read_bmp(prefix + "_cuda.bmp")
+    assert cpu.shape == gpu.shape == (90, 160, 3)
+    # two independent 512-spp estimates of the same image, compared after 8-bit gamma encoding
+    assert psnr > 30.0, r.stdout
+    assert abs(float(cpu.mean()) - float(gpu.mean())) < 1.0

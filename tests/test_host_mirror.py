@@ -1,0 +1,64 @@
+"""The product's host-side mirror (include/spt_host/*.hpp through include/spt_host.h) against golden vectors
+produced by the UNMODIFIED reference: scene generators, camera basis, BMP bytes.  No GPU needed."""
+import os
+
+import numpy as np
+import pytest
+
+import simplepathtracer_b200 as spt
+from conftest import golden_path
+
+
+@pytest.fixture(scope="module", autouse=True)
+def lib():
+    spt.build_library()
+    return spt.load_library()
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_generators_match_reference(seed):
+    for name, gen in (("init", spt.init_spheres), ("random", spt.generate_spheres)):
+        g = np.load(golden_path(f"scene_{name}_seed{seed}.npz"))
+        s = gen(seed)
+        for k in ("centers", "radii", "materials", "colors", "fuzz"):
+            assert np.array_equal(getattr(s, k), g[k]), (name, seed, k)
+
+
+def test_camera_basis_matches_reference():
+    g = np.load(golden_path("camera_default.npz"))
+    c = spt.make_camera()
+    assert np.array_equal(c.view, g["view"]) and np.array_equal(c.eye, g["eye"]) and np.array_equal(c.sky, g["sky"])
+    g = np.load(golden_path("camera_offaxis.npz"))  # goes through the reference's Cross() z-lane bug
+    c = spt.make_camera(tuple(g["eye_in"]), tuple(g["look_in"]))
+    assert np.array_equal(c.view, g["view"])
+
+
+def test_bmp_bytes_match_stb(tmp_path):
+    rgb = np.load(golden_path("tiny_7x5_rgb.npy"))
+    out = str(tmp_path / "t.bmp")
+    spt.save_bmp(out, rgb)
+    assert open(out, "rb").read() == open(golden_path("tiny_7x5.bmp"), "rb").read()
+
+
+def test_synthetic_scenes():
+    mg = spt.generate_metal_glass(4, 500)
+    assert mg.n == 501 and set(np.unique(mg.materials[1:])) == {spt.REFLECTIVE, spt.REFRACTIVE}
+    assert 0.4 < (mg.materials[1:] == spt.REFLECTIVE).mean() < 0.6
+    lat = spt.generate_lattice(5, 128)
+    assert lat.n == 128 * 128 and lat.radii[0] == 1e6
+    assert (lat.radii[1:] >= 0.3).all() and (lat.radii[1:] <= 0.5).all()
+    assert np.array_equal(spt.generate_lattice(5, 128).centers, lat.centers)  # deterministic
+    assert (lat.centers[:, 3] == 0).all() and (mg.centers[:, 3] == 0).all()
+
+
+def test_exports_declared_in_header(lib):
+    import re
+
+    from simplepathtracer_b200 import binding
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = re.sub(r"/\*.*?\*/", "", open(os.path.join(root, "include", "spt_host.h")).read(), flags=re.S)
+    declared = sorted(set(re.findall(r"\b(spt_host_\w+)\s*\(", text)))
+    assert declared == sorted(binding.HOST_EXPORTS)
+    for name in declared:
+        assert hasattr(lib, name)

@@ -200,12 +200,13 @@ def run_native_arm(args, wl):
     rgb_dev = torch.zeros((H, W, 3), dtype=torch.uint8, device="cuda")
     rgb_host = torch.empty((H, W, 3), dtype=torch.uint8, pin_memory=True)
     launches = [0]
+    variant = spt.WAVEFRONT if args.variant == "wavefront" else spt.MEGAKERNEL
 
     def step_device(ev=None):
         accum.zero_()
         if ev:
             ev[0].record()
-        pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, flags=spt.FLAG_COUNTERS)
+        pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, flags=spt.FLAG_COUNTERS, variant=variant)
         if ev:
             ev[1].record()
         launches[0] += 1
@@ -272,7 +273,7 @@ def run_native_arm(args, wl):
         "bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
         "traffic": None,
         "exact_evals_per_segment": ctr["exact"] / max(ctr["segments"], 1),
-        "kernel": "trace_megakernel", "kernel_ms": kernel_ms, "kernel_share_of_step": kernel_ms / ms_step,
+        "kernel": "trace_" + args.variant, "kernel_ms": kernel_ms, "kernel_share_of_step": kernel_ms / ms_step,
         "algorithmic": f"{FLOP_PER_TEST} flop x {tests_per_launch:.4g} ray-sphere tests per launch "
                        f"({ctr['segments'] / args.steps:.4g} ray segments x {scene.n} spheres; {ctr['segments'] / max(ctr['samples'], 1):.3f} segments/sample)",
         "peak_source": f"measured in this run: dependent-FMA chains on all SMs, scalar {peak_scalar:.1f} / packed f32x2 {peak_packed:.1f} TFLOP/s "
@@ -286,10 +287,10 @@ def run_native_arm(args, wl):
     def step_e2e():
         pt.set_scene(scene)  # H2D: the scene globals (Globals.hpp:31-37)
         if world == 1:
-            pt.render(cam, W, H, spp, depth, pass_cap=PASS_CAP, seed=SEED, rgb8=rgb_host.numpy())  # D2H inside
+            pt.render(cam, W, H, spp, depth, pass_cap=PASS_CAP, seed=SEED, rgb8=rgb_host.numpy(), variant=variant)  # D2H inside
         else:
             accum.zero_()
-            pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED)
+            pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, variant=variant)
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
                 pt.resolve(accum, W, H, rgb_dev)
@@ -319,7 +320,7 @@ def run_native_arm(args, wl):
             "data": "synthetic",
             "config": {"workload": f"{args.workload}: {wl['desc']}" + (f" [spp overridden to {spp}]" if args.spp else ""),
                        "spheres": scene.n, "width": W, "height": H, "spp": spp, "depth": depth, "pass_cap": PASS_CAP,
-                       "variant": "megakernel", "sharding": f"sample ranges over {world} rank(s) + NCCL sum-reduce of float4 accumulators",
+                       "variant": args.variant, "sharding": f"sample ranges over {world} rank(s) + NCCL sum-reduce of float4 accumulators",
                        "l2": f"float4 accumulator {W * H * 16 / 1e6:.1f} MB per step vs 126 MB L2; kernel is compute-bound, scene staged in shared memory"},
             "e2e": e2e, "gpu_launches": launches_native, "roofline": roofline, "cpu_baseline": cpu, "clocks": clock_info,
             "device": info["name"], "sm_count": info["sm_count"], "counters": ctr,
@@ -339,6 +340,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (debug only; invalidates the headline)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--variant", default="megakernel", choices=["megakernel", "wavefront"])
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":

@@ -29,6 +29,14 @@
 #include <stddef.h>
 #include <stdint.h>
 
+#ifndef SPT_API
+#if defined(__GNUC__)
+#define SPT_API __attribute__((visibility("default"))) /* the library is built with -fvisibility=hidden */
+#else
+#define SPT_API
+#endif
+#endif
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -113,48 +121,48 @@ typedef struct SptDeviceInfo {
 typedef struct SptContext SptContext;
 
 /* lifetime.  `device` is a CUDA ordinal.  The context owns a stream, the device copy of the scene and scratch. */
-int spt_cuda_create(SptContext **out, int device);
-void spt_cuda_destroy(SptContext *ctx);
+SPT_API int spt_cuda_create(SptContext **out, int device);
+SPT_API void spt_cuda_destroy(SptContext *ctx);
 /* run on a caller stream (cudaStream_t passed as void*; NULL is the legacy default stream) instead of
  * the context's own non-blocking stream; use_own != 0 restores the context's stream */
-int spt_cuda_set_stream(SptContext *ctx, void *cuda_stream, int use_own);
-int spt_cuda_device_info(SptContext *ctx, SptDeviceInfo *out);
+SPT_API int spt_cuda_set_stream(SptContext *ctx, void *cuda_stream, int use_own);
+SPT_API int spt_cuda_device_info(SptContext *ctx, SptDeviceInfo *out);
 
 /* upload the scene (copied; no host pointer is retained) */
-int spt_cuda_set_scene(SptContext *ctx, const SptScene *scene);
+SPT_API int spt_cuda_set_scene(SptContext *ctx, const SptScene *scene);
 
 /* Whole hot path with HOST buffers: trace samples [sample_begin,sample_end) of every pixel of `seg`,
  * normalise, gamma-encode and write the segment's bytes into rgb8 (width*height*3, the caller's g_data;
  * pixel (x,y) lands at the reference's flipped slot, SingleThreadPathTracer.hpp:120).  accum4 (optional,
  * width*height*4 floats, row y*width+x NOT flipped) receives the linear sums and counts. Blocking. */
-int spt_cuda_render(SptContext *ctx, const SptCamera *cam, const SptParams *params, SptSegment seg,
+SPT_API int spt_cuda_render(SptContext *ctx, const SptCamera *cam, const SptParams *params, SptSegment seg,
                     uint8_t *rgb8, float *accum4);
 
 /* Device-buffer pieces (asynchronous on the context stream):
  * d_accum4: width*height float4, caller-zeroed; each call ADDS its samples. */
-int spt_cuda_accumulate(SptContext *ctx, const SptCamera *cam, const SptParams *params, SptSegment seg,
+SPT_API int spt_cuda_accumulate(SptContext *ctx, const SptCamera *cam, const SptParams *params, SptSegment seg,
                         float *d_accum4);
-int spt_cuda_resolve(SptContext *ctx, const float *d_accum4, uint32_t width, uint32_t height, SptSegment seg,
+SPT_API int spt_cuda_resolve(SptContext *ctx, const float *d_accum4, uint32_t width, uint32_t height, SptSegment seg,
                      uint8_t *d_rgb8);
-int spt_cuda_synchronize(SptContext *ctx);
+SPT_API int spt_cuda_synchronize(SptContext *ctx);
 
 /* Parity probes (host buffers, blocking).  Outputs are indexed (x-xBegin) + (y-yBegin)*(xEnd-xBegin). */
-int spt_cuda_first_hit(SptContext *ctx, const SptCamera *cam, uint32_t width, uint32_t height, SptSegment seg,
+SPT_API int spt_cuda_first_hit(SptContext *ctx, const SptCamera *cam, uint32_t width, uint32_t height, SptSegment seg,
                        uint32_t flags, uint32_t *idx, float *t, float *normal3);
 /* exact_evals (optional, count entries): spheres per ray that went through the exact sequence */
-int spt_cuda_closest_hit(SptContext *ctx, uint32_t count, const float *dir3, const float *org3, uint32_t flags,
+SPT_API int spt_cuda_closest_hit(SptContext *ctx, uint32_t count, const float *dir3, const float *org3, uint32_t flags,
                          uint32_t *idx, uint32_t *exact_evals);
 
-int spt_cuda_get_counters(SptContext *ctx, SptCounters *out); /* accumulated since the last reset */
-int spt_cuda_reset_counters(SptContext *ctx);
-int spt_cuda_get_timing(SptContext *ctx, SptTiming *out);
+SPT_API int spt_cuda_get_counters(SptContext *ctx, SptCounters *out); /* accumulated since the last reset */
+SPT_API int spt_cuda_reset_counters(SptContext *ctx);
+SPT_API int spt_cuda_get_timing(SptContext *ctx, SptTiming *out);
 
 /* FP32 CUDA-core peak of this device, measured with dependent-FMA chains on all SMs (the roofline
  * denominator BASELINE.md section 4 asks for).  scalar: fma.rn.f32; packed: fma.rn.f32x2. */
-int spt_cuda_measure_fp32_peak(SptContext *ctx, float *tflops_scalar, float *tflops_packed);
+SPT_API int spt_cuda_measure_fp32_peak(SptContext *ctx, float *tflops_scalar, float *tflops_packed);
 
-const char *spt_cuda_last_error(void);
-const char *spt_cuda_version(void);
+SPT_API const char *spt_cuda_last_error(void);
+SPT_API const char *spt_cuda_version(void);
 
 #ifdef __cplusplus
 }

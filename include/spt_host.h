@@ -16,20 +16,28 @@
 
 #include <stdint.h>
 
+#ifndef SPT_API
+#if defined(__GNUC__)
+#define SPT_API __attribute__((visibility("default"))) /* the library is built with -fvisibility=hidden */
+#else
+#define SPT_API
+#endif
+#endif
+
 #ifdef __cplusplus
 extern "C" {
 #endif
 
-uint32_t spt_host_init_spheres(uint32_t seed, uint32_t cap, float *centers4, float *radii, uint8_t *materials,
+SPT_API uint32_t spt_host_init_spheres(uint32_t seed, uint32_t cap, float *centers4, float *radii, uint8_t *materials,
                                float *colors4, float *fuzz);
-uint32_t spt_host_generate_spheres(uint32_t seed, uint32_t cap, float *centers4, float *radii, uint8_t *materials,
+SPT_API uint32_t spt_host_generate_spheres(uint32_t seed, uint32_t cap, float *centers4, float *radii, uint8_t *materials,
                                    float *colors4, float *fuzz);
-uint32_t spt_host_generate_metal_glass(uint32_t seed, uint32_t count, uint32_t cap, float *centers4, float *radii,
+SPT_API uint32_t spt_host_generate_metal_glass(uint32_t seed, uint32_t count, uint32_t cap, float *centers4, float *radii,
                                        uint8_t *materials, float *colors4, float *fuzz);
-uint32_t spt_host_generate_lattice(uint32_t seed, uint32_t side, uint32_t cap, float *centers4, float *radii,
+SPT_API uint32_t spt_host_generate_lattice(uint32_t seed, uint32_t side, uint32_t cap, float *centers4, float *radii,
                                    uint8_t *materials, float *colors4, float *fuzz);
-void spt_host_camera_basis(const float eye[3], const float look[3], const float up[3], float view16[16]);
-int spt_host_save_bmp(const char *path, uint32_t width, uint32_t height, const uint8_t *rgb8);
+SPT_API void spt_host_camera_basis(const float eye[3], const float look[3], const float up[3], float view16[16]);
+SPT_API int spt_host_save_bmp(const char *path, uint32_t width, uint32_t height, const uint8_t *rgb8);
 
 #ifdef __cplusplus
 }

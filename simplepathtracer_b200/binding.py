@@ -36,7 +36,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
     "--fmad=false",  # belt and braces: every rounded op is spelled out with __f*_rn as well
-    "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-shared",
+    "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-Xcompiler", "-fvisibility=hidden", "-shared",
 ]
 
 

@@ -2,7 +2,9 @@
 // every entry point returns an error when CUDA is unusable.
 #include "../../include/spt_cuda.h"
 #include "spt_kernels.cuh"
+#include "spt_wavefront.cuh"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -174,7 +176,7 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
 {
     if (c->n == 0 || !c->dGeom)
         return fail(SPT_ERR_NO_SCENE, "spt_cuda_set_scene has not been called");
-    if (prm->variant != SPT_VARIANT_MEGAKERNEL)
+    if (prm->variant != SPT_VARIANT_MEGAKERNEL && prm->variant != SPT_VARIANT_WAVEFRONT)
         return fail(SPT_ERR_INVALID, "unknown variant");
     c->timing.trace_ms = 0.f;
     c->timing.launches = 0;
@@ -218,7 +220,33 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
         SPT_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(SMEM)));        \
         kernel<<<grid, block, (SMEM), c->stream>>>(p);                                                               \
     } while (0)
-    if (strict)
+    if (prm->variant == SPT_VARIANT_WAVEFRONT)
+    {
+        // persistent CTAs pulling 32x8 tiles from a counter; static shared memory holds the path state
+        size_t const wfStatic = 30 * 1024;
+        size_t const wfBudget = budget > wfStatic ? budget - wfStatic : 0;
+        uint32_t const tiles = grid.x * grid.y;
+        uint32_t *tileCounter = reinterpret_cast<uint32_t *>(c->dCounters + 7);
+        SPT_CUDA_CHECK(cudaMemsetAsync(tileCounter, 0, sizeof(uint32_t), c->stream));
+#define SPT_LAUNCH_WF(STAGE, SMEM)                                                                                    \
+    do                                                                                                               \
+    {                                                                                                                \
+        auto kernel = spt::trace_wavefront<STAGE>;                                                                   \
+        SPT_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(SMEM)));        \
+        int perSm = 1;                                                                                               \
+        SPT_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, spt::kBlockThreads, (SMEM)));   \
+        uint32_t const ctas = std::min<uint32_t>(tiles, uint32_t(std::max(perSm, 1)) * uint32_t(c->prop.multiProcessorCount)); \
+        kernel<<<ctas, block, (SMEM), c->stream>>>(p, tileCounter);                                                  \
+    } while (0)
+        if (geomBytes + pairBytes <= wfBudget)
+            SPT_LAUNCH_WF(2, geomBytes + pairBytes);
+        else if (pairBytes <= wfBudget)
+            SPT_LAUNCH_WF(1, pairBytes);
+        else
+            SPT_LAUNCH_WF(0, 0);
+#undef SPT_LAUNCH_WF
+    }
+    else if (strict)
     {
         if (geomBytes <= budget)
             SPT_LAUNCH(1, true, geomBytes);

@@ -281,3 +281,31 @@ def test_converged_render_matches_reference_own_render(tracer, cam, scene_init, 
     # and no systematic offset: mean signed error well below the noise floor
     bias = float(np.mean((mean - ref) / 255.0))
     assert abs(bias) < 5e-4, bias
+
+
+# ----------------------------------------------------------------------------- wavefront variant
+@pytest.mark.parametrize("which", ["init", "random"])
+@pytest.mark.parametrize("pass_cap", [0, 10, 1])
+def test_wavefront_variant_bit_exact(tracer, oracle, cam, scene_init, scene_random, which, pass_cap):
+    """The wavefront kernel (persistent CTAs, per-material queues) computes the same per-sample radiance
+    and the same in-order per-pixel sums as the megakernel and the oracle."""
+    scene = scene_init if which == "init" else scene_random
+    w, h, spp, depth = 100, 45, 6, 8  # not a multiple of the 32x8 tile
+    tracer.set_scene(scene)
+    tracer.reset_counters()
+    rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=pass_cap, seed=21, want_accum=True, variant=spt.WAVEFRONT,
+                             flags=spt.FLAG_COUNTERS)
+    c = tracer.counters()
+    oacc, octr = oracle.render_accum(scene, cam, w, h, spp, depth, pass_cap=pass_cap, seed=21)
+    assert_accum_equal(acc, oacc)
+    assert np.array_equal(rgb, oracle.resolve(oacc))
+    assert c["segments"] == octr["segments"] and c["samples"] == octr["samples"] and c["dropped"] == octr["dropped"]
+
+
+def test_wavefront_segment(tracer, oracle, cam, scene_random):
+    w, h, spp, depth = 70, 45, 3, 5
+    tracer.set_scene(scene_random)
+    seg = (3, 29, 11, 58)
+    _, acc = tracer.render(cam, w, h, spp, depth, seed=5, seg=seg, want_accum=True, variant=spt.WAVEFRONT)
+    oacc, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, seed=5, seg=seg)
+    assert_accum_equal(acc, oacc)

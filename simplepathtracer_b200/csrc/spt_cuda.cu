@@ -105,37 +105,49 @@ float round_up_to_float(double d)
     return f;
 }
 
-// Pre-filter records (spt_filter.cuh): per sphere (cx, cy, cz, nk) with
-//   nk = -(|C|^2 - r^2) + S_i - 1e-3f,  S_i = 96 u (|C|^2 + r^2),  evaluated in binary64 and rounded UP.
-// Spheres that are too large for the filter to say anything useful, and the padding up to a whole mask
-// word, get a record that can never pass; the large ones are listed in bigIdx and always evaluated exactly.
-void build_filter(const SptScene *s, std::vector<spt::FilterPair> &pairs, std::vector<uint32_t> &big, float &amax)
+// Pre-filter blob (spt_filter.cuh): the filterable spheres in index order take consecutive SLOTS; per slot
+// (cx, cy, cz, nk) with
+//   nk = -(|C|^2 - r^2) + S_i - 1e-3f,  S_i = 96 u (|C|^2 + r^2),  evaluated in binary64 and rounded UP,
+// two slots per record, followed by the slot -> sphere index map.  Spheres too large for the filter to say
+// anything useful take no slot: they are listed in bigIdx and always evaluated exactly.  Slots are padded to a
+// multiple of kQuadSpheres with records that can never pass (index 0xFFFFFFFF).
+void build_filter(const SptScene *s, std::vector<unsigned char> &blob, uint32_t &nSlots, std::vector<uint32_t> &big, float &amax)
 {
-    uint32_t const nWords = (s->n + spt::kWordSpheres - 1) / spt::kWordSpheres;
-    pairs.assign(size_t(nWords) * (spt::kWordSpheres / 2), spt::FilterPair{});
+    std::vector<uint32_t> slots;
     big.clear();
-    double amaxD = 0.0;
-    for (uint32_t i = 0; i < nWords * spt::kWordSpheres; ++i)
+    for (uint32_t i = 0; i < s->n; ++i)
     {
-        spt::FilterPair &rec = pairs[i / 2];
-        int const h = int(i & 1);
-        rec.cx[h] = rec.cy[h] = rec.cz[h] = 0.f;
-        rec.nk[h] = -1e30f; // never a candidate
-        if (i >= s->n)
-            continue;
         double const cx = s->centers4[4 * i], cy = s->centers4[4 * i + 1], cz = s->centers4[4 * i + 2], r = s->radii[i];
         double const a2 = cx * cx + cy * cy + cz * cz;
         bool const finite = std::isfinite(a2) && std::isfinite(r);
         if (!finite || std::fabs(r) > spt::kBigRadius || std::sqrt(a2) > spt::kBigCentre)
-        {
             big.push_back(i);
+        else
+            slots.push_back(i);
+    }
+    nSlots = uint32_t((slots.size() + spt::kQuadSpheres - 1) / spt::kQuadSpheres * spt::kQuadSpheres);
+    blob.assign(spt::filter_blob_bytes(nSlots), 0);
+    spt::FilterPair *pairs = reinterpret_cast<spt::FilterPair *>(blob.data());
+    uint32_t *slotIdx = reinterpret_cast<uint32_t *>(pairs + nSlots / 2);
+    double amaxD = 0.0;
+    for (uint32_t k = 0; k < nSlots; ++k)
+    {
+        spt::FilterPair &rec = pairs[k / 2];
+        int const h = int(k & 1);
+        rec.cx[h] = rec.cy[h] = rec.cz[h] = 0.f;
+        rec.nk[h] = -1e30f; // never a candidate
+        slotIdx[k] = 0xFFFFFFFFu;
+        if (k >= slots.size())
             continue;
-        }
+        uint32_t const i = slots[k];
+        double const cx = s->centers4[4 * i], cy = s->centers4[4 * i + 1], cz = s->centers4[4 * i + 2], r = s->radii[i];
+        double const a2 = cx * cx + cy * cy + cz * cz;
         double const slack = spt::kSlackU * (a2 + r * r);
         rec.cx[h] = float(cx);
         rec.cy[h] = float(cy);
         rec.cz[h] = float(cz);
         rec.nk[h] = round_up_to_float(-(a2 - r * r) + slack - double(1e-3f));
+        slotIdx[k] = i;
         amaxD = std::max(amaxD, std::sqrt(a2));
     }
     amax = round_up_to_float(amaxD);
@@ -208,7 +220,7 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
     dim3 const grid((segW + spt::kTileW - 1) / spt::kTileW, (segH + spt::kTileH - 1) / spt::kTileH);
     dim3 const block(spt::kBlockThreads);
     size_t const geomBytes = size_t(c->n) * sizeof(float4);
-    size_t const pairBytes = size_t(c->filter.nWords) * (spt::kWordSpheres / 2) * sizeof(spt::FilterPair);
+    size_t const pairBytes = spt::filter_blob_bytes(c->filter.nSlots); // records + slot->index map
     size_t const budget = c->maxSmemOptin > 2048 ? c->maxSmemOptin - 2048 : 0;
     bool const strict = (prm->flags & SPT_FLAG_STRICT_LOOP) != 0;
 
@@ -392,10 +404,11 @@ int spt_cuda_set_scene(SptContext *c, const SptScene *s)
         geom[i] = make_float4(s->centers4[4 * i], s->centers4[4 * i + 1], s->centers4[4 * i + 2], s->radii[i]);
         shade[i] = make_float4(s->colors4[4 * i], s->colors4[4 * i + 1], s->colors4[4 * i + 2], s->fuzz[i]);
     }
-    std::vector<spt::FilterPair> pairs;
+    std::vector<unsigned char> blob;
     std::vector<uint32_t> big;
+    uint32_t nSlots = 0;
     float amax = 0.f;
-    build_filter(s, pairs, big, amax);
+    build_filter(s, blob, nSlots, big, amax);
     SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     cudaFree(c->dGeom);
     cudaFree(c->dShade);
@@ -407,13 +420,15 @@ int spt_cuda_set_scene(SptContext *c, const SptScene *s)
     c->dPairs = nullptr;
     c->dBigIdx = nullptr;
     c->n = 0;
-    SPT_CUDA_CHECK(cudaMalloc(&c->dPairs, pairs.size() * sizeof(spt::FilterPair)));
+    SPT_CUDA_CHECK(cudaMalloc(&c->dPairs, blob.size() + 16));
     SPT_CUDA_CHECK(cudaMalloc(&c->dBigIdx, (big.size() + 1) * sizeof(uint32_t)));
-    SPT_CUDA_CHECK(cudaMemcpy(c->dPairs, pairs.data(), pairs.size() * sizeof(spt::FilterPair), cudaMemcpyHostToDevice));
+    if (!blob.empty())
+        SPT_CUDA_CHECK(cudaMemcpy(c->dPairs, blob.data(), blob.size(), cudaMemcpyHostToDevice));
     if (!big.empty())
         SPT_CUDA_CHECK(cudaMemcpy(c->dBigIdx, big.data(), big.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     c->filter.pairs = c->dPairs;
-    c->filter.nWords = uint32_t(pairs.size() / (spt::kWordSpheres / 2));
+    c->filter.nSlots = nSlots;
+    c->filter.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairs + nSlots / 2);
     c->filter.bigIdx = c->dBigIdx;
     c->filter.nBig = uint32_t(big.size());
     c->filter.amax = amax;

@@ -36,6 +36,7 @@ namespace spt
 constexpr float kBigRadius = 64.f;
 constexpr float kBigCentre = 4096.f;
 constexpr uint32_t kWordSpheres = 32;                // one mask word
+constexpr uint32_t kQuadSpheres = 8;                 // filter slots are padded to a multiple of this (4 records)
 constexpr uint32_t kSuperWords = 4;                  // words per candidate-resolution round
 constexpr double kSlackU = 96.0 / 16777216.0;        // 96 u
 
@@ -46,14 +47,30 @@ struct __align__(16) FilterPair
     float cx[2], cy[2], cz[2], nk[2];
 };
 
+// The filter works on SLOTS: the filterable spheres in index order, compacted (the big spheres take no slot)
+// and padded with never-pass records to a multiple of kQuadSpheres.  slotIdx maps a slot back to its sphere
+// index (0xFFFFFFFF for padding).  `pairs` and `slotIdx` are ONE device allocation ([records | indices]) so that a
+// single TMA bulk copy stages both.
 struct FilterScene
 {
-    const FilterPair *pairs; // nWords * 16 records (padded with never-pass spheres); big spheres are never-pass here
-    uint32_t nWords;
-    const uint32_t *bigIdx;  // spheres always evaluated exactly
+    const FilterPair *pairs;  // nSlots / 2 records
+    const uint32_t *slotIdx;  // nSlots entries
+    uint32_t nSlots;          // multiple of kQuadSpheres
+    const uint32_t *bigIdx;   // spheres always evaluated exactly
     uint32_t nBig;
-    float amax;              // max |C_i| over filtered spheres
+    float amax;               // max |C_i| over filtered spheres
 };
+
+__host__ __device__ __forceinline__ uint32_t filter_blob_bytes(uint32_t nSlots)
+{
+    return nSlots / 2u * uint32_t(sizeof(FilterPair)) + nSlots * uint32_t(sizeof(uint32_t));
+}
+// point the filter at a staged copy of the blob
+__device__ __forceinline__ void rebase_filter(FilterScene &fs, const void *blob)
+{
+    fs.pairs = reinterpret_cast<const FilterPair *>(blob);
+    fs.slotIdx = reinterpret_cast<const uint32_t *>(fs.pairs + fs.nSlots / 2u);
+}
 
 // ---- packed f32x2 helpers (sm_100a: FFMA2 / FADD2) -------------------------------------------------
 __device__ __forceinline__ unsigned long long pack2(float lo, float hi)
@@ -134,6 +151,12 @@ __device__ __forceinline__ void filter_pair(const FilterPair *__restrict__ rec, 
 // Returns exactly what closest_hit_strict returns.  `exactEvals` counts exact_sphere calls (instrumentation).
 // `live` = false marks a lane that only keeps its warp company (finished pixel): it runs the convergent
 // filter loop with the rest of the warp but never enters the exact path.
+//
+// Loop shape: ONE rolled loop over mask words whose body is 16 unrolled records (32 slots), so the hot code is
+// ~230 instructions that stay in the instruction cache however many warps are in it; the last word runs
+// only the quads (4 records) that exist.  The masks of up to kSuperWords words are parked in registers and
+// the divergent candidate loop runs once per super-word, so lanes with candidates in different words of the
+// same super-word are served in the same trips.
 template <typename GeomPtr>
 __device__ __forceinline__ uint32_t closest_hit_filtered(const FilterScene &fs, GeomPtr geom, uint32_t n, V3 dir, V3 org,
                                                          uint32_t &exactEvals, bool live = true)
@@ -154,38 +177,58 @@ __device__ __forceinline__ uint32_t closest_hit_filtered(const FilterScene &fs, 
 
     FilterRay const fr = make_filter_ray(dir, org, od, fs.amax);
     const FilterPair *rec = fs.pairs;
-    for (uint32_t w0 = 0; w0 < fs.nWords; w0 += kSuperWords)
+    uint32_t const nWords = (fs.nSlots + kWordSpheres - 1u) / kWordSpheres;
+    uint32_t const tailQuads = (fs.nSlots - (nWords - 1u) * kWordSpheres) / kQuadSpheres; // 1..4 quads in the last word
+    uint32_t c0 = 0u, c1 = 0u, c2 = 0u, c3 = 0u; // candidate masks of the current super-word
+#pragma unroll 1
+    for (uint32_t w = 0; w < nWords; ++w) // everything about w is warp-uniform
     {
-        uint32_t cand[kSuperWords];
-#pragma unroll
-        for (uint32_t w = 0; w < kSuperWords; ++w)
+        uint32_t mask = 0xFFFFFFFFu; // all "fail"
+        if (w + 1u < nWords || tailQuads == kWordSpheres / kQuadSpheres)
         {
-            uint32_t mask = 0xFFFFFFFFu; // all "fail"
-            if (w0 + w < fs.nWords)      // warp-uniform
+#pragma unroll
+            for (uint32_t pp = 0; pp < kWordSpheres / 2; ++pp)
+                filter_pair(rec + pp, fr, mask);
+            rec += kWordSpheres / 2;
+        }
+        else
+        {
+#pragma unroll 1
+            for (uint32_t q = 0; q < tailQuads; ++q)
             {
 #pragma unroll
-                for (uint32_t pp = 0; pp < kWordSpheres / 2; ++pp)
+                for (uint32_t pp = 0; pp < kQuadSpheres / 2; ++pp)
                     filter_pair(rec + pp, fr, mask);
-                rec += kWordSpheres / 2;
+                rec += kQuadSpheres / 2;
             }
-            cand[w] = live ? ~mask : 0u; // bit (31 - j) set <=> sphere j of the word is a candidate
+            uint32_t const sh = kWordSpheres - kQuadSpheres * tailQuads; // 8, 16 or 24 missing slots: fail bits
+            mask = (mask << sh) | ((1u << sh) - 1u);
         }
+        uint32_t const cw = live ? ~mask : 0u; // bit (31 - j) set <=> slot j of the word is a candidate
+        uint32_t const k = w & (kSuperWords - 1u);
+        if (k == 0u) c0 = cw;
+        else if (k == 1u) c1 = cw;
+        else if (k == 2u) c2 = cw;
+        else c3 = cw;
+        if (k != kSuperWords - 1u && w + 1u != nWords)
+            continue;
         // exact sequence on this lane's candidates; lanes without any idle here (the only divergent part)
+        uint32_t const w0 = w - k;
         for (;;)
         {
-            uint32_t w, bits;
-            if (cand[0]) { w = 0; bits = cand[0]; }
-            else if (cand[1]) { w = 1; bits = cand[1]; }
-            else if (cand[2]) { w = 2; bits = cand[2]; }
-            else if (cand[3]) { w = 3; bits = cand[3]; }
+            uint32_t ww, bits;
+            if (c0) { ww = 0; bits = c0; }
+            else if (c1) { ww = 1; bits = c1; }
+            else if (c2) { ww = 2; bits = c2; }
+            else if (c3) { ww = 3; bits = c3; }
             else break;
             uint32_t const j = __clz(bits);
             uint32_t const cleared = bits & ~(0x80000000u >> j);
-            if (w == 0) cand[0] = cleared;
-            else if (w == 1) cand[1] = cleared;
-            else if (w == 2) cand[2] = cleared;
-            else cand[3] = cleared;
-            uint32_t const i = (w0 + w) * kWordSpheres + j;
+            if (ww == 0) c0 = cleared;
+            else if (ww == 1) c1 = cleared;
+            else if (ww == 2) c2 = cleared;
+            else c3 = cleared;
+            uint32_t const i = fs.slotIdx[(w0 + ww) * kWordSpheres + j];
             if (i < n) // padding records can only show up for NaN rays
             {
                 exact_sphere<false>(geom[i], i, dir, org, od, minIndex, minDistanceSq);

@@ -360,14 +360,14 @@ __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_megakerne
     extern __shared__ __align__(16) unsigned char smemRaw[];
     __shared__ __align__(8) uint64_t mbar;
     uint32_t const geomBytes = p.n * uint32_t(sizeof(float4));
-    uint32_t const pairBytes = STRICT ? 0u : p.filter.nWords * (kWordSpheres / 2) * uint32_t(sizeof(FilterPair));
+    uint32_t const pairBytes = STRICT ? 0u : filter_blob_bytes(p.filter.nSlots); // records + slot->index map
     const float4 *geom = p.geom;
     FilterScene fs = p.filter;
     if (STAGE == 2)
     {
         stage_scene_tma(smemRaw, p.geom, geomBytes, smemRaw + geomBytes, p.filter.pairs, pairBytes, &mbar);
         geom = reinterpret_cast<const float4 *>(smemRaw);
-        fs.pairs = reinterpret_cast<const FilterPair *>(smemRaw + geomBytes);
+        rebase_filter(fs, smemRaw + geomBytes);
     }
     else if (STAGE == 1)
     {
@@ -379,7 +379,7 @@ __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_megakerne
         else
         {
             stage_scene_tma(smemRaw, p.filter.pairs, pairBytes, nullptr, nullptr, 0, &mbar);
-            fs.pairs = reinterpret_cast<const FilterPair *>(smemRaw);
+            rebase_filter(fs, smemRaw);
         }
     }
 

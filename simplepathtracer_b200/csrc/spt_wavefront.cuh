@@ -64,19 +64,19 @@ __global__ void __launch_bounds__(kBlockThreads, 2) trace_wavefront(const __grid
     ShellSlots &slots = shellSlots[threadIdx.x >> 5];
 
     uint32_t const geomBytes = p.n * uint32_t(sizeof(float4));
-    uint32_t const pairBytes = p.filter.nWords * (kWordSpheres / 2) * uint32_t(sizeof(FilterPair));
+    uint32_t const pairBytes = filter_blob_bytes(p.filter.nSlots);
     const float4 *geom = p.geom;
     FilterScene fs = p.filter;
     if (STAGE == 2)
     {
         stage_scene_tma(smemRaw, p.geom, geomBytes, smemRaw + geomBytes, p.filter.pairs, pairBytes, &mbar);
         geom = reinterpret_cast<const float4 *>(smemRaw);
-        fs.pairs = reinterpret_cast<const FilterPair *>(smemRaw + geomBytes);
+        rebase_filter(fs, smemRaw + geomBytes);
     }
     else if (STAGE == 1)
     {
         stage_scene_tma(smemRaw, p.filter.pairs, pairBytes, nullptr, nullptr, 0, &mbar);
-        fs.pairs = reinterpret_cast<const FilterPair *>(smemRaw);
+        rebase_filter(fs, smemRaw);
     }
 
     uint32_t const tid = threadIdx.x;

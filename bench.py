@@ -38,6 +38,11 @@ WORKLOADS = {
                desc="single diffuse sphere + ground sphere, 1920x1080, 64 spp, depth 4"),
     "c3": dict(scene="random", width=3840, height=2160, spp=1024, depth=50, tile=240,
                desc="random-spheres scene, 3840x2160, 1024 spp, depth 50"),
+    # not bench headlines: parity / stress configurations, timed for DESIGN.md's per-config table
+    "c4": dict(scene="metalglass", width=1920, height=1080, spp=256, depth=50, tile=120,
+               desc="ground + 500 mirror/glass spheres, 1920x1080, 256 spp, depth 50 (divergence stress)"),
+    "c5": dict(scene="lattice", width=1920, height=1080, spp=128, depth=16, tile=120,
+               desc="ground + 16383 spheres on a jittered lattice, 1920x1080, 128 spp, depth 16 (staging stress)"),
 }
 PASS_CAP = 10  # RenderSegmentTask semantics (TaskBasedPathTracer.hpp:81), the tracer BASELINE.json names
 SEED = 1
@@ -55,6 +60,10 @@ def load_scene(kind):
             centers=np.array([[0, -1000.5, 0, 0], [0, 1, 0, 0]], np.float32), radii=np.array([1000.0, 0.5], np.float32),
             materials=np.array([3, 3], np.uint8), colors=np.array([[30, 144, 255, 0], [255, 100, 230, 0]], np.float32),
             fuzz=np.zeros(2, np.float32))
+    if kind == "metalglass":
+        return spt.generate_metal_glass(4, 500)
+    if kind == "lattice":
+        return spt.generate_lattice(5, 128)
     raise ValueError(kind)
 
 
@@ -113,8 +122,9 @@ def cpu_reference_rate(wl, budget_s, threads=None):
     threads = threads or os.cpu_count() or 1
     scene = load_scene(wl["scene"])
     w, h, tile = 640, 360, 40
-    if ref_available():
-        R = Reference()
+    wide = scene.n > 255  # the reference's uint8_t sphere index widened, nothing else touched
+    if ref_available(wide=wide):
+        R = Reference(wide=wide)
         R.set_camera()
         R.set_scene(scene)
         R.set_config(w, h, 2, wl["depth"])

@@ -79,8 +79,15 @@ enum {
     SPT_FLAG_STRICT_LOOP = 1u, /* closest-hit evaluates every sphere with the reference's exact op sequence
                                   (no conservative pre-filter); results are identical either way */
     SPT_FLAG_COUNTERS = 2u,    /* maintain SptCounters (cheap: per-thread registers, one atomic per warp) */
-    SPT_FLAG_CROSS_CHECK = 4u  /* spt_cuda_closest_hit only: run pre-filter AND strict loop, report 0xFFFFFFFF on disagreement */
+    SPT_FLAG_CROSS_CHECK = 4u, /* spt_cuda_closest_hit only: run pre-filter AND strict loop, report 0xFFFFFFFF on disagreement */
+    SPT_FLAG_STREAMED = 8u,    /* megakernel: stream the sphere list through a TMA chunk ring in shared memory even when it
+                                  would fit whole (the default for lists above SPT_RESIDENT_LIMIT_BYTES) */
+    SPT_FLAG_RESIDENT = 16u    /* megakernel: keep the whole list resident in shared memory whenever it fits at all, even at
+                                  the price of fewer CTAs per SM */
 };
+/* geometry + pre-filter bytes (36 B per sphere) up to which the whole list is staged once per CTA; four CTAs per SM
+ * stay resident below it.  Longer lists stream (spt_streamed.cuh). */
+#define SPT_RESIDENT_LIMIT_BYTES (48u * 1024u)
 
 typedef struct SptParams {
     uint32_t width, height;            /* g_width, g_height (Globals.hpp:14-15) */

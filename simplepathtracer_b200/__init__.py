@@ -22,6 +22,8 @@ from .binding import (  # noqa: F401
     FLAG_STRICT_LOOP,
     FLAG_COUNTERS,
     FLAG_CROSS_CHECK,
+    FLAG_STREAMED,
+    FLAG_RESIDENT,
     DIFFUSE,
     REFLECTIVE,
     REFRACTIVE,

@@ -3,6 +3,7 @@
 #include "../../include/spt_cuda.h"
 #include "spt_kernels.cuh"
 #include "spt_wavefront.cuh"
+#include "spt_streamed.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -264,6 +265,13 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             SPT_LAUNCH(1, true, geomBytes);
         else
             SPT_LAUNCH(0, true, 0);
+    }
+    else if ((prm->flags & SPT_FLAG_STREAMED) ||
+             (geomBytes + pairBytes > SPT_RESIDENT_LIMIT_BYTES && !(prm->flags & SPT_FLAG_RESIDENT) && c->filter.nSlots > 0))
+    {
+        // list too long to sit in shared memory next to four resident CTAs: TMA chunk ring (spt_streamed.cuh)
+        SPT_CUDA_CHECK(cudaFuncSetAttribute(spt::trace_streamed, cudaFuncAttributeMaxDynamicSharedMemorySize, int(spt::kStreamSmemBytes)));
+        spt::trace_streamed<<<grid, block, spt::kStreamSmemBytes, c->stream>>>(p);
     }
     else
     {

@@ -147,10 +147,10 @@ __device__ __forceinline__ void filter_pair(const FilterPair *__restrict__ rec, 
     mask = __funnelshift_l(__float_as_uint(fminf(v1, t1)), mask, 1);
 }
 
-// FindClosestIntersectionSphere (Collision.hpp:87-109): pre-filter + exact evaluation of the candidates.
-// Returns exactly what closest_hit_strict returns.  `exactEvals` counts exact_sphere calls (instrumentation).
-// `live` = false marks a lane that only keeps its warp company (finished pixel): it runs the convergent
-// filter loop with the rest of the warp but never enters the exact path.
+// The pre-filter over a SPAN of slots (a multiple of kQuadSpheres; the whole list, or one staged chunk of it),
+// followed by the exact sequence on the span's candidates.  minIndex / minDistanceSq carry the running closest
+// hit across spans.  `live` = false marks a lane that only keeps its warp company (finished pixel): it runs the
+// convergent filter loop with the rest of the warp but never enters the exact path.
 //
 // Loop shape: ONE rolled loop over mask words whose body is 16 unrolled records (32 slots), so the hot code is
 // ~230 instructions that stay in the instruction cache however many warps are in it; the last word runs
@@ -158,27 +158,12 @@ __device__ __forceinline__ void filter_pair(const FilterPair *__restrict__ rec, 
 // the divergent candidate loop runs once per super-word, so lanes with candidates in different words of the
 // same super-word are served in the same trips.
 template <typename GeomPtr>
-__device__ __forceinline__ uint32_t closest_hit_filtered(const FilterScene &fs, GeomPtr geom, uint32_t n, V3 dir, V3 org,
-                                                         uint32_t &exactEvals, bool live = true)
+__device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_t *slotIdx, uint32_t spanSlots, const FilterRay &fr,
+                                            GeomPtr geom, uint32_t n, V3 dir, V3 org, float od, uint32_t &minIndex,
+                                            float &minDistanceSq, uint32_t &exactEvals, bool live)
 {
-    uint32_t minIndex = n;
-    float minDistanceSq = FLT_MAX;
-    float const od = vdot(org, dir);
-
-    if (live)
-    {
-        for (uint32_t b = 0; b < fs.nBig; ++b)
-        {
-            uint32_t const i = fs.bigIdx[b];
-            exact_sphere<false>(geom[i], i, dir, org, od, minIndex, minDistanceSq);
-            ++exactEvals;
-        }
-    }
-
-    FilterRay const fr = make_filter_ray(dir, org, od, fs.amax);
-    const FilterPair *rec = fs.pairs;
-    uint32_t const nWords = (fs.nSlots + kWordSpheres - 1u) / kWordSpheres;
-    uint32_t const tailQuads = (fs.nSlots - (nWords - 1u) * kWordSpheres) / kQuadSpheres; // 1..4 quads in the last word
+    uint32_t const nWords = (spanSlots + kWordSpheres - 1u) / kWordSpheres;
+    uint32_t const tailQuads = (spanSlots - (nWords - 1u) * kWordSpheres) / kQuadSpheres; // 1..4 quads in the last word
     uint32_t c0 = 0u, c1 = 0u, c2 = 0u, c3 = 0u; // candidate masks of the current super-word
 #pragma unroll 1
     for (uint32_t w = 0; w < nWords; ++w) // everything about w is warp-uniform
@@ -228,7 +213,7 @@ __device__ __forceinline__ uint32_t closest_hit_filtered(const FilterScene &fs, 
             else if (ww == 1) c1 = cleared;
             else if (ww == 2) c2 = cleared;
             else c3 = cleared;
-            uint32_t const i = fs.slotIdx[(w0 + ww) * kWordSpheres + j];
+            uint32_t const i = slotIdx[(w0 + ww) * kWordSpheres + j];
             if (i < n) // padding records can only show up for NaN rays
             {
                 exact_sphere<false>(geom[i], i, dir, org, od, minIndex, minDistanceSq);
@@ -236,6 +221,37 @@ __device__ __forceinline__ uint32_t closest_hit_filtered(const FilterScene &fs, 
             }
         }
     }
+}
+
+// the spheres the filter cannot judge (the ground): always through the exact sequence
+template <typename GeomPtr>
+__device__ __forceinline__ void exact_big_spheres(const FilterScene &fs, GeomPtr geom, V3 dir, V3 org, float od, uint32_t &minIndex,
+                                                  float &minDistanceSq, uint32_t &exactEvals, bool live)
+{
+    if (live)
+    {
+        for (uint32_t b = 0; b < fs.nBig; ++b)
+        {
+            uint32_t const i = fs.bigIdx[b];
+            exact_sphere<false>(geom[i], i, dir, org, od, minIndex, minDistanceSq);
+            ++exactEvals;
+        }
+    }
+}
+
+// FindClosestIntersectionSphere (Collision.hpp:87-109) = big spheres + pre-filter + exact candidates, with the
+// whole filter blob addressable (shared memory, or global memory for the probes).  Returns exactly what
+// closest_hit_strict returns.  `exactEvals` counts exact_sphere calls (instrumentation).
+template <typename GeomPtr>
+__device__ __forceinline__ uint32_t closest_hit_filtered(const FilterScene &fs, GeomPtr geom, uint32_t n, V3 dir, V3 org,
+                                                         uint32_t &exactEvals, bool live = true)
+{
+    uint32_t minIndex = n;
+    float minDistanceSq = FLT_MAX;
+    float const od = vdot(org, dir);
+    exact_big_spheres(fs, geom, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
+    FilterRay const fr = make_filter_ray(dir, org, od, fs.amax);
+    filter_span(fs.pairs, fs.slotIdx, fs.nSlots, fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
     return minIndex;
 }
 

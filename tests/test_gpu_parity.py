@@ -309,3 +309,126 @@ def test_wavefront_segment(tracer, oracle, cam, scene_random):
     _, acc = tracer.render(cam, w, h, spp, depth, seed=5, seg=seg, want_accum=True, variant=spt.WAVEFRONT)
     oacc, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, seed=5, seg=seg)
     assert_accum_equal(acc, oacc)
+
+
+# ----------------------------------------------------------------------------- BASELINE configs 4 and 5
+@pytest.fixture(scope="module")
+def scene_metal_glass():
+    return spt.generate_metal_glass(4, 500)  # config 4: ground + 500 mirror / glass spheres (N > 255: wide index)
+
+
+@pytest.fixture(scope="module")
+def scene_lattice():
+    return spt.generate_lattice(5, 128)  # config 5: ground + 16 383 spheres (list larger than shared memory)
+
+
+@pytest.mark.parametrize("variant", [spt.MEGAKERNEL, spt.WAVEFRONT])
+@pytest.mark.parametrize("pass_cap", [0, 10])
+def test_config4_metal_glass_bit_exact(tracer, oracle, cam, scene_metal_glass, variant, pass_cap):
+    """Divergence stress: every small sphere is specular, paths are long.  Accumulators equal the oracle's."""
+    w, h, spp, depth = 96, 56, 4, 50
+    tracer.set_scene(scene_metal_glass)
+    tracer.reset_counters()
+    rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=pass_cap, seed=4, want_accum=True, variant=variant,
+                             flags=spt.FLAG_COUNTERS)
+    c = tracer.counters()
+    oacc, octr = oracle.render_accum(scene_metal_glass, cam, w, h, spp, depth, pass_cap=pass_cap, seed=4)
+    assert_accum_equal(acc, oacc)
+    assert np.array_equal(rgb, oracle.resolve(oacc))
+    assert c["segments"] == octr["segments"] and c["dropped"] == octr["dropped"]
+    assert c["segments"] > 2.0 * w * h * spp
+
+
+def test_config4_first_hit_wide_index(tracer, oracle, cam, scene_metal_glass):
+    tracer.set_scene(scene_metal_glass)
+    gi, gt, gn = tracer.first_hit(cam, 480, 270)
+    oi, ot, on, _ = oracle.first_hit(scene_metal_glass, cam, 480, 270)
+    assert np.array_equal(gi, oi) and np.array_equal(gt, ot) and np.array_equal(gn, on)
+    assert gi[gi < scene_metal_glass.n].max() > 255  # indices the reference's uint8_t could not hold
+
+
+@pytest.mark.parametrize("variant,flags", [(spt.MEGAKERNEL, 0), (spt.MEGAKERNEL, spt.FLAG_RESIDENT), (spt.MEGAKERNEL, spt.FLAG_STRICT_LOOP),
+                                           (spt.WAVEFRONT, 0)])
+def test_config5_lattice_bit_exact(tracer, oracle, cam, scene_lattice, variant, flags):
+    """16 384 spheres: neither the geometry nor the pre-filter records fit in shared memory."""
+    w, h, spp, depth = 64, 40, 2, 16
+    tracer.set_scene(scene_lattice)
+    rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=5, want_accum=True, variant=variant, flags=flags)
+    oacc, _ = oracle.render_accum(scene_lattice, cam, w, h, spp, depth, pass_cap=10, seed=5)
+    assert_accum_equal(acc, oacc)
+    assert np.array_equal(rgb, oracle.resolve(oacc))
+
+
+def test_config5_first_hit_and_prefilter(tracer, oracle, cam, scene_lattice):
+    tracer.set_scene(scene_lattice)
+    gi, gt, gn = tracer.first_hit(cam, 320, 180)
+    oi, ot, on, _ = oracle.first_hit(scene_lattice, cam, 320, 180)
+    assert np.array_equal(gi, oi) and np.array_equal(gt, ot) and np.array_equal(gn, on)
+    rng = np.random.default_rng(55)
+    d = rng.normal(size=(20000, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True).astype(np.float32)
+    o = (rng.uniform(-1, 1, size=(20000, 3)) * np.array([80, 0, 80]) + np.array([0, 1.0, 80])).astype(np.float32)
+    got = tracer.closest_hit(d, o, flags=spt.FLAG_CROSS_CHECK)
+    assert not (got == 0xFFFFFFFF).any()
+    assert np.array_equal(got, oracle.closest_hit_many(scene_lattice, d, o))
+
+
+@pytest.mark.parametrize("which", ["c4", "c5"])
+def test_full_size_properties(tracer, cam, scene_metal_glass, scene_lattice, which):
+    """At BASELINE's full image sizes the oracle is out of reach; what must still hold: the three code paths
+    (pre-filter megakernel, strict-loop megakernel, wavefront) produce identical accumulators, sample ranges
+    compose, and count + dropped == spp."""
+    import torch
+
+    scene, depth, spp = (scene_metal_glass, 50, 4) if which == "c4" else (scene_lattice, 16, 1)
+    w, h = 1920, 1080
+    tracer.set_scene(scene)
+    outs = []
+    for variant, flags in ((spt.MEGAKERNEL, 0), (spt.MEGAKERNEL, spt.FLAG_STREAMED), (spt.MEGAKERNEL, spt.FLAG_RESIDENT),
+                           (spt.MEGAKERNEL, spt.FLAG_STRICT_LOOP), (spt.WAVEFRONT, 0)):
+        if which == "c5" and flags == spt.FLAG_STRICT_LOOP:  # the strict loop over 16k spheres at full HD is minutes: use a band of it
+            continue
+        acc = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+        tracer.set_stream(torch.cuda.current_stream().cuda_stream)
+        tracer.accumulate(cam, w, h, 0, spp, depth, acc, pass_cap=10, seed=8, variant=variant, flags=flags)
+        torch.cuda.synchronize()
+        outs.append(acc)
+    for other in outs[1:]:
+        assert torch.equal(outs[0], other)
+    cnt = outs[0][..., 3]
+    assert float(cnt.max()) == spp and float(cnt.min()) >= 0
+    if spp >= 2:  # sample ranges [0, k) + [k, spp) land on the same sums when added in order on the device
+        acc = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+        tracer.accumulate(cam, w, h, 0, 1, depth, acc, pass_cap=10, seed=8)
+        tracer.accumulate(cam, w, h, 1, spp, depth, acc, pass_cap=10, seed=8)
+        torch.cuda.synchronize()
+        assert torch.equal(acc[..., 3], cnt)
+        assert torch.allclose(acc, outs[0], rtol=1e-6, atol=1e-3)
+    tracer.set_stream(None)
+
+
+# ----------------------------------------------------------------------------- streamed sphere list (TMA chunk ring)
+@pytest.mark.parametrize("which", ["init", "random", "metal_glass", "lattice40"])
+@pytest.mark.parametrize("pass_cap", [0, 10])
+def test_streamed_megakernel_bit_exact(tracer, oracle, cam, scene_init, scene_random, scene_metal_glass, which, pass_cap):
+    """SPT_FLAG_STREAMED forces the chunk-ring kernel on lists of every length: a fraction of one chunk (10, 149),
+    one almost full chunk (501) and several chunks with a ragged tail (1600 spheres = 3 full chunks + 63 slots)."""
+    scene = {"init": scene_init, "random": scene_random, "metal_glass": scene_metal_glass}.get(which) or spt.generate_lattice(7, 40)
+    w, h, spp, depth = 100, 45, 5, 12  # ragged tiles: CTAs with dead warps and dead lanes must keep the ring moving
+    tracer.set_scene(scene)
+    tracer.reset_counters()
+    rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=pass_cap, seed=33, want_accum=True, flags=spt.FLAG_STREAMED | spt.FLAG_COUNTERS)
+    c = tracer.counters()
+    oacc, octr = oracle.render_accum(scene, cam, w, h, spp, depth, pass_cap=pass_cap, seed=33)
+    assert_accum_equal(acc, oacc)
+    assert np.array_equal(rgb, oracle.resolve(oacc))
+    assert c["segments"] == octr["segments"] and c["samples"] == octr["samples"] and c["dropped"] == octr["dropped"]
+
+
+def test_streamed_equals_resident_on_segments(tracer, cam, scene_random):
+    w, h, spp, depth = 200, 120, 8, 8
+    tracer.set_scene(scene_random)
+    seg = (5, 101, 17, 190)
+    _, a = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=2, seg=seg, want_accum=True)
+    _, b = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=2, seg=seg, want_accum=True, flags=spt.FLAG_STREAMED)
+    assert_accum_equal(a, b)

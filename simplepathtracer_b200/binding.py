@@ -52,7 +52,8 @@ def build_library(verbose: bool = False, force: bool = False) -> str:
         return out
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     units = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cpp"))]
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-I", os.path.join(ROOT, "include")] + units + ["-o", out]
+    extra = os.environ.get("SPT_NVCC_EXTRA", "").split()  # experiments only, e.g. -DSPT_FILTER_TC=1
+    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-I", os.path.join(ROOT, "include")] + units + ["-o", out]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise SptError("nvcc failed:\n" + res.stdout + res.stderr)

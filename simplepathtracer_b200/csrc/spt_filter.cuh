@@ -33,6 +33,9 @@
 namespace spt
 {
 
+#ifndef SPT_FILTER_TC
+#define SPT_FILTER_TC 0 // 1: the pre-filter also tests the sign of tC (one more FMNMX per sphere, fewer candidates)
+#endif
 constexpr float kBigRadius = 64.f;
 constexpr float kBigCentre = 4096.f;
 constexpr uint32_t kWordSpheres = 32;                // one mask word
@@ -143,8 +146,14 @@ __device__ __forceinline__ void filter_pair(const FilterPair *__restrict__ rec, 
     float t0, t1, v0, v1;
     unpack2(tc, t0, t1);
     unpack2(v, v0, v1);
+#if SPT_FILTER_TC
     mask = __funnelshift_l(__float_as_uint(fminf(v0, t0)), mask, 1);
     mask = __funnelshift_l(__float_as_uint(fminf(v1, t1)), mask, 1);
+#else
+    // discriminant only: the tC > 1e-3 half of the test is left to the exact sequence's early-out
+    mask = __funnelshift_l(__float_as_uint(v0), mask, 1);
+    mask = __funnelshift_l(__float_as_uint(v1), mask, 1);
+#endif
 }
 
 // The pre-filter over a SPAN of slots (a multiple of kQuadSpheres; the whole list, or one staged chunk of it),

@@ -196,8 +196,10 @@ def run_native_arm(args, wl):
     scene = load_scene(wl["scene"])
     cam = spt.Camera()  # the reference camera (Globals.hpp:22-24 through Renderer.hpp:321)
     W, H, spp, depth = wl["width"], wl["height"], args.spp or wl["spp"], wl["depth"]
+    from simplepathtracer_b200 import sharding
+
     # sample-range sharding: rank r renders samples [s0, s1) of every pixel
-    s0, s1 = rank * spp // world, (rank + 1) * spp // world
+    s0, s1 = sharding.sample_range(rank, world, spp)
 
     pt = spt.PathTracer(local)
     # one explicit stream for torch fills, our kernels and the timing events
@@ -220,8 +222,7 @@ def run_native_arm(args, wl):
         if ev:
             ev[1].record()
         launches[0] += 1
-        if world > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        sharding.reduce_accumulators(accum, dst=0)  # NCCL sum-reduce over NVLink; a no-op for one rank
         if rank == 0:
             pt.resolve(accum, W, H, rgb_dev)
             launches[0] += 1
@@ -279,9 +280,17 @@ def run_native_arm(args, wl):
     peak = max(peak_scalar, peak_packed)
     tests_per_launch = ctr["tests"] / args.steps
     achieved = FLOP_PER_TEST * tests_per_launch / (kernel_ms * 1e-3) / 1e12
+    traffic = None
+    try:  # measured once per round under ncu --set full and committed; never measured inside a timed run
+        t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(f"{args.workload}:{args.variant}")
+        if t:
+            traffic = {"dram_bytes_per_launch": t["dram_bytes_read"] + t["dram_bytes_write"], "algorithmic_bytes_per_launch": W * H * 32,
+                       "source": t["capture"]}
+    except (OSError, ValueError):
+        pass
     roofline = {
         "bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
-        "traffic": None,
+        "traffic": traffic,
         "exact_evals_per_segment": ctr["exact"] / max(ctr["segments"], 1),
         "kernel": "trace_" + args.variant, "kernel_ms": kernel_ms, "kernel_share_of_step": kernel_ms / ms_step,
         "algorithmic": f"{FLOP_PER_TEST} flop x {tests_per_launch:.4g} ray-sphere tests per launch "

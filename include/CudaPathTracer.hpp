@@ -122,6 +122,57 @@ inline void Render(RenderSegmentData segment, uint32_t passCap, uint32_t variant
     SptSegment const seg{segment.yBegin, segment.yEnd, segment.xBegin, segment.xEnd};
     Check(spt_cuda_render(ctx, &cam, &p, seg, g_data, nullptr), "spt_cuda_render");
 }
+inline void FillCameraAndParams(SptCamera &cam, SptParams &p, uint32_t passCap, uint32_t variant)
+{
+    for (int k = 0; k < 16; ++k)
+        cam.view[k] = viewMatrix.array[k];
+    cam.view[3] = cam.view[7] = cam.view[11] = cam.view[12] = cam.view[13] = cam.view[14] = cam.view[15] = 0.f;
+    for (int k = 0; k < 3; ++k)
+    {
+        cam.eye[k] = eyePos.xyzw[k];
+        cam.sky[k] = initColor.xyzw[k];
+    }
+    p.width = g_width;
+    p.height = g_height;
+    p.depth = g_bounces;
+    p.pass_cap = passCap;
+    p.sample_begin = 0;
+    p.sample_end = g_samples;
+    p.seed = GetState().seed;
+    p.variant = variant;
+    p.flags = GetState().flags;
+}
+
+// Progressive rendering of the whole image on the context-owned accumulator: the reference's live preview
+// (UpdateTexture re-reads g_data every frame while RenderJob threads fill it, Renderer.hpp:157-164,282-290,355) and its
+// progress lines (Renderer.hpp:285), as passes over the SAMPLES instead of tiles.  After pass k, g_data holds the image
+// of the first samplesDone samples and onPass(k, passes, samplesDone) is called.  Passes leave the bits of one
+// g_samples render.  firstSample > 0 resumes (accum4 = the checkpointed sums, width*height*4 floats).
+template <typename OnPass>
+inline void RenderImageProgressiveCuda(uint32_t passes, uint32_t passCap, uint32_t variant, OnPass onPass, uint32_t firstSample = 0,
+                                       float const *resumeAccum4 = nullptr, float *accumOut4 = nullptr)
+{
+    SptContext *ctx = Acquire();
+    SptCamera cam{};
+    SptParams p{};
+    FillCameraAndParams(cam, p, passCap, variant);
+    SptSegment const all{0, g_height, 0, g_width};
+    Check(spt_cuda_progressive_begin(ctx, g_width, g_height), "spt_cuda_progressive_begin");
+    if (resumeAccum4)
+        Check(spt_cuda_progressive_load(ctx, resumeAccum4), "spt_cuda_progressive_load");
+    if (passes == 0)
+        passes = 1;
+    uint32_t const todo = g_samples > firstSample ? g_samples - firstSample : 0;
+    for (uint32_t k = 0; k < passes; ++k)
+    {
+        p.sample_begin = firstSample + uint32_t(uint64_t(todo) * k / passes);
+        p.sample_end = firstSample + uint32_t(uint64_t(todo) * (k + 1) / passes);
+        Check(spt_cuda_progressive_add(ctx, &cam, &p, all), "spt_cuda_progressive_add");
+        bool const last = k + 1 == passes;
+        Check(spt_cuda_progressive_image(ctx, all, g_data, last ? accumOut4 : nullptr), "spt_cuda_progressive_image");
+        onPass(k + 1, passes, p.sample_end);
+    }
+}
 } // namespace spt_cuda
 
 // RenderSegment on the GPU: recursive-tracer semantics (specular recursion unbounded), megakernel.

@@ -13,6 +13,8 @@
  *                          in a DEVICE float4 accumulator so that sample ranges / GPUs can be combined
  *   spt_cuda_resolve       the normalise + io::WritePixel tail of both tracers
  *                          (SingleThreadPathTracer.hpp:133-134, TaskBasedPathTracer.hpp:196-205)
+ *   spt_cuda_progressive_* the per-tile / per-pass scheduling around them, include/Renderer.hpp:257-302, on a
+ *                          context-owned accumulator (progressive refinement, checkpoint / resume)
  *   spt_cuda_first_hit     cd::FindClosestIntersectionSphere + contact helpers on jitter-free pinhole rays
  *   spt_cuda_closest_hit   cd::FindClosestIntersectionSphere  include/Collision.hpp:87-109
  *   spt_cuda_set_scene     the SoA scene globals  include/Globals.hpp:31-37
@@ -152,6 +154,20 @@ SPT_API int spt_cuda_accumulate(SptContext *ctx, const SptCamera *cam, const Spt
 SPT_API int spt_cuda_resolve(SptContext *ctx, const float *d_accum4, uint32_t width, uint32_t height, SptSegment seg,
                      uint8_t *d_rgb8);
 SPT_API int spt_cuda_synchronize(SptContext *ctx);
+
+/* Progressive rendering on an accumulator OWNED BY THE CONTEXT (host programs that have no CUDA runtime of their own):
+ * the per-tile / per-pass call pattern of RenderImageParallelMain (include/Renderer.hpp:257-302) and the live
+ * preview that re-reads g_data every frame (Renderer.hpp:157-164,355).  The per-pixel running sums continue across
+ * calls, so P passes of spp/P samples leave exactly the bits of one render of spp samples.
+ *   begin  : (re)allocate and zero a width*height float4 accumulator
+ *   add    : trace samples [sample_begin,sample_end) of `seg` into it (asynchronous)
+ *   image  : normalise + gamma + pack the segment and copy it into rgb8 (the caller's g_data; may be NULL) and the
+ *            linear sums/counts into accum4 (width*height*4 floats, may be NULL).  Blocking.
+ *   load   : overwrite the accumulator from host memory (resume from a checkpoint written from `image`) */
+SPT_API int spt_cuda_progressive_begin(SptContext *ctx, uint32_t width, uint32_t height);
+SPT_API int spt_cuda_progressive_add(SptContext *ctx, const SptCamera *cam, const SptParams *params, SptSegment seg);
+SPT_API int spt_cuda_progressive_image(SptContext *ctx, SptSegment seg, uint8_t *rgb8, float *accum4);
+SPT_API int spt_cuda_progressive_load(SptContext *ctx, const float *accum4);
 
 /* Parity probes (host buffers, blocking).  Outputs are indexed (x-xBegin) + (y-yBegin)*(xEnd-xBegin). */
 SPT_API int spt_cuda_first_hit(SptContext *ctx, const SptCamera *cam, uint32_t width, uint32_t height, SptSegment seg,

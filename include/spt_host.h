@@ -7,6 +7,8 @@
  *   spt_host_generate_metal_glass / _lattice       BASELINE.json configs 4 / 5 (no reference counterpart)
  *   spt_host_camera_basis      Transpose(CreateCameraBasisMatrix(...))  include/Math.hpp:198-231, Renderer.hpp:321
  *   spt_host_save_bmp          stbi_write_bmp as called by io::SaveImage  include/IOHelpers.hpp:24-27
+ *   spt_host_save_pfm          linear-float companion of the BMP (no reference counterpart)
+ *   spt_host_save_accum / spt_host_load_accum   accumulator checkpoint for resume (no reference counterpart)
  *
  * Generators return the sphere count; arrays are filled when cap >= count (call with cap = 0 to size).
  * Layout = the reference's SoA globals (include/Globals.hpp:31-37).
@@ -38,6 +40,12 @@ SPT_API uint32_t spt_host_generate_lattice(uint32_t seed, uint32_t side, uint32_
                                    uint8_t *materials, float *colors4, float *fuzz);
 SPT_API void spt_host_camera_basis(const float eye[3], const float look[3], const float up[3], float view16[16]);
 SPT_API int spt_host_save_bmp(const char *path, uint32_t width, uint32_t height, const uint8_t *rgb8);
+SPT_API int spt_host_save_pfm(const char *path, uint32_t width, uint32_t height, const float *accum4);
+SPT_API int spt_host_save_accum(const char *path, uint32_t width, uint32_t height, uint32_t samples_done, uint32_t depth, uint64_t seed,
+                        const float *accum4);
+/* returns 1 and fills samples_done / depth / seed / accum4 (width*height*4) when the file matches the image size */
+SPT_API int spt_host_load_accum(const char *path, uint32_t width, uint32_t height, uint32_t *samples_done, uint32_t *depth,
+                        uint64_t *seed, float *accum4);
 
 #ifdef __cplusplus
 }

@@ -11,6 +11,7 @@
 
 #include <cstdio>
 #include <string>
+#include <vector>
 
 namespace io
 {
@@ -49,6 +50,71 @@ inline bool WriteBmp(char const *path, uint32_t width, uint32_t height, uint8_t 
             std::fputc(0, f);
     }
     return std::fclose(f) == 0;
+}
+
+// Linear-float output next to the 8-bit BMP: Portable Float Map, "PF\n<w> <h>\n-1.0\n" followed by
+// little-endian float RGB rows, BOTTOM row first -- which is the tracers' own y direction (y = 0 is the bottom
+// row, SingleThreadPathTracer.hpp:120), so accumulator rows are written in order.  Values are the mean radiance
+// sum / count on the reference's 0..255 scale divided by 255 (linear, no gamma).  accum4 = width*height (sum r,
+// sum g, sum b, count) as spt_cuda_render / spt_cuda_progressive_image return it.
+inline bool WritePfm(char const *path, uint32_t width, uint32_t height, float const *accum4)
+{
+    FILE *f = std::fopen(path, "wb");
+    if (!f)
+        return false;
+    std::fprintf(f, "PF\n%u %u\n-1.0\n", width, height);
+    std::vector<float> row(size_t(width) * 3u);
+    for (uint32_t y = 0; y < height; ++y)
+    {
+        for (uint32_t x = 0; x < width; ++x)
+        {
+            float const *a = accum4 + (size_t(y) * width + x) * 4u;
+            float const inv = 1.f / a[3];
+            for (int k = 0; k < 3; ++k)
+                row[size_t(x) * 3u + k] = a[k] * inv / 255.f;
+        }
+        std::fwrite(row.data(), sizeof(float), row.size(), f);
+    }
+    return std::fclose(f) == 0;
+}
+
+// Accumulator checkpoint (resume a render later, or on another GPU): 32-byte header
+//   "SPTACC1\0", u32 width, u32 height, u32 samplesDone, u32 depth, u64 seed
+// then width*height float4 (sum r, sum g, sum b, count), little-endian, row y*width + x.
+struct AccumHeader
+{
+    char magic[8];
+    uint32_t width, height, samplesDone, depth;
+    uint64_t seed;
+};
+static_assert(sizeof(AccumHeader) == 32, "checkpoint header layout");
+
+inline bool SaveAccum(char const *path, uint32_t width, uint32_t height, uint32_t samplesDone, uint32_t depth, uint64_t seed,
+                      float const *accum4)
+{
+    FILE *f = std::fopen(path, "wb");
+    if (!f)
+        return false;
+    AccumHeader h{{'S', 'P', 'T', 'A', 'C', 'C', '1', 0}, width, height, samplesDone, depth, seed};
+    bool ok = std::fwrite(&h, sizeof(h), 1, f) == 1;
+    ok = ok && std::fwrite(accum4, sizeof(float) * 4u, size_t(width) * height, f) == size_t(width) * height;
+    return (std::fclose(f) == 0) && ok;
+}
+
+// returns false when the file is missing, malformed or of another image size
+inline bool LoadAccum(char const *path, uint32_t width, uint32_t height, AccumHeader &h, std::vector<float> &accum4)
+{
+    FILE *f = std::fopen(path, "rb");
+    if (!f)
+        return false;
+    bool ok = std::fread(&h, sizeof(h), 1, f) == 1 && std::string(h.magic, 7) == "SPTACC1" && h.width == width && h.height == height;
+    if (ok)
+    {
+        accum4.resize(size_t(width) * height * 4u);
+        ok = std::fread(accum4.data(), sizeof(float) * 4u, size_t(width) * height, f) == size_t(width) * height;
+    }
+    std::fclose(f);
+    return ok;
 }
 
 // io::SaveImage (include/IOHelpers.hpp:24-27): same file name rule

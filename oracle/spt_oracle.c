@@ -535,9 +535,12 @@ void spo_render_accum(const spo_scene *sc, const spo_camera *cam, const spo_para
 {
     for (uint32_t y = yBegin; y < yEnd; ++y) {
         for (uint32_t x = xBegin; x < xEnd; ++x) {
-            /* pixelColor += sample, in sample order (SingleThreadPathTracer.hpp:121-131) */
-            v4 sum = v3(0.f, 0.f, 0.f);
-            float count = 0.f;
+            /* pixelColor += sample, in sample order (SingleThreadPathTracer.hpp:121-131).  The running sum
+             * CONTINUES from what the accumulator holds, so consecutive sample ranges rendered one after another
+             * give the very bits of a single render of the whole range (progressive refinement, resume). */
+            float *a = accum4 + 4 * ((size_t)y * p->width + x);
+            v4 sum = v3(a[0], a[1], a[2]);
+            float count = a[3];
             for (uint32_t s = p->sample_begin; s < p->sample_end; ++s) {
                 float rgb[4];
                 if (spo_sample_radiance(sc, cam, p, x, y, s, rgb, ctr)) {
@@ -545,11 +548,10 @@ void spo_render_accum(const spo_scene *sc, const spo_camera *cam, const spo_para
                     count += 1.f;
                 }
             }
-            float *a = accum4 + 4 * ((size_t)y * p->width + x);
-            a[0] += sum.v[0];
-            a[1] += sum.v[1];
-            a[2] += sum.v[2];
-            a[3] += count;
+            a[0] = sum.v[0];
+            a[1] = sum.v[1];
+            a[2] = sum.v[2];
+            a[3] = count;
         }
     }
 }

@@ -34,6 +34,9 @@ from .binding import (  # noqa: F401
     generate_lattice,
     make_camera,
     save_bmp,
+    save_pfm,
+    save_accum,
+    load_accum,
 )
 
 __version__ = "0.1.0"

@@ -166,12 +166,13 @@ class DeviceInfo(C.Structure):
 EXPORTS = [
     "spt_cuda_create", "spt_cuda_destroy", "spt_cuda_set_stream", "spt_cuda_device_info", "spt_cuda_set_scene",
     "spt_cuda_render", "spt_cuda_accumulate", "spt_cuda_resolve", "spt_cuda_synchronize", "spt_cuda_first_hit",
+    "spt_cuda_progressive_begin", "spt_cuda_progressive_add", "spt_cuda_progressive_image", "spt_cuda_progressive_load",
     "spt_cuda_closest_hit", "spt_cuda_get_counters", "spt_cuda_reset_counters", "spt_cuda_get_timing",
     "spt_cuda_measure_fp32_peak", "spt_cuda_last_error", "spt_cuda_version",
 ]
 HOST_EXPORTS = [
     "spt_host_init_spheres", "spt_host_generate_spheres", "spt_host_generate_metal_glass", "spt_host_generate_lattice",
-    "spt_host_camera_basis", "spt_host_save_bmp",
+    "spt_host_camera_basis", "spt_host_save_bmp", "spt_host_save_pfm", "spt_host_save_accum", "spt_host_load_accum",
 ]
 
 _LIB = None
@@ -199,6 +200,10 @@ def load_library():
     L.spt_cuda_accumulate.argtypes = [C.c_void_p, C.POINTER(_CCamera), C.POINTER(_CParams), Segment, C.c_void_p]
     L.spt_cuda_resolve.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, Segment, C.c_void_p]
     L.spt_cuda_synchronize.argtypes = [C.c_void_p]
+    L.spt_cuda_progressive_begin.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
+    L.spt_cuda_progressive_add.argtypes = [C.c_void_p, C.POINTER(_CCamera), C.POINTER(_CParams), Segment]
+    L.spt_cuda_progressive_image.argtypes = [C.c_void_p, Segment, C.c_void_p, C.c_void_p]
+    L.spt_cuda_progressive_load.argtypes = [C.c_void_p, C.c_void_p]
     L.spt_cuda_first_hit.argtypes = [C.c_void_p, C.POINTER(_CCamera), C.c_uint32, C.c_uint32, Segment, C.c_uint32, C.c_void_p,
                                      C.c_void_p, C.c_void_p]
     L.spt_cuda_closest_hit.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
@@ -216,6 +221,9 @@ def load_library():
     L.spt_host_camera_basis.argtypes = [f32p, f32p, f32p, f32p]
     L.spt_host_camera_basis.restype = None
     L.spt_host_save_bmp.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, u8p]
+    L.spt_host_save_pfm.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, f32p]
+    L.spt_host_save_accum.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, f32p]
+    L.spt_host_load_accum.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, u32p, u32p, C.POINTER(C.c_uint64), f32p]
     _LIB = L
     return L
 
@@ -320,6 +328,32 @@ class PathTracer:
         self._check(self.L.spt_cuda_resolve(self.h, C.c_void_p(_devptr(d_accum)), width, height, _seg(seg, width, height),
                                             C.c_void_p(_devptr(d_rgb8))))
 
+    # progressive rendering on the context-owned accumulator (spt_cuda_progressive_*)
+    def progressive_begin(self, width, height):
+        self._check(self.L.spt_cuda_progressive_begin(self.h, width, height))
+        self._prog = (width, height)
+
+    def progressive_add(self, cam, sample_begin, sample_end, depth, pass_cap=0, seed=1, seg=None, variant=MEGAKERNEL, flags=0):
+        width, height = self._prog
+        cm = _ccam(Camera.of(cam))
+        p = self._params(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags)
+        self._check(self.L.spt_cuda_progressive_add(self.h, C.byref(cm), C.byref(p), _seg(seg, width, height)))
+
+    def progressive_image(self, seg=None, want_accum=False, rgb8: Optional[np.ndarray] = None):
+        width, height = self._prog
+        if rgb8 is None:
+            rgb8 = np.zeros((height, width, 3), np.uint8)
+        accum = np.zeros((height, width, 4), np.float32) if want_accum else None
+        self._check(self.L.spt_cuda_progressive_image(self.h, _seg(seg, width, height), rgb8.ctypes.data,
+                                                      accum.ctypes.data if want_accum else None))
+        return rgb8, accum
+
+    def progressive_load(self, accum: np.ndarray):
+        width, height = self._prog
+        accum = np.ascontiguousarray(accum, np.float32)
+        assert accum.shape == (height, width, 4)
+        self._check(self.L.spt_cuda_progressive_load(self.h, accum.ctypes.data))
+
     def synchronize(self):
         self._check(self.L.spt_cuda_synchronize(self.h))
 
@@ -406,3 +440,27 @@ def save_bmp(path: str, rgb8: np.ndarray) -> None:
     h, w = rgb8.shape[:2]
     if not load_library().spt_host_save_bmp(path.encode(), w, h, rgb8.ctypes.data_as(u8p)):
         raise SptError("cannot write " + path)
+
+
+def save_pfm(path: str, accum: np.ndarray) -> None:
+    """Linear float image (mean radiance / 255) as a Portable Float Map; accum = (H, W, 4) sums and counts."""
+    accum = np.ascontiguousarray(accum, np.float32)
+    h, w = accum.shape[:2]
+    if not load_library().spt_host_save_pfm(path.encode(), w, h, accum.ctypes.data_as(f32p)):
+        raise SptError("cannot write " + path)
+
+
+def save_accum(path: str, accum: np.ndarray, samples_done: int, depth: int, seed: int) -> None:
+    accum = np.ascontiguousarray(accum, np.float32)
+    h, w = accum.shape[:2]
+    if not load_library().spt_host_save_accum(path.encode(), w, h, samples_done, depth, seed, accum.ctypes.data_as(f32p)):
+        raise SptError("cannot write " + path)
+
+
+def load_accum(path: str, width: int, height: int):
+    """Returns (accum (H, W, 4), samples_done, depth, seed) or None when the file does not match."""
+    accum = np.zeros((height, width, 4), np.float32)
+    sd, dp, seed = C.c_uint32(), C.c_uint32(), C.c_uint64()
+    if not load_library().spt_host_load_accum(path.encode(), width, height, C.byref(sd), C.byref(dp), C.byref(seed), accum.ctypes.data_as(f32p)):
+        return None
+    return accum, int(sd.value), int(dp.value), int(seed.value)

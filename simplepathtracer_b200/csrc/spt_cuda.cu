@@ -61,6 +61,10 @@ struct SptContext
     float4 *dAccum = nullptr;
     uint8_t *dRgb = nullptr;
     size_t accumPixels = 0;
+    // context-owned accumulator of the progressive entry points
+    float4 *dProgAccum = nullptr;
+    uint8_t *dProgRgb = nullptr;
+    uint32_t progW = 0, progH = 0;
     void *dProbe = nullptr;
     size_t probeBytes = 0;
     size_t maxSmemOptin = 0;
@@ -361,6 +365,8 @@ void spt_cuda_destroy(SptContext *c)
     cudaFree(c->dAccum);
     cudaFree(c->dRgb);
     cudaFree(c->dProbe);
+    cudaFree(c->dProgAccum);
+    cudaFree(c->dProgRgb);
     for (auto &e : c->ev)
         if (e)
             cudaEventDestroy(e);
@@ -525,6 +531,95 @@ int spt_cuda_render(SptContext *c, const SptCamera *cam, const SptParams *prm, S
         SPT_CUDA_CHECK(cudaMemcpy2DAsync(accum4 + (size_t(seg.yBegin) * W + seg.xBegin) * 4, size_t(W) * sizeof(float4),
                                          c->dAccum + size_t(seg.yBegin) * W + seg.xBegin, size_t(W) * sizeof(float4),
                                          size_t(segW) * sizeof(float4), segH, cudaMemcpyDeviceToHost, c->stream));
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    return SPT_OK;
+}
+
+int spt_cuda_progressive_begin(SptContext *c, uint32_t width, uint32_t height)
+{
+    if (!c)
+        return fail(SPT_ERR_INVALID, "context is null");
+    int const rc = check_segment(width, height, SptSegment{0, height, 0, width});
+    if (rc)
+        return rc;
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    if (width != c->progW || height != c->progH || !c->dProgAccum)
+    {
+        cudaFree(c->dProgAccum);
+        cudaFree(c->dProgRgb);
+        c->dProgAccum = nullptr;
+        c->dProgRgb = nullptr;
+        c->progW = c->progH = 0;
+        SPT_CUDA_CHECK(cudaMalloc(&c->dProgAccum, size_t(width) * height * sizeof(float4)));
+        SPT_CUDA_CHECK(cudaMalloc(&c->dProgRgb, size_t(width) * height * 3));
+        c->progW = width;
+        c->progH = height;
+    }
+    SPT_CUDA_CHECK(cudaMemsetAsync(c->dProgAccum, 0, size_t(width) * height * sizeof(float4), c->stream));
+    return SPT_OK;
+}
+
+int spt_cuda_progressive_add(SptContext *c, const SptCamera *cam, const SptParams *prm, SptSegment seg)
+{
+    if (!c || !prm)
+        return fail(SPT_ERR_INVALID, "null argument");
+    int rc = check_camera(cam);
+    if (rc)
+        return rc;
+    rc = check_segment(prm->width, prm->height, seg);
+    if (rc)
+        return rc;
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    if (!c->dProgAccum || prm->width != c->progW || prm->height != c->progH)
+        return fail(SPT_ERR_INVALID, "spt_cuda_progressive_begin has not been called with this image size");
+    return launch_trace(c, cam, prm, seg, c->dProgAccum);
+}
+
+int spt_cuda_progressive_image(SptContext *c, SptSegment seg, uint8_t *rgb8, float *accum4)
+{
+    if (!c)
+        return fail(SPT_ERR_INVALID, "context is null");
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    if (!c->dProgAccum)
+        return fail(SPT_ERR_INVALID, "spt_cuda_progressive_begin has not been called");
+    uint32_t const W = c->progW, H = c->progH;
+    int rc = check_segment(W, H, seg);
+    if (rc)
+        return rc;
+    uint32_t const segW = seg.xEnd - seg.xBegin, segH = seg.yEnd - seg.yBegin;
+    if (segW == 0 || segH == 0)
+        return SPT_OK;
+    if (rgb8)
+    {
+        rc = launch_resolve(c, c->dProgAccum, W, H, seg, c->dProgRgb);
+        if (rc)
+            return rc;
+        uint32_t const rowTop = H - seg.yEnd; // pixel (x,y) lives in byte row H-1-y
+        SPT_CUDA_CHECK(cudaMemcpy2DAsync(rgb8 + (size_t(rowTop) * W + seg.xBegin) * 3, size_t(W) * 3,
+                                         c->dProgRgb + (size_t(rowTop) * W + seg.xBegin) * 3, size_t(W) * 3, size_t(segW) * 3, segH,
+                                         cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (accum4)
+        SPT_CUDA_CHECK(cudaMemcpy2DAsync(accum4 + (size_t(seg.yBegin) * W + seg.xBegin) * 4, size_t(W) * sizeof(float4),
+                                         c->dProgAccum + size_t(seg.yBegin) * W + seg.xBegin, size_t(W) * sizeof(float4),
+                                         size_t(segW) * sizeof(float4), segH, cudaMemcpyDeviceToHost, c->stream));
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    return SPT_OK;
+}
+
+int spt_cuda_progressive_load(SptContext *c, const float *accum4)
+{
+    if (!c || !accum4)
+        return fail(SPT_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    if (!c->dProgAccum)
+        return fail(SPT_ERR_INVALID, "spt_cuda_progressive_begin has not been called");
+    SPT_CUDA_CHECK(cudaMemcpyAsync(c->dProgAccum, accum4, size_t(c->progW) * c->progH * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     return SPT_OK;
 }

@@ -66,4 +66,26 @@ int spt_host_save_bmp(const char *path, uint32_t width, uint32_t height, const u
 {
     return io::WriteBmp(path, width, height, rgb8) ? 1 : 0;
 }
+int spt_host_save_pfm(const char *path, uint32_t width, uint32_t height, const float *accum4)
+{
+    return io::WritePfm(path, width, height, accum4) ? 1 : 0;
+}
+int spt_host_save_accum(const char *path, uint32_t width, uint32_t height, uint32_t samples_done, uint32_t depth, uint64_t seed,
+                        const float *accum4)
+{
+    return io::SaveAccum(path, width, height, samples_done, depth, seed, accum4) ? 1 : 0;
+}
+int spt_host_load_accum(const char *path, uint32_t width, uint32_t height, uint32_t *samples_done, uint32_t *depth, uint64_t *seed,
+                        float *accum4)
+{
+    io::AccumHeader h{};
+    std::vector<float> data;
+    if (!io::LoadAccum(path, width, height, h, data))
+        return 0;
+    if (samples_done) *samples_done = h.samplesDone;
+    if (depth) *depth = h.depth;
+    if (seed) *seed = h.seed;
+    if (accum4) std::memcpy(accum4, data.data(), data.size() * sizeof(float));
+    return 1;
+}
 }

@@ -392,9 +392,12 @@ __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_megakerne
     __shared__ ShellSlots shellSlots[kBlockThreads / 32];
     ShellSlots &slots = shellSlots[threadIdx.x >> 5];
 
+    // the per-pixel running sum CONTINUES from the accumulator (zero for a fresh render): sample ranges traced one
+    // after another give the bits of a single launch over the whole range (progressive refinement, resume)
     Lane L;
-    L.sum = v3(0.f, 0.f, 0.f);
-    L.count = 0.f;
+    float4 const acc0 = inside ? p.accum[pixel] : make_float4(0.f, 0.f, 0.f, 0.f);
+    L.sum = v3(acc0.x, acc0.y, acc0.z);
+    L.count = acc0.w;
     L.mode = MODE_NEW;
     L.sample = p.sampleBegin;
     L.dir = v3(0.f, 0.f, 1.f);
@@ -447,12 +450,8 @@ __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_megakerne
     }
     if (inside)
     {
-        // one lane owns one pixel for the whole launch: plain read-modify-write, no atomics
-        float4 a = p.accum[pixel];
-        a.x = fadd(a.x, L.sum.x);
-        a.y = fadd(a.y, L.sum.y);
-        a.z = fadd(a.z, L.sum.z);
-        a.w = fadd(a.w, L.count);
+        // one lane owns one pixel for the whole launch: plain load at the start, plain store here, no atomics
+        float4 const a = make_float4(L.sum.x, L.sum.y, L.sum.z, L.count);
         p.accum[pixel] = a;
     }
     if (p.counters)

@@ -101,7 +101,11 @@ __global__ void __launch_bounds__(kBlockThreads, 2) trace_wavefront(const __grid
         bool const inside = px < p.xEnd && py < p.yEnd;
         uint32_t const pixel = py * p.width + px;
         uint64_t const pixKey = pixel_key(p.seed, pixel);
-        S.sr[tid] = S.sg[tid] = S.sb[tid] = S.sn[tid] = 0.f;
+        {
+            // the running sum continues from the accumulator (see trace_megakernel)
+            float4 const acc0 = inside ? p.accum[pixel] : make_float4(0.f, 0.f, 0.f, 0.f);
+            S.sr[tid] = acc0.x; S.sg[tid] = acc0.y; S.sb[tid] = acc0.z; S.sn[tid] = acc0.w;
+        }
         S.mode[tid] = MODE_NEW;
         S.sample[tid] = inside ? p.sampleBegin : p.sampleEnd;
         S.cr[tid] = S.cg[tid] = S.cb[tid] = 0.f;
@@ -305,12 +309,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) trace_wavefront(const __grid
 
         if (inside)
         {
-            float4 a = p.accum[pixel];
-            a.x = fadd(a.x, S.sr[tid]);
-            a.y = fadd(a.y, S.sg[tid]);
-            a.z = fadd(a.z, S.sb[tid]);
-            a.w = fadd(a.w, S.sn[tid]);
-            p.accum[pixel] = a;
+            p.accum[pixel] = make_float4(S.sr[tid], S.sg[tid], S.sb[tid], S.sn[tid]);
         }
     }
     if (p.counters)

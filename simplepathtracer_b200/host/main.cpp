@@ -5,6 +5,10 @@
 //
 //   spt_headless [--scene reference|random|metalglass|lattice] [--seed S] [--width W] [--height H]
 //                [--spp N] [--depth D] [--tracer recursive|task|wavefront] [--tiles T] [--out file.bmp]
+//                [--progressive P]   P passes over the samples on a persistent accumulator; prints k/P and rewrites
+//                                    the image after each (the reference's live preview, Renderer.hpp:157-164)
+//                [--pfm file.pfm]    also write the linear float image (needs --progressive >= 1)
+//                [--checkpoint file] resume from the accumulators in `file` when it matches, write them back at the end
 #include "../../include/spt_host/Scene.hpp"
 #include "../../include/spt_host/SceneGenerators.hpp"
 #include "../../include/spt_host/Image.hpp"
@@ -15,11 +19,13 @@
 #include <iostream>
 #include <string>
 #include <thread>
+#include <vector>
 
 int main(int argc, char **argv)
 {
     std::string scene = "reference", tracer = "recursive", out;
-    uint32_t seed = 1, width = 1440, height = 1440, spp = 100, depth = 10, tiles = 1;
+    std::string pfm, checkpoint;
+    uint32_t seed = 1, width = 1440, height = 1440, spp = 100, depth = 10, tiles = 1, progressive = 0;
     for (int i = 1; i + 1 < argc; i += 2)
     {
         std::string const k = argv[i], v = argv[i + 1];
@@ -32,6 +38,9 @@ int main(int argc, char **argv)
         else if (k == "--tracer") tracer = v;
         else if (k == "--tiles") tiles = uint32_t(std::stoul(v));
         else if (k == "--out") out = v;
+        else if (k == "--progressive") progressive = uint32_t(std::stoul(v));
+        else if (k == "--pfm") pfm = v;
+        else if (k == "--checkpoint") checkpoint = v;
         else { std::cerr << "unknown flag " << k << "\n"; return 2; }
     }
     SetRenderConfig(width, height, spp, depth);
@@ -44,9 +53,41 @@ int main(int argc, char **argv)
     spt_cuda::SetSeed(seed);
     spt_cuda::InvalidateScene();
 
+    if ((!pfm.empty() || !checkpoint.empty()) && progressive == 0)
+        progressive = 1;
     auto const t0 = std::chrono::high_resolution_clock::now();
     try
     {
+        if (progressive > 0)
+        {
+            uint32_t const passCap = tracer == "recursive" ? 0u : 10u;
+            uint32_t const variant = tracer == "wavefront" ? SPT_VARIANT_WAVEFRONT : SPT_VARIANT_MEGAKERNEL;
+            std::vector<float> accum(size_t(width) * height * 4u), resume;
+            io::AccumHeader h{};
+            uint32_t first = 0;
+            if (!checkpoint.empty() && io::LoadAccum(checkpoint.c_str(), width, height, h, resume) && h.depth == depth && h.seed == seed &&
+                h.samplesDone <= spp)
+            {
+                first = h.samplesDone;
+                std::cout << "Resuming at sample " << first << " of " << spp << std::endl;
+            }
+            else
+                resume.clear();
+            spt_cuda::RenderImageProgressiveCuda(
+                progressive, passCap, variant,
+                [&](uint32_t k, uint32_t n, uint32_t samplesDone) {
+                    std::cout << k << "/" << n << "  (" << samplesDone << " spp)" << std::endl; // Renderer.hpp:285
+                    if (n > 1 && !io::SaveImage(out.empty() ? nullptr : out.c_str()))               // the live preview, as a file
+                        std::cerr << "cannot write image\n";
+                },
+                first, resume.empty() ? nullptr : resume.data(), accum.data());
+            if (!pfm.empty() && !io::WritePfm(pfm.c_str(), width, height, accum.data()))
+                std::cerr << "cannot write " << pfm << "\n";
+            if (!checkpoint.empty() && !io::SaveAccum(checkpoint.c_str(), width, height, spp, depth, seed, accum.data()))
+                std::cerr << "cannot write " << checkpoint << "\n";
+        }
+        else
+        {
         // tiles == 1: RenderImage's single {0, H, 0, W} call (Renderer.hpp:304-308); tiles > 1: the
         // threadCount x threadCount grid of RenderImageParallelMain (Renderer.hpp:264-274), one call per tile
         uint32_t const sw = (g_width + tiles - 1) / tiles, sh = (g_height + tiles - 1) / tiles;
@@ -62,6 +103,7 @@ int main(int argc, char **argv)
                 else if (tracer == "wavefront") RenderSegmentCudaWavefront(seg);
                 else { std::cerr << "unknown tracer " << tracer << "\n"; return 2; }
             }
+        }
     }
     catch (std::exception const &e)
     {

@@ -54,3 +54,43 @@ def test_drop_in_inside_the_reference_translation_unit(tmp_path, scene):
     # two independent 512-spp estimates of the same image, compared after 8-bit gamma encoding
     assert psnr > 30.0, r.stdout
     assert abs(float(cpu.mean()) - float(gpu.mean())) < 1.0
+
+
+def read_pfm(path):
+    raw = open(path, "rb").read()
+    head, dims, scale, body = raw.split(b"\n", 3)
+    assert head == b"PF" and float(scale) < 0  # little-endian
+    w, h = (int(v) for v in dims.split())
+    return np.frombuffer(body, "<f4").reshape(h, w, 3)  # bottom row first == the tracers' y
+
+
+def test_headless_progressive_checkpoint_resume(tmp_path, oracle):
+    """--progressive passes leave the bits of a one-shot render; a render stopped at spp/2 with --checkpoint and
+    resumed to spp gives the same BMP, PFM and accumulators (the running sums continue across launches)."""
+    exe = os.path.join(ROOT, "simplepathtracer_b200", "host", "spt_headless")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-s", "-C", os.path.dirname(exe)], check=True)
+    w, h, spp, depth, seed = 80, 48, 12, 6, 5
+    base = [exe, "--scene", "reference", "--seed", str(seed), "--width", str(w), "--height", str(h), "--depth", str(depth), "--tracer", "task"]
+    one, prog, half = str(tmp_path / "one.bmp"), str(tmp_path / "prog.bmp"), str(tmp_path / "half.bmp")
+    pfm, ck = str(tmp_path / "img.pfm"), str(tmp_path / "render.sptacc")
+    assert subprocess.run(base + ["--spp", str(spp), "--out", one]).returncode == 0
+    r = subprocess.run(base + ["--spp", str(spp), "--out", prog, "--progressive", "4", "--pfm", pfm], capture_output=True, text=True)
+    assert r.returncode == 0 and "4/4" in r.stdout and f"({spp} spp)" in r.stdout, r.stdout + r.stderr
+    assert open(one, "rb").read() == open(prog, "rb").read()
+    # stop half way, then resume from the checkpoint
+    assert subprocess.run(base + ["--spp", str(spp // 2), "--out", half, "--checkpoint", ck]).returncode == 0
+    r = subprocess.run(base + ["--spp", str(spp), "--out", half, "--checkpoint", ck, "--progressive", "2"], capture_output=True, text=True)
+    assert r.returncode == 0 and f"Resuming at sample {spp // 2}" in r.stdout, r.stdout + r.stderr
+    assert open(one, "rb").read() == open(half, "rb").read()
+    # the oracle agrees with all of it, bytes and floats
+    import simplepathtracer_b200 as spt
+
+    scene = oracle.init_spheres(seed)
+    acc, _ = oracle.render_accum(scene, oracle.camera(), w, h, spp, depth, pass_cap=10, seed=seed)
+    assert np.array_equal(read_bmp(one), oracle.resolve(acc))
+    got = spt.load_accum(ck, w, h)
+    assert got is not None and got[1:] == (spp, depth, seed)
+    assert np.array_equal(got[0], acc)
+    want = (acc[..., :3] * (np.float32(1) / acc[..., 3:4])) / np.float32(255)
+    assert np.array_equal(read_pfm(pfm), want.astype(np.float32))

@@ -432,3 +432,32 @@ def test_streamed_equals_resident_on_segments(tracer, cam, scene_random):
     _, a = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=2, seg=seg, want_accum=True)
     _, b = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=2, seg=seg, want_accum=True, flags=spt.FLAG_STREAMED)
     assert_accum_equal(a, b)
+
+
+# ----------------------------------------------------------------------------- progressive rendering (context-owned accumulator)
+@pytest.mark.parametrize("variant", [spt.MEGAKERNEL, spt.WAVEFRONT])
+def test_progressive_passes_equal_one_render(tracer, oracle, cam, scene_random, variant):
+    """P passes over the samples, and per-tile calls in the reference scheduler's grid (Renderer.hpp:264-274), leave
+    the bits of one render: the per-pixel running sums continue from the accumulator."""
+    w, h, spp, depth = 96, 64, 12, 8
+    tracer.set_scene(scene_random)
+    _, one = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=6, want_accum=True, variant=variant)
+    tracer.progressive_begin(w, h)
+    for s0, s1 in [(0, 1), (1, 6), (6, 12)]:
+        for seg in [(0, 32, 0, 48), (0, 32, 48, 96), (32, 64, 0, 48), (32, 64, 48, 96)]:
+            tracer.progressive_add(cam, s0, s1, depth, pass_cap=10, seed=6, seg=seg, variant=variant)
+        rgb, acc = tracer.progressive_image(want_accum=True)
+        assert acc[..., 3].max() == s1
+    assert_accum_equal(acc, one)
+    oacc, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, pass_cap=10, seed=6)
+    assert_accum_equal(acc, oacc)
+    assert np.array_equal(rgb, oracle.resolve(oacc))
+    # resume: load a checkpoint of the first 6 samples into a fresh accumulator and finish
+    tracer.progressive_begin(w, h)
+    tracer.progressive_add(cam, 0, 6, depth, pass_cap=10, seed=6, variant=variant)
+    _, half = tracer.progressive_image(want_accum=True)
+    tracer.progressive_begin(w, h)
+    tracer.progressive_load(half)
+    tracer.progressive_add(cam, 6, 12, depth, pass_cap=10, seed=6, variant=variant)
+    _, acc2 = tracer.progressive_image(want_accum=True)
+    assert_accum_equal(acc2, one)

@@ -62,3 +62,24 @@ def test_exports_declared_in_header(lib):
     assert declared == sorted(binding.HOST_EXPORTS)
     for name in declared:
         assert hasattr(lib, name)
+
+
+def test_pfm_and_accumulator_checkpoint_files(tmp_path):
+    rng = np.random.default_rng(3)
+    acc = np.zeros((5, 7, 4), np.float32)
+    acc[..., :3] = rng.uniform(0, 255 * 9, size=(5, 7, 3))
+    acc[..., 3] = 9
+    pfm = str(tmp_path / "a.pfm")
+    spt.save_pfm(pfm, acc)
+    raw = open(pfm, "rb").read()
+    assert raw.startswith(b"PF\n7 5\n-1.0\n")
+    body = np.frombuffer(raw[len(b"PF\n7 5\n-1.0\n"):], "<f4").reshape(5, 7, 3)
+    want = (acc[..., :3] * (np.float32(1) / acc[..., 3:4])) / np.float32(255)
+    assert np.array_equal(body, want)
+    ck = str(tmp_path / "a.sptacc")
+    spt.save_accum(ck, acc, samples_done=9, depth=4, seed=77)
+    assert os.path.getsize(ck) == 32 + acc.nbytes
+    got = spt.load_accum(ck, 7, 5)
+    assert got is not None and np.array_equal(got[0], acc) and got[1:] == (9, 4, 77)
+    assert spt.load_accum(ck, 8, 5) is None  # another image size
+    assert spt.load_accum(str(tmp_path / "missing"), 7, 5) is None

@@ -34,6 +34,8 @@ from .binding import (  # noqa: F401
     generate_lattice,
     make_camera,
     save_bmp,
+    save_scene_file,
+    load_scene_file,
     save_pfm,
     save_accum,
     load_accum,

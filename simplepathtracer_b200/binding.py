@@ -172,6 +172,7 @@ EXPORTS = [
 ]
 HOST_EXPORTS = [
     "spt_host_init_spheres", "spt_host_generate_spheres", "spt_host_generate_metal_glass", "spt_host_generate_lattice",
+    "spt_host_save_scene", "spt_host_load_scene",
     "spt_host_camera_basis", "spt_host_save_bmp", "spt_host_save_pfm", "spt_host_save_accum", "spt_host_load_accum",
 ]
 
@@ -221,6 +222,9 @@ def load_library():
     L.spt_host_camera_basis.argtypes = [f32p, f32p, f32p, f32p]
     L.spt_host_camera_basis.restype = None
     L.spt_host_save_bmp.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, u8p]
+    L.spt_host_save_scene.argtypes = [C.c_char_p, C.c_uint32, f32p, f32p, u8p, f32p, f32p, f32p]
+    L.spt_host_load_scene.argtypes = [C.c_char_p, C.c_uint32, f32p, f32p, u8p, f32p, f32p, f32p]
+    L.spt_host_load_scene.restype = C.c_uint32
     L.spt_host_save_pfm.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, f32p]
     L.spt_host_save_accum.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, f32p]
     L.spt_host_load_accum.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, u32p, u32p, C.POINTER(C.c_uint64), f32p]
@@ -464,3 +468,30 @@ def load_accum(path: str, width: int, height: int):
     if not load_library().spt_host_load_accum(path.encode(), width, height, C.byref(sd), C.byref(dp), C.byref(seed), accum.ctypes.data_as(f32p)):
         return None
     return accum, int(sd.value), int(dp.value), int(seed.value)
+
+
+def save_scene_file(path: str, scene, eye=(0, 1, -3), look=(0, 1, 0), up=(0, 1, 0), sky=(137, 207, 240)) -> None:
+    """The scene + camera globals as a .sptscene file (include/spt_host/SceneFile.hpp)."""
+    sc = Scene.of(scene)
+    cam = np.array([*eye, 0, *look, 0, *up, 0, *sky, 0], np.float32)
+    ok = load_library().spt_host_save_scene(path.encode(), sc.n, sc.centers.ctypes.data_as(f32p), sc.radii.ctypes.data_as(f32p),
+                                            sc.materials.ctypes.data_as(u8p), sc.colors.ctypes.data_as(f32p), sc.fuzz.ctypes.data_as(f32p),
+                                            cam.ctypes.data_as(f32p))
+    if not ok:
+        raise SptError("cannot write " + path)
+
+
+def load_scene_file(path: str):
+    """Returns (Scene, camera dict with eye / look / up / sky) or raises on a malformed file."""
+    L = load_library()
+    cam = np.zeros(16, np.float32)
+    n = L.spt_host_load_scene(path.encode(), 0, None, None, None, None, None, cam.ctypes.data_as(f32p))
+    if n == 0:
+        raise SptError("not a scene file: " + path)
+    sc = Scene(np.zeros((n, 4), np.float32), np.zeros(n, np.float32), np.zeros(n, np.uint8), np.zeros((n, 4), np.float32),
+               np.zeros(n, np.float32))
+    got = L.spt_host_load_scene(path.encode(), n, sc.centers.ctypes.data_as(f32p), sc.radii.ctypes.data_as(f32p),
+                                sc.materials.ctypes.data_as(u8p), sc.colors.ctypes.data_as(f32p), sc.fuzz.ctypes.data_as(f32p),
+                                cam.ctypes.data_as(f32p))
+    assert got == n
+    return sc, {"eye": cam[0:3].copy(), "look": cam[4:7].copy(), "up": cam[8:11].copy(), "sky": cam[12:15].copy()}

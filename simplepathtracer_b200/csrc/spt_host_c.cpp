@@ -1,6 +1,7 @@
 // spt_host_c.cpp -- C exports (include/spt_host.h) over the header-only host mirror.
 #include "../../include/spt_host.h"
 #include "../../include/spt_host/Image.hpp"
+#include "../../include/spt_host/SceneFile.hpp"
 #include "../../include/spt_host/SceneGenerators.hpp"
 
 #include <cstring>
@@ -65,6 +66,35 @@ void spt_host_camera_basis(const float eye[3], const float look[3], const float 
 int spt_host_save_bmp(const char *path, uint32_t width, uint32_t height, const uint8_t *rgb8)
 {
     return io::WriteBmp(path, width, height, rgb8) ? 1 : 0;
+}
+int spt_host_save_scene(const char *path, uint32_t n, const float *c, const float *r, const uint8_t *m, const float *k, const float *f,
+                        const float camera16[16])
+{
+    std::lock_guard<std::mutex> g(g_lock);
+    spt_host::ClearScene();
+    for (uint32_t i = 0; i < n; ++i)
+        spt_host::PushSphere(math::MakeVec4(c[4 * i], c[4 * i + 1], c[4 * i + 2]), r[i], math::MakeVec4(k[4 * i], k[4 * i + 1], k[4 * i + 2]),
+                             static_cast<Material>(m[i]), f[i]);
+    g_sphereNumber = n;
+    std::memcpy(eyePos.xyzw, camera16 + 0, 16);
+    std::memcpy(lookAt.xyzw, camera16 + 4, 16);
+    std::memcpy(upDir.xyzw, camera16 + 8, 16);
+    std::memcpy(initColor.xyzw, camera16 + 12, 16);
+    return io::SaveScene(path) ? 1 : 0;
+}
+uint32_t spt_host_load_scene(const char *path, uint32_t cap, float *c, float *r, uint8_t *m, float *k, float *f, float camera16[16])
+{
+    std::lock_guard<std::mutex> g(g_lock);
+    if (!io::LoadScene(path))
+        return 0;
+    if (camera16)
+    {
+        std::memcpy(camera16 + 0, eyePos.xyzw, 16);
+        std::memcpy(camera16 + 4, lookAt.xyzw, 16);
+        std::memcpy(camera16 + 8, upDir.xyzw, 16);
+        std::memcpy(camera16 + 12, initColor.xyzw, 16);
+    }
+    return Export(cap, c, r, m, k, f);
 }
 int spt_host_save_pfm(const char *path, uint32_t width, uint32_t height, const float *accum4)
 {

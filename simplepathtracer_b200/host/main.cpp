@@ -3,13 +3,14 @@
 // GL/GLFW parts left out (no graphics stack on this box) and the compile-time constants of Globals.hpp:8-18
 // turned into flags.
 //
-//   spt_headless [--scene reference|random|metalglass|lattice] [--seed S] [--width W] [--height H]
+//   spt_headless [--scene reference|random|metalglass|lattice|<file.sptscene>] [--dump-scene file.sptscene] [--seed S] [--width W] [--height H]
 //                [--spp N] [--depth D] [--tracer recursive|task|wavefront] [--tiles T] [--out file.bmp]
 //                [--progressive P]   P passes over the samples on a persistent accumulator; prints k/P and rewrites
 //                                    the image after each (the reference's live preview, Renderer.hpp:157-164)
 //                [--pfm file.pfm]    also write the linear float image (needs --progressive >= 1)
 //                [--checkpoint file] resume from the accumulators in `file` when it matches, write them back at the end
 #include "../../include/spt_host/Scene.hpp"
+#include "../../include/spt_host/SceneFile.hpp"
 #include "../../include/spt_host/SceneGenerators.hpp"
 #include "../../include/spt_host/Image.hpp"
 #include "../../include/CudaPathTracer.hpp"
@@ -24,7 +25,7 @@
 int main(int argc, char **argv)
 {
     std::string scene = "reference", tracer = "recursive", out;
-    std::string pfm, checkpoint;
+    std::string pfm, checkpoint, dumpScene;
     uint32_t seed = 1, width = 1440, height = 1440, spp = 100, depth = 10, tiles = 1, progressive = 0;
     for (int i = 1; i + 1 < argc; i += 2)
     {
@@ -40,6 +41,7 @@ int main(int argc, char **argv)
         else if (k == "--out") out = v;
         else if (k == "--progressive") progressive = uint32_t(std::stoul(v));
         else if (k == "--pfm") pfm = v;
+        else if (k == "--dump-scene") dumpScene = v;
         else if (k == "--checkpoint") checkpoint = v;
         else { std::cerr << "unknown flag " << k << "\n"; return 2; }
     }
@@ -49,7 +51,8 @@ int main(int argc, char **argv)
     else if (scene == "random") GenerateSpheres(seed);      // eSceneGenerator::RANDOM
     else if (scene == "metalglass") GenerateMetalGlassSpheres(seed);
     else if (scene == "lattice") GenerateLatticeSpheres(seed);
-    else { std::cerr << "unknown scene " << scene << "\n"; return 2; }
+    else if (!io::LoadScene(scene.c_str())) { std::cerr << "unknown scene / not a scene file: " << scene << "\n"; return 2; }
+    if (!dumpScene.empty() && !io::SaveScene(dumpScene.c_str())) { std::cerr << "cannot write " << dumpScene << "\n"; return 1; }
     spt_cuda::SetSeed(seed);
     spt_cuda::InvalidateScene();
 

@@ -94,3 +94,17 @@ def test_headless_progressive_checkpoint_resume(tmp_path, oracle):
     assert np.array_equal(got[0], acc)
     want = (acc[..., :3] * (np.float32(1) / acc[..., 3:4])) / np.float32(255)
     assert np.array_equal(read_pfm(pfm), want.astype(np.float32))
+
+
+def test_headless_scene_file(tmp_path):
+    """--dump-scene writes the generated scene; rendering from the file gives the same image."""
+    exe = os.path.join(ROOT, "simplepathtracer_b200", "host", "spt_headless")
+    common = ["--seed", "4", "--width", "64", "--height", "40", "--spp", "4", "--depth", "6", "--tracer", "task"]
+    a, b, scn = str(tmp_path / "a.bmp"), str(tmp_path / "b.bmp"), str(tmp_path / "mg.sptscene")
+    assert subprocess.run([exe, "--scene", "metalglass", "--dump-scene", scn, "--out", a] + common).returncode == 0
+    assert subprocess.run([exe, "--scene", scn, "--out", b] + common).returncode == 0
+    assert open(a, "rb").read() == open(b, "rb").read()
+    import simplepathtracer_b200 as spt
+
+    sc, _ = spt.load_scene_file(scn)
+    assert sc.n == 501

@@ -83,3 +83,19 @@ def test_pfm_and_accumulator_checkpoint_files(tmp_path):
     assert got is not None and np.array_equal(got[0], acc) and got[1:] == (9, 4, 77)
     assert spt.load_accum(ck, 8, 5) is None  # another image size
     assert spt.load_accum(str(tmp_path / "missing"), 7, 5) is None
+
+
+def test_scene_file_round_trip(tmp_path):
+    for sc in (spt.generate_spheres(2), spt.generate_metal_glass(4, 500), spt.generate_lattice(5, 16)):
+        path = str(tmp_path / "scene.sptscene")
+        spt.save_scene_file(path, sc, eye=(1, 2, -4), look=(0, 1, 0), sky=(10, 20, 30))
+        size = 80 + sum((b + 15) // 16 * 16 for b in (sc.n * 16, sc.n * 4, sc.n, sc.n * 16, sc.n * 4))
+        assert os.path.getsize(path) == size and open(path, "rb").read(8) == b"SPTSCN1\0"
+        got, cam = spt.load_scene_file(path)
+        for name in ("centers", "radii", "materials", "colors", "fuzz"):
+            assert np.array_equal(getattr(got, name), getattr(sc, name)), name
+        assert tuple(cam["eye"]) == (1, 2, -4) and tuple(cam["sky"]) == (10, 20, 30)
+    bad = str(tmp_path / "bad.sptscene")
+    open(bad, "wb").write(b"SPTSCN1\0" + b"\x05\0\0\0" * 10)
+    with pytest.raises(spt.SptError):
+        spt.load_scene_file(bad)

@@ -218,7 +218,7 @@ def run_native_arm(args, wl):
         accum.zero_()
         if ev:
             ev[0].record()
-        pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, flags=spt.FLAG_COUNTERS, variant=variant)
+        pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, flags=spt.FLAG_COUNTERS | args.flags, variant=variant)
         if ev:
             ev[1].record()
         launches[0] += 1
@@ -306,10 +306,10 @@ def run_native_arm(args, wl):
     def step_e2e():
         pt.set_scene(scene)  # H2D: the scene globals (Globals.hpp:31-37)
         if world == 1:
-            pt.render(cam, W, H, spp, depth, pass_cap=PASS_CAP, seed=SEED, rgb8=rgb_host.numpy(), variant=variant)  # D2H inside
+            pt.render(cam, W, H, spp, depth, pass_cap=PASS_CAP, seed=SEED, rgb8=rgb_host.numpy(), variant=variant, flags=args.flags)  # D2H inside
         else:
             accum.zero_()
-            pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, variant=variant)
+            pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, variant=variant, flags=args.flags)
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
                 pt.resolve(accum, W, H, rgb_dev)
@@ -360,6 +360,7 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (debug only; invalidates the headline)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--variant", default="megakernel", choices=["megakernel", "wavefront"])
+    ap.add_argument("--flags", type=int, default=0, help="extra SPT_FLAG_* bits for the trace launches (experiments)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":

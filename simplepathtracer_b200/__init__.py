@@ -24,6 +24,7 @@ from .binding import (  # noqa: F401
     FLAG_CROSS_CHECK,
     FLAG_STREAMED,
     FLAG_RESIDENT,
+    FLAG_SPLIT,
     DIFFUSE,
     REFLECTIVE,
     REFRACTIVE,

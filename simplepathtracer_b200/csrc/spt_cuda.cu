@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -61,6 +62,14 @@ struct SptContext
     float4 *dAccum = nullptr;
     uint8_t *dRgb = nullptr;
     size_t accumPixels = 0;
+    // split rendering: camera-form filter blob (rebuilt when the eye changes) and the first-hit staging buffer
+    spt::FilterPair *dPairsCam = nullptr;
+    std::vector<unsigned char> hostBlob; // the general blob, kept to derive the camera form
+    std::vector<double> hostGeom;        // cx, cy, cz, r per SLOT in binary64
+    float camEye[3] = {NAN, NAN, NAN};
+    float camEpsT = 0.f;
+    uint16_t *dFirstHits = nullptr;
+    size_t firstHitsBytes = 0;
     // context-owned accumulator of the progressive entry points
     float4 *dProgAccum = nullptr;
     uint8_t *dProgRgb = nullptr;
@@ -156,6 +165,46 @@ void build_filter(const SptScene *s, std::vector<unsigned char> &blob, uint32_t 
         amaxD = std::max(amaxD, std::sqrt(a2));
     }
     amax = round_up_to_float(amaxD);
+}
+
+// Camera form of the blob (spt_filter.cuh, filter_pair_cam): per slot nkc = -(|C - E|^2 - r^2) + S_i + S_ray(E) - 1e-3 in
+// binary64, rounded up; S_ray and epsT exactly as make_filter_ray derives them for an origin at E.
+int ensure_camera_blob(SptContext *c, const float eye[3])
+{
+    if (c->dPairsCam && eye[0] == c->camEye[0] && eye[1] == c->camEye[1] && eye[2] == c->camEye[2])
+        return SPT_OK;
+    uint32_t const nSlots = c->filter.nSlots;
+    std::vector<unsigned char> blob = c->hostBlob;
+    spt::FilterPair *pairs = reinterpret_cast<spt::FilterPair *>(blob.data());
+    double const ex = eye[0], ey = eye[1], ez = eye[2];
+    double const oo = ex * ex + ey * ey + ez * ez, B = std::sqrt(oo), m = double(c->filter.amax) + B;
+    double sRay = oo * spt::kSlackU * 1.0002;
+    double epsT = 0.0;
+    if (m > 1024.0)
+    {
+        epsT = m * 9.5367431640625e-7 * 1.0000002;  // 2^-20 (Amax + B), not below the device's rounded-up value
+        sRay += m * m * 3.8146973e-6 * 1.000001;    // + 2^-18 (Amax + B)^2
+    }
+    for (uint32_t k = 0; k < nSlots; ++k)
+    {
+        double const cx = c->hostGeom[4 * k], cy = c->hostGeom[4 * k + 1], cz = c->hostGeom[4 * k + 2], r = c->hostGeom[4 * k + 3];
+        if (!(r >= 0.0)) // padding slot: stays never-pass
+            continue;
+        double const a2 = cx * cx + cy * cy + cz * cz;
+        double const dx = cx - ex, dy = cy - ey, dz = cz - ez;
+        double const slack = spt::kSlackU * (a2 + r * r);
+        pairs[k / 2].nk[k & 1] = round_up_to_float(-(dx * dx + dy * dy + dz * dz - r * r) + slack + sRay - double(1e-3f));
+    }
+    if (!c->dPairsCam)
+        SPT_CUDA_CHECK(cudaMalloc(&c->dPairsCam, blob.size() + 16));
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream)); // an earlier launch may still read the previous camera's records
+    if (!blob.empty())
+        SPT_CUDA_CHECK(cudaMemcpy(c->dPairsCam, blob.data(), blob.size(), cudaMemcpyHostToDevice));
+    c->camEye[0] = eye[0];
+    c->camEye[1] = eye[1];
+    c->camEye[2] = eye[2];
+    c->camEpsT = round_up_to_float(epsT);
+    return SPT_OK;
 }
 
 int check_camera(const SptCamera *cam)
@@ -277,6 +326,50 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
         SPT_CUDA_CHECK(cudaFuncSetAttribute(spt::trace_streamed, cudaFuncAttributeMaxDynamicSharedMemorySize, int(spt::kStreamSmemBytes)));
         spt::trace_streamed<<<grid, block, spt::kStreamSmemBytes, c->stream>>>(p);
     }
+    else if ((prm->flags & SPT_FLAG_SPLIT) && geomBytes + pairBytes <= SPT_RESIDENT_LIMIT_BYTES && c->n < 0xFFFFu &&
+             c->filter.nSlots > 0)
+    {
+        // split rendering: per chunk of samples, primary_hits_kernel (camera form of the filter, all lanes in step)
+        // writes the first-hit index of every camera sample, then the SPLIT megakernel runs the bounce loop on
+        // secondary rays only.  The per-pixel running sums continue across chunks.
+        int rc = ensure_camera_blob(c, cam->eye);
+        if (rc)
+            return rc;
+        p.filterCam = c->filter;
+        p.filterCam.pairs = c->dPairsCam;
+        p.filterCam.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairsCam + c->filter.nSlots / 2);
+        p.filterCam.epsTCam = c->camEpsT;
+        size_t const pixels = size_t(segW) * segH;
+        size_t const cap = size_t(2) << 30; // staging buffer: at most 2 GiB
+        uint32_t const total = prm->sample_end - prm->sample_begin;
+        uint32_t chunk = uint32_t(std::max<size_t>(1, std::min<size_t>(total, cap / (pixels * sizeof(uint16_t)))));
+        if (const char *knob = std::getenv("SPT_SPLIT_CHUNK")) // test knob: force several chunks on small renders
+            chunk = std::max<uint32_t>(1u, std::min<uint32_t>(chunk, uint32_t(std::atoi(knob))));
+        size_t const need = pixels * chunk * sizeof(uint16_t);
+        if (need > c->firstHitsBytes)
+        {
+            SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+            cudaFree(c->dFirstHits);
+            c->dFirstHits = nullptr;
+            c->firstHitsBytes = 0;
+            SPT_CUDA_CHECK(cudaMalloc(&c->dFirstHits, need));
+            c->firstHitsBytes = need;
+        }
+        p.firstHits = c->dFirstHits;
+        auto primary = spt::primary_hits_kernel<2>;
+        auto secondary = spt::trace_megakernel<2, false, true>;
+        SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(geomBytes + pairBytes)));
+        SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(geomBytes + pairBytes)));
+        for (uint32_t s0 = prm->sample_begin; s0 < prm->sample_end; s0 += chunk)
+        {
+            p.sampleBegin = s0;
+            p.sampleEnd = std::min(prm->sample_end, s0 + chunk);
+            primary<<<grid, block, geomBytes + pairBytes, c->stream>>>(p);
+            secondary<<<grid, block, geomBytes + pairBytes, c->stream>>>(p);
+            c->timing.launches += 2;
+        }
+        c->timing.launches -= 1; // the common tail below counts one
+    }
     else
     {
         if (geomBytes + pairBytes <= budget)
@@ -367,6 +460,8 @@ void spt_cuda_destroy(SptContext *c)
     cudaFree(c->dProbe);
     cudaFree(c->dProgAccum);
     cudaFree(c->dProgRgb);
+    cudaFree(c->dPairsCam);
+    cudaFree(c->dFirstHits);
     for (auto &e : c->ev)
         if (e)
             cudaEventDestroy(e);
@@ -440,6 +535,25 @@ int spt_cuda_set_scene(SptContext *c, const SptScene *s)
         SPT_CUDA_CHECK(cudaMemcpy(c->dPairs, blob.data(), blob.size(), cudaMemcpyHostToDevice));
     if (!big.empty())
         SPT_CUDA_CHECK(cudaMemcpy(c->dBigIdx, big.data(), big.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    // host copies from which the camera form of the records is derived per eye (ensure_camera_blob)
+    c->hostBlob = blob;
+    c->hostGeom.assign(size_t(nSlots) * 4, -1.0);
+    {
+        const uint32_t *slotIdx = reinterpret_cast<const uint32_t *>(blob.data() + size_t(nSlots) / 2 * sizeof(spt::FilterPair));
+        for (uint32_t k = 0; k < nSlots; ++k)
+        {
+            uint32_t const i = slotIdx[k];
+            if (i >= s->n)
+                continue; // padding: radius stays -1
+            c->hostGeom[4 * k + 0] = s->centers4[4 * i];
+            c->hostGeom[4 * k + 1] = s->centers4[4 * i + 1];
+            c->hostGeom[4 * k + 2] = s->centers4[4 * i + 2];
+            c->hostGeom[4 * k + 3] = std::fabs(double(s->radii[i]));
+        }
+    }
+    cudaFree(c->dPairsCam);
+    c->dPairsCam = nullptr;
+    c->camEye[0] = c->camEye[1] = c->camEye[2] = NAN;
     c->filter.pairs = c->dPairs;
     c->filter.nSlots = nSlots;
     c->filter.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairs + nSlots / 2);

@@ -62,6 +62,7 @@ struct FilterScene
     const uint32_t *bigIdx;   // spheres always evaluated exactly
     uint32_t nBig;
     float amax;               // max |C_i| over filtered spheres
+    float epsTCam;            // camera form only: the epsT the launch's records were built with (0 unless the eye is far away)
 };
 
 __host__ __device__ __forceinline__ uint32_t filter_blob_bytes(uint32_t nSlots)
@@ -156,6 +157,34 @@ __device__ __forceinline__ void filter_pair(const FilterPair *__restrict__ rec, 
 #endif
 }
 
+// Camera rays all start at the eye E, so everything of v that does not involve the direction is a per-sphere constant of
+// the launch: the record's 4th field then holds  nkc = -(|C - E|^2 - r^2) + S_i + S_ray(E) - 1e-3  (binary64 on the host,
+// rounded up) and the test is  v = tC^2 + nkc  with the same tC chain: 4 FFMA2 per record instead of 7 FFMA2 + 1 FADD2.
+// Fewer rounding steps than the general chain under the same slack, so it is conservative a fortiori.
+__device__ __forceinline__ void filter_pair_cam(const FilterPair *__restrict__ rec, const FilterRay &r, uint32_t &mask)
+{
+    ulonglong2 const a = *reinterpret_cast<const ulonglong2 *>(rec->cx); // (cx0,cx1) (cy0,cy1)
+    ulonglong2 const b = *reinterpret_cast<const ulonglong2 *>(rec->cz); // (cz0,cz1) (nkc0,nkc1)
+    unsigned long long const tc = fma2(b.x, r.dz, fma2(a.y, r.dy, fma2(a.x, r.dx, r.nod)));
+    unsigned long long const v = fma2(tc, tc, b.y);
+    float v0, v1;
+    unpack2(v, v0, v1);
+    mask = __funnelshift_l(__float_as_uint(v0), mask, 1);
+    mask = __funnelshift_l(__float_as_uint(v1), mask, 1);
+}
+// per-ray constants of the camera form: direction and -(E.D) + epsT (epsT is a constant of the launch)
+__device__ __forceinline__ FilterRay make_filter_ray_cam(V3 dir, float od, float epsT)
+{
+    float const nod = __fadd_ru(-od, epsT);
+    FilterRay r;
+    r.dx = pack2(dir.x, dir.x);
+    r.dy = pack2(dir.y, dir.y);
+    r.dz = pack2(dir.z, dir.z);
+    r.nod = pack2(nod, nod);
+    r.ox2 = r.oy2 = r.oz2 = r.noo = 0ull; // unused
+    return r;
+}
+
 // The pre-filter over a SPAN of slots (a multiple of kQuadSpheres; the whole list, or one staged chunk of it),
 // followed by the exact sequence on the span's candidates.  minIndex / minDistanceSq carry the running closest
 // hit across spans.  `live` = false marks a lane that only keeps its warp company (finished pixel): it runs the
@@ -166,7 +195,7 @@ __device__ __forceinline__ void filter_pair(const FilterPair *__restrict__ rec, 
 // only the quads (4 records) that exist.  The masks of up to kSuperWords words are parked in registers and
 // the divergent candidate loop runs once per super-word, so lanes with candidates in different words of the
 // same super-word are served in the same trips.
-template <typename GeomPtr>
+template <bool CAM = false, typename GeomPtr>
 __device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_t *slotIdx, uint32_t spanSlots, const FilterRay &fr,
                                             GeomPtr geom, uint32_t n, V3 dir, V3 org, float od, uint32_t &minIndex,
                                             float &minDistanceSq, uint32_t &exactEvals, bool live)
@@ -182,7 +211,12 @@ __device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_
         {
 #pragma unroll
             for (uint32_t pp = 0; pp < kWordSpheres / 2; ++pp)
-                filter_pair(rec + pp, fr, mask);
+            {
+                if (CAM)
+                    filter_pair_cam(rec + pp, fr, mask);
+                else
+                    filter_pair(rec + pp, fr, mask);
+            }
             rec += kWordSpheres / 2;
         }
         else
@@ -192,7 +226,12 @@ __device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_
             {
 #pragma unroll
                 for (uint32_t pp = 0; pp < kQuadSpheres / 2; ++pp)
-                    filter_pair(rec + pp, fr, mask);
+                {
+                    if (CAM)
+                        filter_pair_cam(rec + pp, fr, mask);
+                    else
+                        filter_pair(rec + pp, fr, mask);
+                }
                 rec += kQuadSpheres / 2;
             }
             uint32_t const sh = kWordSpheres - kQuadSpheres * tailQuads; // 8, 16 or 24 missing slots: fail bits
@@ -261,6 +300,20 @@ __device__ __forceinline__ uint32_t closest_hit_filtered(const FilterScene &fs, 
     exact_big_spheres(fs, geom, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
     FilterRay const fr = make_filter_ray(dir, org, od, fs.amax);
     filter_span(fs.pairs, fs.slotIdx, fs.nSlots, fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
+    return minIndex;
+}
+
+// the same for a camera ray (org = the eye the records in `fs` were specialised for)
+template <typename GeomPtr>
+__device__ __forceinline__ uint32_t closest_hit_camera(const FilterScene &fs, GeomPtr geom, uint32_t n, V3 dir, V3 org,
+                                                       uint32_t &exactEvals, bool live = true)
+{
+    uint32_t minIndex = n;
+    float minDistanceSq = FLT_MAX;
+    float const od = vdot(org, dir);
+    exact_big_spheres(fs, geom, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
+    FilterRay const fr = make_filter_ray_cam(dir, od, fs.epsTCam);
+    filter_span<true>(fs.pairs, fs.slotIdx, fs.nSlots, fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
     return minIndex;
 }
 

@@ -461,3 +461,34 @@ def test_progressive_passes_equal_one_render(tracer, oracle, cam, scene_random, 
     tracer.progressive_add(cam, 6, 12, depth, pass_cap=10, seed=6, variant=variant)
     _, acc2 = tracer.progressive_image(want_accum=True)
     assert_accum_equal(acc2, one)
+
+
+# ----------------------------------------------------------------------------- split rendering (primary pass + secondary bounce loop)
+@pytest.mark.parametrize("which", ["init", "random", "metal_glass"])
+@pytest.mark.parametrize("pass_cap", [0, 10, 1])
+def test_split_render_bit_exact(tracer, oracle, cam, scene_init, scene_random, scene_metal_glass, which, pass_cap, monkeypatch):
+    """SPT_FLAG_SPLIT: camera segments traced by primary_hits_kernel with the camera form of the pre-filter, bounce loop
+    on secondary rays only.  Same bits as the oracle, same counters; several chunks of samples on purpose."""
+    scene = {"init": scene_init, "random": scene_random, "metal_glass": scene_metal_glass}[which]
+    monkeypatch.setenv("SPT_SPLIT_CHUNK", "3")
+    w, h, spp, depth = 100, 45, 7, 12
+    tracer.set_scene(scene)
+    tracer.reset_counters()
+    rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=pass_cap, seed=17, want_accum=True, flags=spt.FLAG_SPLIT | spt.FLAG_COUNTERS)
+    c = tracer.counters()
+    oacc, octr = oracle.render_accum(scene, cam, w, h, spp, depth, pass_cap=pass_cap, seed=17)
+    assert_accum_equal(acc, oacc)
+    assert np.array_equal(rgb, oracle.resolve(oacc))
+    assert c["segments"] == octr["segments"] and c["samples"] == octr["samples"] and c["dropped"] == octr["dropped"]
+
+
+def test_split_render_segment_and_other_camera(tracer, oracle, scene_random):
+    """An off-axis, far-away eye (the camera records are rebuilt per eye; epsT > 0 beyond |E| + Amax > 1024) and a segment."""
+    tracer.set_scene(scene_random)
+    for eye in ((3.0, 2.5, -6.0), (0.0, 400.0, -1500.0)):
+        cam = oracle.camera(eye=eye, look=(0, 1, 5))
+        w, h, spp, depth = 90, 50, 4, 8
+        seg = (4, 41, 9, 77)
+        _, acc = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=3, seg=seg, want_accum=True, flags=spt.FLAG_SPLIT)
+        oacc, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, pass_cap=10, seed=3, seg=seg)
+        assert_accum_equal(acc, oacc)

@@ -273,7 +273,8 @@ def run_native_arm(args, wl):
     value = total_samples / (ms_step * 1e-3) / 1e6
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kernel_events]))
     ctr = pt.counters()
-    launches_native = int(sumr(launches[0]))
+    trace_launches = pt.timing()["launches"]  # kernels of ONE accumulate call (split rendering: 2 per chunk of samples)
+    launches_native = int(sumr(launches[0] + args.steps * (trace_launches - 1)))
 
     # ---- roofline of the dominant kernel (rank 0's trace kernel) ----------------------------------
     peak_scalar, peak_packed = pt.measure_fp32_peak()
@@ -292,7 +293,9 @@ def run_native_arm(args, wl):
         "bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
         "traffic": traffic,
         "exact_evals_per_segment": ctr["exact"] / max(ctr["segments"], 1),
-        "kernel": "trace_" + args.variant, "kernel_ms": kernel_ms, "kernel_share_of_step": kernel_ms / ms_step,
+        "kernel": ("trace_" + args.variant) if (args.variant == "wavefront" or trace_launches == 1)
+                  else f"primary_hits_kernel + trace_secondary ({trace_launches // 2} chunk(s) of samples)",
+        "kernel_ms": kernel_ms, "kernel_share_of_step": kernel_ms / ms_step,
         "algorithmic": f"{FLOP_PER_TEST} flop x {tests_per_launch:.4g} ray-sphere tests per launch "
                        f"({ctr['segments'] / args.steps:.4g} ray segments x {scene.n} spheres; {ctr['segments'] / max(ctr['samples'], 1):.3f} segments/sample)",
         "peak_source": f"measured in this run: dependent-FMA chains on all SMs, scalar {peak_scalar:.1f} / packed f32x2 {peak_packed:.1f} TFLOP/s "

@@ -25,6 +25,7 @@ from .binding import (  # noqa: F401
     FLAG_STREAMED,
     FLAG_RESIDENT,
     FLAG_SPLIT,
+    FLAG_SINGLE_KERNEL,
     DIFFUSE,
     REFLECTIVE,
     REFRACTIVE,

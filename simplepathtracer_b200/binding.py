@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_NAME = "libspt_cuda.so"
 
 MEGAKERNEL, WAVEFRONT = 0, 1
-FLAG_STRICT_LOOP, FLAG_COUNTERS, FLAG_CROSS_CHECK, FLAG_STREAMED, FLAG_RESIDENT, FLAG_SPLIT = 1, 2, 4, 8, 16, 32
+FLAG_STRICT_LOOP, FLAG_COUNTERS, FLAG_CROSS_CHECK, FLAG_STREAMED, FLAG_RESIDENT, FLAG_SPLIT, FLAG_SINGLE_KERNEL = 1, 2, 4, 8, 16, 32, 64
 SKYBOX, REFLECTIVE, REFRACTIVE, DIFFUSE = 0, 1, 2, 3  # include/Definitions.hpp:7-13
 
 f32p = C.POINTER(C.c_float)

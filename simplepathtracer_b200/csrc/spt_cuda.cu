@@ -4,6 +4,7 @@
 #include "spt_kernels.cuh"
 #include "spt_wavefront.cuh"
 #include "spt_streamed.cuh"
+#include "spt_split.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -326,7 +327,7 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
         SPT_CUDA_CHECK(cudaFuncSetAttribute(spt::trace_streamed, cudaFuncAttributeMaxDynamicSharedMemorySize, int(spt::kStreamSmemBytes)));
         spt::trace_streamed<<<grid, block, spt::kStreamSmemBytes, c->stream>>>(p);
     }
-    else if ((prm->flags & SPT_FLAG_SPLIT) && geomBytes + pairBytes <= SPT_RESIDENT_LIMIT_BYTES && c->n < 0xFFFFu &&
+    else if (!(prm->flags & SPT_FLAG_SINGLE_KERNEL) && geomBytes + pairBytes <= SPT_RESIDENT_LIMIT_BYTES && c->n < 0xFFFFu &&
              c->filter.nSlots > 0)
     {
         // split rendering: per chunk of samples, primary_hits_kernel (camera form of the filter, all lanes in step)
@@ -357,7 +358,7 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
         }
         p.firstHits = c->dFirstHits;
         auto primary = spt::primary_hits_kernel<2>;
-        auto secondary = spt::trace_megakernel<2, false, true>;
+        auto secondary = spt::trace_secondary<2>;
         SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(geomBytes + pairBytes)));
         SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(geomBytes + pairBytes)));
         for (uint32_t s0 = prm->sample_begin; s0 < prm->sample_end; s0 += chunk)

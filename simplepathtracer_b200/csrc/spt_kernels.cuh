@@ -41,8 +41,8 @@ struct TraceParams
     FilterScene filter;  // pre-filter records (global memory copies)
     float4 *accum;       // width*height (sum r, sum g, sum b, count), row y*width + x (not flipped)
     unsigned long long *counters; // [0] segments [1] samples [2] dropped [3] exact evaluations (may be null)
-    // split rendering (primary_hits_kernel -> trace_megakernel<.., SPLIT>): first-hit sphere index of every camera
-    // sample of the launch, [(y - yBegin) * segW + (x - xBegin)][sample - sampleBegin], 0xFFFF = miss
+    // split rendering (spt_split.cuh): first-hit sphere index of every camera sample of the launch,
+    // [(y - yBegin) * segW + (x - xBegin)][sample - sampleBegin], 0xFFFF = miss
     uint16_t *firstHits;
     FilterScene filterCam; // pre-filter records specialised for the eye (camera form)
 };
@@ -360,10 +360,7 @@ __device__ __forceinline__ void lane_pixel(const TraceParams &p, uint32_t &x, ui
 // reads the same address: a broadcast).  2 = exact geometry + pre-filter records, 1 = pre-filter records only
 // (strict: geometry only), 0 = nothing (lists larger than shared memory are read through L1/L2 with
 // warp-uniform addresses).  STRICT: no pre-filter, every sphere through the exact sequence.
-// SPLIT: the camera segment of every sample was traced by primary_hits_kernel (cheaper filter form, all lanes in step);
-// a lane that needs a new sample consumes its stored first-hit index instead of tracing, shades it (a warp-wide
-// shade_step of the fresh lanes) and joins the closest-hit loop with its first SECONDARY ray in the same iteration.
-template <int STAGE, bool STRICT, bool SPLIT = false>
+template <int STAGE, bool STRICT>
 __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_megakernel(const __grid_constant__ TraceParams p)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
@@ -424,53 +421,8 @@ __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_megakerne
     // All 32 lanes stay in the loop until the whole warp is finished (the shell sampler is a warp
     // collective); a lane whose pixel is complete is carried along with live = false.
     bool live = inside;
-    size_t const hitBase = SPLIT ? (size_t(y - p.yBegin) * (p.xEnd - p.xBegin) + (x - p.xBegin)) * (p.sampleEnd - p.sampleBegin) : 0;
     for (;;)
     {
-        if (SPLIT)
-        {
-            bool fresh = false;
-            uint32_t freshIdx = p.n;
-            while (live && L.mode == MODE_NEW)
-            {
-                if (L.sample >= p.sampleEnd)
-                {
-                    live = false;
-                    break;
-                }
-                uint32_t const h = p.firstHits[hitBase + (L.sample - p.sampleBegin)];
-                L.rng.key = stream_key(pixKey, L.sample);
-                L.rng.event = 0;
-                L.rng.open_event();
-                float xiU, xiV;
-                L.rng.uniform2(-1.f, 1.f, xiU, xiV);
-                L.dir = primary_direction(p.cam, widthF, heightF, x, y, xiU, xiV);
-                L.org = v3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
-                L.specular = 0;
-                L.mode = MODE_TRACE;
-                ++L.sample;
-                if (h == kMissU16)
-                {
-                    // SampleColorSkybox on a miss: terminal, no scatter, no random numbers
-                    L.sum = vadd(L.sum, sample_sky(p.cam, L.dir));
-                    L.count = fadd(L.count, 1.f);
-                    L.mode = MODE_NEW;
-                    continue;
-                }
-                fresh = true;
-                freshIdx = h;
-                break;
-            }
-            if (!__any_sync(0xffffffffu, live))
-                break;
-            if (__any_sync(0xffffffffu, fresh))
-                shade_step(p, geom, L, freshIdx, dropped, fresh, slots);
-            bool const needTrace = live && L.mode != MODE_NEW; // a fresh hit may have ended its path (pass cap, SKYBOX sphere)
-            uint32_t const idx = closest_hit_filtered(fs, geom, p.n, L.dir, L.org, exactEvals, needTrace);
-            segments += needTrace ? 1u : 0u;
-            shade_step(p, geom, L, idx, dropped, needTrace, slots);
-            continue;
-        }
         if (live && L.mode == MODE_NEW)
         {
             if (L.sample >= p.sampleEnd)
@@ -512,61 +464,9 @@ __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_megakerne
     {
         __syncwarp();
         warp_counter_add(p.counters + 0, segments);
-        warp_counter_add(p.counters + 1, (inside && !SPLIT) ? (p.sampleEnd - p.sampleBegin) : 0u);
+        warp_counter_add(p.counters + 1, inside ? (p.sampleEnd - p.sampleBegin) : 0u);
         warp_counter_add(p.counters + 2, dropped);
         warp_counter_add(p.counters + 3, STRICT ? segments * (unsigned long long)(p.n) : exactEvals);
-    }
-}
-
-// The camera segment of every sample of the launch, all lanes in step: jittered primary ray (the same counter-RNG
-// draws trace_megakernel makes), closest hit with the camera form of the pre-filter (4 FFMA2 per record), index
-// stored for trace_megakernel<.., SPLIT>.  No shading, no divergence outside the exact-candidate loop.
-template <int STAGE>
-__global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) primary_hits_kernel(const __grid_constant__ TraceParams p)
-{
-    extern __shared__ __align__(16) unsigned char smemRaw[];
-    __shared__ __align__(8) uint64_t mbar;
-    uint32_t const geomBytes = p.n * uint32_t(sizeof(float4));
-    uint32_t const blobBytes = filter_blob_bytes(p.filterCam.nSlots);
-    const float4 *geom = p.geom;
-    FilterScene fs = p.filterCam;
-    if (STAGE == 2)
-    {
-        stage_scene_tma(smemRaw, p.geom, geomBytes, smemRaw + geomBytes, p.filterCam.pairs, blobBytes, &mbar);
-        geom = reinterpret_cast<const float4 *>(smemRaw);
-        rebase_filter(fs, smemRaw + geomBytes);
-    }
-    uint32_t x, y;
-    bool inside;
-    lane_pixel(p, x, y, inside);
-    uint32_t const pixel = y * p.width + x;
-    float const widthF = __uint2float_rn(p.width), heightF = __uint2float_rn(p.height);
-    uint64_t const pixKey = pixel_key(p.seed, pixel);
-    V3 const eye = v3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
-    uint32_t const nSamples = p.sampleEnd - p.sampleBegin;
-    uint16_t *out = p.firstHits + (size_t(y - p.yBegin) * (p.xEnd - p.xBegin) + (x - p.xBegin)) * nSamples;
-    uint32_t exactEvals = 0;
-    if (!__any_sync(0xffffffffu, inside))
-        return;
-    for (uint32_t s = 0; s < nSamples; ++s) // warp-uniform trip count
-    {
-        Rng rng;
-        rng.key = stream_key(pixKey, p.sampleBegin + s);
-        rng.event = 0;
-        rng.open_event();
-        float xiU, xiV;
-        rng.uniform2(-1.f, 1.f, xiU, xiV);
-        V3 const dir = primary_direction(p.cam, widthF, heightF, x, y, xiU, xiV);
-        uint32_t const idx = closest_hit_camera(fs, geom, p.n, dir, eye, exactEvals, inside);
-        if (inside)
-            out[s] = idx < p.n ? uint16_t(idx) : uint16_t(kMissU16);
-    }
-    if (p.counters)
-    {
-        __syncwarp();
-        warp_counter_add(p.counters + 0, inside ? nSamples : 0u);
-        warp_counter_add(p.counters + 1, inside ? nSamples : 0u);
-        warp_counter_add(p.counters + 3, exactEvals);
     }
 }
 

@@ -129,7 +129,7 @@ def test_prefilter_never_rejects_a_true_hit(tracer, scene_random, scene_init):
 # ----------------------------------------------------------------------------- renders
 @pytest.mark.parametrize("which", ["init", "random"])
 @pytest.mark.parametrize("pass_cap", [0, 10])
-@pytest.mark.parametrize("flags", [0, spt.FLAG_STRICT_LOOP])
+@pytest.mark.parametrize("flags", [0, spt.FLAG_SINGLE_KERNEL, spt.FLAG_STRICT_LOOP])
 def test_render_accumulators_bit_exact(tracer, oracle, cam, scene_init, scene_random, which, pass_cap, flags):
     scene = scene_init if which == "init" else scene_random
     w, h, spp, depth = 96, 64, 8, 8
@@ -384,7 +384,8 @@ def test_full_size_properties(tracer, cam, scene_metal_glass, scene_lattice, whi
     w, h = 1920, 1080
     tracer.set_scene(scene)
     outs = []
-    for variant, flags in ((spt.MEGAKERNEL, 0), (spt.MEGAKERNEL, spt.FLAG_STREAMED), (spt.MEGAKERNEL, spt.FLAG_RESIDENT),
+    for variant, flags in ((spt.MEGAKERNEL, 0), (spt.MEGAKERNEL, spt.FLAG_SINGLE_KERNEL), (spt.MEGAKERNEL, spt.FLAG_STREAMED),
+                           (spt.MEGAKERNEL, spt.FLAG_RESIDENT),
                            (spt.MEGAKERNEL, spt.FLAG_STRICT_LOOP), (spt.WAVEFRONT, 0)):
         if which == "c5" and flags == spt.FLAG_STRICT_LOOP:  # the strict loop over 16k spheres at full HD is minutes: use a band of it
             continue
@@ -431,7 +432,9 @@ def test_streamed_equals_resident_on_segments(tracer, cam, scene_random):
     seg = (5, 101, 17, 190)
     _, a = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=2, seg=seg, want_accum=True)
     _, b = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=2, seg=seg, want_accum=True, flags=spt.FLAG_STREAMED)
+    _, c = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=2, seg=seg, want_accum=True, flags=spt.FLAG_SINGLE_KERNEL)
     assert_accum_equal(a, b)
+    assert_accum_equal(a, c)
 
 
 # ----------------------------------------------------------------------------- progressive rendering (context-owned accumulator)

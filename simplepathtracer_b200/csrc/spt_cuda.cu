@@ -320,60 +320,63 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
         else
             SPT_LAUNCH(0, true, 0);
     }
-    else if ((prm->flags & SPT_FLAG_STREAMED) ||
-             (geomBytes + pairBytes > SPT_RESIDENT_LIMIT_BYTES && !(prm->flags & SPT_FLAG_RESIDENT) && c->filter.nSlots > 0))
-    {
-        // list too long to sit in shared memory next to four resident CTAs: TMA chunk ring (spt_streamed.cuh)
-        SPT_CUDA_CHECK(cudaFuncSetAttribute(spt::trace_streamed, cudaFuncAttributeMaxDynamicSharedMemorySize, int(spt::kStreamSmemBytes)));
-        spt::trace_streamed<<<grid, block, spt::kStreamSmemBytes, c->stream>>>(p);
-    }
-    else if (!(prm->flags & SPT_FLAG_SINGLE_KERNEL) && geomBytes + pairBytes <= SPT_RESIDENT_LIMIT_BYTES && c->n < 0xFFFFu &&
-             c->filter.nSlots > 0)
-    {
-        // split rendering: per chunk of samples, primary_hits_kernel (camera form of the filter, all lanes in step)
-        // writes the first-hit index of every camera sample, then the SPLIT megakernel runs the bounce loop on
-        // secondary rays only.  The per-pixel running sums continue across chunks.
-        int rc = ensure_camera_blob(c, cam->eye);
-        if (rc)
-            return rc;
-        p.filterCam = c->filter;
-        p.filterCam.pairs = c->dPairsCam;
-        p.filterCam.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairsCam + c->filter.nSlots / 2);
-        p.filterCam.epsTCam = c->camEpsT;
-        size_t const pixels = size_t(segW) * segH;
-        size_t const cap = size_t(2) << 30; // staging buffer: at most 2 GiB
-        uint32_t const total = prm->sample_end - prm->sample_begin;
-        uint32_t chunk = uint32_t(std::max<size_t>(1, std::min<size_t>(total, cap / (pixels * sizeof(uint16_t)))));
-        if (const char *knob = std::getenv("SPT_SPLIT_CHUNK")) // test knob: force several chunks on small renders
-            chunk = std::max<uint32_t>(1u, std::min<uint32_t>(chunk, uint32_t(std::atoi(knob))));
-        size_t const need = pixels * chunk * sizeof(uint16_t);
-        if (need > c->firstHitsBytes)
-        {
-            SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
-            cudaFree(c->dFirstHits);
-            c->dFirstHits = nullptr;
-            c->firstHitsBytes = 0;
-            SPT_CUDA_CHECK(cudaMalloc(&c->dFirstHits, need));
-            c->firstHitsBytes = need;
-        }
-        p.firstHits = c->dFirstHits;
-        auto primary = spt::primary_hits_kernel<2>;
-        auto secondary = spt::trace_secondary<2>;
-        SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(geomBytes + pairBytes)));
-        SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(geomBytes + pairBytes)));
-        for (uint32_t s0 = prm->sample_begin; s0 < prm->sample_end; s0 += chunk)
-        {
-            p.sampleBegin = s0;
-            p.sampleEnd = std::min(prm->sample_end, s0 + chunk);
-            primary<<<grid, block, geomBytes + pairBytes, c->stream>>>(p);
-            secondary<<<grid, block, geomBytes + pairBytes, c->stream>>>(p);
-            c->timing.launches += 2;
-        }
-        c->timing.launches -= 1; // the common tail below counts one
-    }
     else
     {
-        if (geomBytes + pairBytes <= budget)
+        bool const streamed = (prm->flags & SPT_FLAG_STREAMED) ||
+                              (geomBytes + pairBytes > SPT_RESIDENT_LIMIT_BYTES && !(prm->flags & SPT_FLAG_RESIDENT) && c->filter.nSlots > 0);
+        bool const fitsResident = geomBytes + pairBytes <= SPT_RESIDENT_LIMIT_BYTES;
+        bool const split = !(prm->flags & SPT_FLAG_SINGLE_KERNEL) && (streamed || fitsResident) && c->n < 0xFFFFu && c->filter.nSlots > 0;
+        size_t const smem = streamed ? size_t(spt::kStreamSmemBytes) : geomBytes + pairBytes;
+        if (split)
+        {
+            // split rendering (spt_split.cuh): per chunk of samples, the primary kernel (camera form of the filter, all lanes
+            // in step) writes the first-hit index of every camera sample, then the secondary kernel runs the bounce loop
+            // on secondary rays only.  The per-pixel running sums continue across chunks.
+            int rc = ensure_camera_blob(c, cam->eye);
+            if (rc)
+                return rc;
+            p.filterCam = c->filter;
+            p.filterCam.pairs = c->dPairsCam;
+            p.filterCam.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairsCam + c->filter.nSlots / 2);
+            p.filterCam.epsTCam = c->camEpsT;
+            size_t const pixels = size_t(segW) * segH;
+            size_t const cap = size_t(2) << 30; // staging buffer: at most 2 GiB
+            uint32_t const total = prm->sample_end - prm->sample_begin;
+            uint32_t chunk = uint32_t(std::max<size_t>(1, std::min<size_t>(total, cap / (pixels * sizeof(uint16_t)))));
+            if (const char *knob = std::getenv("SPT_SPLIT_CHUNK")) // test knob: force several chunks on small renders
+                chunk = std::max<uint32_t>(1u, std::min<uint32_t>(chunk, uint32_t(std::atoi(knob))));
+            size_t const need = pixels * chunk * sizeof(uint16_t);
+            if (need > c->firstHitsBytes)
+            {
+                SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+                cudaFree(c->dFirstHits);
+                c->dFirstHits = nullptr;
+                c->firstHitsBytes = 0;
+                SPT_CUDA_CHECK(cudaMalloc(&c->dFirstHits, need));
+                c->firstHitsBytes = need;
+            }
+            p.firstHits = c->dFirstHits;
+            void (*primary)(const spt::TraceParams) = streamed ? spt::primary_hits_streamed : spt::primary_hits_kernel<2>;
+            void (*secondary)(const spt::TraceParams) = streamed ? spt::trace_secondary_streamed : spt::trace_secondary<2>;
+            SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+            SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+            for (uint32_t s0 = prm->sample_begin; s0 < prm->sample_end; s0 += chunk)
+            {
+                p.sampleBegin = s0;
+                p.sampleEnd = std::min(prm->sample_end, s0 + chunk);
+                primary<<<grid, block, smem, c->stream>>>(p);
+                secondary<<<grid, block, smem, c->stream>>>(p);
+                c->timing.launches += 2;
+            }
+            c->timing.launches -= 1; // the common tail below counts one
+        }
+        else if (streamed)
+        {
+            // list too long to sit in shared memory next to four resident CTAs: TMA chunk ring (spt_streamed.cuh)
+            SPT_CUDA_CHECK(cudaFuncSetAttribute(spt::trace_streamed, cudaFuncAttributeMaxDynamicSharedMemorySize, int(spt::kStreamSmemBytes)));
+            spt::trace_streamed<<<grid, block, spt::kStreamSmemBytes, c->stream>>>(p);
+        }
+        else if (geomBytes + pairBytes <= budget)
             SPT_LAUNCH(2, false, geomBytes + pairBytes);
         else if (pairBytes <= budget)
             SPT_LAUNCH(1, false, pairBytes);

@@ -21,6 +21,7 @@
 #pragma once
 
 #include "spt_kernels.cuh"
+#include "spt_streamed.cuh"
 
 namespace spt
 {
@@ -165,6 +166,140 @@ __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_secondary
     }
     if (inside)
         p.accum[pixel] = make_float4(L.sum.x, L.sum.y, L.sum.z, L.count); // one lane owns one pixel: plain store
+    if (p.counters)
+    {
+        __syncwarp();
+        warp_counter_add(p.counters + 0, segments);
+        warp_counter_add(p.counters + 2, dropped);
+        warp_counter_add(p.counters + 3, exactEvals);
+    }
+}
+
+// ---- the same two kernels for lists that stream through the TMA chunk ring (spt_streamed.cuh) ---------------------
+__global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) primary_hits_streamed(const __grid_constant__ TraceParams p)
+{
+    extern __shared__ __align__(128) unsigned char ring[];
+    __shared__ __align__(8) uint64_t fullBar[kStages];
+    __shared__ __align__(8) uint64_t emptyBar[kStages];
+    StreamRing R;
+    stream_ring_init(R, ring, fullBar, emptyBar);
+    const float4 *geom = p.geom;
+    FilterScene const fs = p.filterCam;
+    uint32_t x, y;
+    bool inside;
+    lane_pixel(p, x, y, inside);
+    uint32_t const pixel = y * p.width + x;
+    float const widthF = __uint2float_rn(p.width), heightF = __uint2float_rn(p.height);
+    uint64_t const pixKey = pixel_key(p.seed, pixel);
+    V3 const eye = v3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
+    uint32_t const nSamples = p.sampleEnd - p.sampleBegin;
+    uint16_t *out = p.firstHits + (size_t(y - p.yBegin) * (p.xEnd - p.xBegin) + (x - p.xBegin)) * nSamples;
+    uint32_t exactEvals = 0;
+    bool const warpLive = __any_sync(0xffffffffu, inside);
+    for (uint32_t s = 0; s < nSamples; ++s) // CTA-uniform trip count
+    {
+        __syncthreads(); // no warp reads the ring any more
+        Rng rng;
+        rng.key = stream_key(pixKey, p.sampleBegin + s);
+        rng.event = 0;
+        rng.open_event();
+        float xiU, xiV;
+        rng.uniform2(-1.f, 1.f, xiU, xiV);
+        V3 const dir = primary_direction(p.cam, widthF, heightF, x, y, xiU, xiV);
+        uint32_t const idx = streamed_closest_hit<true>(fs, geom, p.n, dir, eye, R, exactEvals, inside, warpLive);
+        if (inside)
+            out[s] = idx < p.n ? uint16_t(idx) : uint16_t(kMissU16);
+    }
+    if (p.counters)
+    {
+        __syncwarp();
+        warp_counter_add(p.counters + 0, inside ? nSamples : 0u);
+        warp_counter_add(p.counters + 1, inside ? nSamples : 0u);
+        warp_counter_add(p.counters + 3, exactEvals);
+    }
+}
+
+__global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_secondary_streamed(const __grid_constant__ TraceParams p)
+{
+    extern __shared__ __align__(128) unsigned char ring[];
+    __shared__ __align__(8) uint64_t fullBar[kStages];
+    __shared__ __align__(8) uint64_t emptyBar[kStages];
+    __shared__ ShellSlots shellSlots[kBlockThreads / 32];
+    ShellSlots &slots = shellSlots[threadIdx.x >> 5];
+    StreamRing R;
+    stream_ring_init(R, ring, fullBar, emptyBar);
+    const float4 *geom = p.geom;
+    FilterScene const fs = p.filter;
+    uint32_t x, y;
+    bool inside;
+    lane_pixel(p, x, y, inside);
+    uint32_t const pixel = y * p.width + x;
+    float const widthF = __uint2float_rn(p.width), heightF = __uint2float_rn(p.height);
+
+    Lane L;
+    float4 const acc0 = inside ? p.accum[pixel] : make_float4(0.f, 0.f, 0.f, 0.f); // the running sum continues
+    L.sum = v3(acc0.x, acc0.y, acc0.z);
+    L.count = acc0.w;
+    L.mode = MODE_NEW;
+    L.sample = p.sampleBegin;
+    L.dir = v3(0.f, 0.f, 1.f);
+    L.org = v3(0.f, 0.f, 0.f);
+    L.chain = v3(0.f, 0.f, 0.f);
+    L.rng.state = 0;
+    L.rng.key = 0;
+    L.rng.event = 0;
+    L.rng.word = 0;
+    L.bounce = 0;
+    L.specular = 0;
+    uint32_t segments = 0, dropped = 0, exactEvals = 0;
+    uint64_t const pixKey = pixel_key(p.seed, pixel);
+    size_t const hitBase = (size_t(y - p.yBegin) * (p.xEnd - p.xBegin) + (x - p.xBegin)) * (p.sampleEnd - p.sampleBegin);
+
+    bool live = inside;
+    for (;;)
+    {
+        bool fresh = false;
+        uint32_t freshIdx = p.n;
+        while (live && L.mode == MODE_NEW)
+        {
+            if (L.sample >= p.sampleEnd)
+            {
+                live = false;
+                break;
+            }
+            uint32_t const h = p.firstHits[hitBase + (L.sample - p.sampleBegin)];
+            L.rng.key = stream_key(pixKey, L.sample);
+            L.rng.event = 0;
+            L.rng.open_event();
+            float xiU, xiV;
+            L.rng.uniform2(-1.f, 1.f, xiU, xiV);
+            L.dir = primary_direction(p.cam, widthF, heightF, x, y, xiU, xiV);
+            L.org = v3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
+            L.specular = 0;
+            ++L.sample;
+            if (h == kMissU16)
+            {
+                L.sum = vadd(L.sum, sample_sky(p.cam, L.dir));
+                L.count = fadd(L.count, 1.f);
+                continue;
+            }
+            L.mode = MODE_TRACE;
+            fresh = true;
+            freshIdx = h;
+        }
+        // also the barrier after which no warp reads the ring any more: the producer may start over
+        if (!__syncthreads_or(live ? 1 : 0))
+            break;
+        if (__any_sync(0xffffffffu, fresh))
+            shade_step(p, geom, L, freshIdx, dropped, fresh, slots);
+        bool const needTrace = live && L.mode != MODE_NEW;
+        bool const warpLive = __any_sync(0xffffffffu, needTrace);
+        uint32_t const idx = streamed_closest_hit<false>(fs, geom, p.n, L.dir, L.org, R, exactEvals, needTrace, warpLive);
+        segments += needTrace ? 1u : 0u;
+        shade_step(p, geom, L, idx, dropped, needTrace, slots);
+    }
+    if (inside)
+        p.accum[pixel] = make_float4(L.sum.x, L.sum.y, L.sum.z, L.count);
     if (p.counters)
     {
         __syncwarp();

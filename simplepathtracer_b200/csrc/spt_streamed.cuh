@@ -72,14 +72,20 @@ __device__ __forceinline__ void stream_produce(const FilterScene &fs, unsigned c
                  : "memory");
 }
 
-__global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_streamed(const __grid_constant__ TraceParams p)
+// The ring as the kernels carry it around
+struct StreamRing
 {
-    extern __shared__ __align__(128) unsigned char ring[];
-    __shared__ __align__(8) uint64_t fullBar[kStages];
-    __shared__ __align__(8) uint64_t emptyBar[kStages];
-    __shared__ ShellSlots shellSlots[kBlockThreads / 32];
-    ShellSlots &slots = shellSlots[threadIdx.x >> 5];
+    unsigned char *ring;
+    uint64_t *fullBar, *emptyBar;
+    uint32_t seq; // chunks this CTA has streamed so far: the ring position
+};
 
+__device__ __forceinline__ void stream_ring_init(StreamRing &R, unsigned char *ring, uint64_t *fullBar, uint64_t *emptyBar)
+{
+    R.ring = ring;
+    R.fullBar = fullBar;
+    R.emptyBar = emptyBar;
+    R.seq = 0;
     if (threadIdx.x == 0)
     {
         for (uint32_t s = 0; s < kStages; ++s)
@@ -90,12 +96,60 @@ __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_streamed(
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+}
+
+// FindClosestIntersectionSphere (Collision.hpp:87-109) over the streamed list.  Called by EVERY thread of the CTA, after
+// a CTA-wide barrier that follows the previous call (no warp reads the ring any more: the producer starts over at
+// chunk 0).  live = the lane has a ray; warpLive = some lane of the warp has (a warp without any only keeps the
+// barriers moving).  CAM: camera form of the records (fs = the eye-specialised blob).
+template <bool CAM>
+__device__ __forceinline__ uint32_t streamed_closest_hit(const FilterScene &fs, const float4 *geom, uint32_t n, V3 dir, V3 org,
+                                                         StreamRing &R, uint32_t &exactEvals, bool live, bool warpLive)
+{
+    constexpr uint32_t kAhead = kStages - 1u;
+    uint32_t const nChunks = (fs.nSlots + kChunkSlots - 1u) / kChunkSlots;
+    if (threadIdx.x == 0)
+        for (uint32_t c = 0; c < kAhead && c < nChunks; ++c)
+            stream_produce(fs, R.ring, R.fullBar, R.emptyBar, R.seq + c, c);
+    uint32_t minIndex = n;
+    float minDistanceSq = FLT_MAX;
+    float const od = vdot(org, dir);
+    exact_big_spheres(fs, geom, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
+    FilterRay const fr = CAM ? make_filter_ray_cam(dir, od, fs.epsTCam) : make_filter_ray(dir, org, od, fs.amax);
+    for (uint32_t c = 0; c < nChunks; ++c)
+    {
+        if (threadIdx.x == 0 && c + kAhead < nChunks)
+            stream_produce(fs, R.ring, R.fullBar, R.emptyBar, R.seq + c + kAhead, c + kAhead);
+        uint32_t const buf = (R.seq + c) % kStages, use = (R.seq + c) / kStages;
+        mbar_wait(R.fullBar + buf, use & 1u);
+        if (warpLive)
+        {
+            const unsigned char *chunk = R.ring + buf * kChunkBytes;
+            uint32_t const span = min(kChunkSlots, fs.nSlots - c * kChunkSlots);
+            filter_span<CAM>(reinterpret_cast<const FilterPair *>(chunk), reinterpret_cast<const uint32_t *>(chunk + kChunkRecordBytes),
+                             span, fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
+        }
+        __syncwarp();
+        if ((threadIdx.x & 31u) == 0u)
+            mbar_arrive(R.emptyBar + buf);
+    }
+    R.seq += nChunks;
+    return minIndex;
+}
+
+__global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_streamed(const __grid_constant__ TraceParams p)
+{
+    extern __shared__ __align__(128) unsigned char ring[];
+    __shared__ __align__(8) uint64_t fullBar[kStages];
+    __shared__ __align__(8) uint64_t emptyBar[kStages];
+    __shared__ ShellSlots shellSlots[kBlockThreads / 32];
+    ShellSlots &slots = shellSlots[threadIdx.x >> 5];
+
+    StreamRing R;
+    stream_ring_init(R, ring, fullBar, emptyBar);
 
     const float4 *geom = p.geom; // exact geometry through L1/L2: only candidates and shading touch it
     FilterScene const fs = p.filter;
-    uint32_t const nChunks = (fs.nSlots + kChunkSlots - 1u) / kChunkSlots;
-    constexpr uint32_t kAhead = kStages - 1u;
-
     uint32_t x, y;
     bool inside;
     lane_pixel(p, x, y, inside);
@@ -121,8 +175,6 @@ __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_streamed(
     L.specular = 0;
     uint32_t segments = 0, dropped = 0, exactEvals = 0;
     uint64_t const pixKey = pixel_key(p.seed, pixel);
-    uint32_t seq = 0; // chunks this CTA has streamed so far: the ring position
-
     bool live = inside;
     for (;;)
     {
@@ -152,34 +204,7 @@ __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_streamed(
             break;
         bool const warpLive = __any_sync(0xffffffffu, live);
 
-        if (threadIdx.x == 0)
-            for (uint32_t c = 0; c < kAhead && c < nChunks; ++c)
-                stream_produce(fs, ring, fullBar, emptyBar, seq + c, c);
-
-        // ---- FindClosestIntersectionSphere (Collision.hpp:87-109) over the streamed list ----
-        uint32_t minIndex = p.n;
-        float minDistanceSq = FLT_MAX;
-        float const od = vdot(L.org, L.dir);
-        exact_big_spheres(fs, geom, L.dir, L.org, od, minIndex, minDistanceSq, exactEvals, live);
-        FilterRay const fr = make_filter_ray(L.dir, L.org, od, fs.amax);
-        for (uint32_t c = 0; c < nChunks; ++c)
-        {
-            if (threadIdx.x == 0 && c + kAhead < nChunks)
-                stream_produce(fs, ring, fullBar, emptyBar, seq + c + kAhead, c + kAhead);
-            uint32_t const buf = (seq + c) % kStages, use = (seq + c) / kStages;
-            mbar_wait(fullBar + buf, use & 1u);
-            if (warpLive)
-            {
-                const unsigned char *chunk = ring + buf * kChunkBytes;
-                uint32_t const span = min(kChunkSlots, fs.nSlots - c * kChunkSlots);
-                filter_span(reinterpret_cast<const FilterPair *>(chunk), reinterpret_cast<const uint32_t *>(chunk + kChunkRecordBytes),
-                            span, fr, geom, p.n, L.dir, L.org, od, minIndex, minDistanceSq, exactEvals, live);
-            }
-            __syncwarp();
-            if ((threadIdx.x & 31u) == 0u)
-                mbar_arrive(emptyBar + buf);
-        }
-        seq += nChunks;
+        uint32_t const minIndex = streamed_closest_hit<false>(fs, geom, p.n, L.dir, L.org, R, exactEvals, live, warpLive);
         segments += live ? 1u : 0u;
         shade_step(p, geom, L, minIndex, dropped, live, slots);
     }

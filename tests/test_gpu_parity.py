@@ -347,8 +347,8 @@ def test_config4_first_hit_wide_index(tracer, oracle, cam, scene_metal_glass):
     assert gi[gi < scene_metal_glass.n].max() > 255  # indices the reference's uint8_t could not hold
 
 
-@pytest.mark.parametrize("variant,flags", [(spt.MEGAKERNEL, 0), (spt.MEGAKERNEL, spt.FLAG_RESIDENT), (spt.MEGAKERNEL, spt.FLAG_STRICT_LOOP),
-                                           (spt.WAVEFRONT, 0)])
+@pytest.mark.parametrize("variant,flags", [(spt.MEGAKERNEL, 0), (spt.MEGAKERNEL, spt.FLAG_SINGLE_KERNEL), (spt.MEGAKERNEL, spt.FLAG_RESIDENT),
+                                           (spt.MEGAKERNEL, spt.FLAG_STRICT_LOOP), (spt.WAVEFRONT, 0)])
 def test_config5_lattice_bit_exact(tracer, oracle, cam, scene_lattice, variant, flags):
     """16 384 spheres: neither the geometry nor the pre-filter records fit in shared memory."""
     w, h, spp, depth = 64, 40, 2, 16
@@ -411,14 +411,17 @@ def test_full_size_properties(tracer, cam, scene_metal_glass, scene_lattice, whi
 # ----------------------------------------------------------------------------- streamed sphere list (TMA chunk ring)
 @pytest.mark.parametrize("which", ["init", "random", "metal_glass", "lattice40"])
 @pytest.mark.parametrize("pass_cap", [0, 10])
-def test_streamed_megakernel_bit_exact(tracer, oracle, cam, scene_init, scene_random, scene_metal_glass, which, pass_cap):
+@pytest.mark.parametrize("single", [0, spt.FLAG_SINGLE_KERNEL])
+def test_streamed_megakernel_bit_exact(tracer, oracle, cam, scene_init, scene_random, scene_metal_glass, which, pass_cap, single, monkeypatch):
     """SPT_FLAG_STREAMED forces the chunk-ring kernel on lists of every length: a fraction of one chunk (10, 149),
     one almost full chunk (501) and several chunks with a ragged tail (1600 spheres = 3 full chunks + 63 slots)."""
     scene = {"init": scene_init, "random": scene_random, "metal_glass": scene_metal_glass}.get(which) or spt.generate_lattice(7, 40)
     w, h, spp, depth = 100, 45, 5, 12  # ragged tiles: CTAs with dead warps and dead lanes must keep the ring moving
+    monkeypatch.setenv("SPT_SPLIT_CHUNK", "2")  # split rendering (the default): 3 chunks of samples
     tracer.set_scene(scene)
     tracer.reset_counters()
-    rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=pass_cap, seed=33, want_accum=True, flags=spt.FLAG_STREAMED | spt.FLAG_COUNTERS)
+    rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=pass_cap, seed=33, want_accum=True,
+                             flags=spt.FLAG_STREAMED | spt.FLAG_COUNTERS | single)
     c = tracer.counters()
     oacc, octr = oracle.render_accum(scene, cam, w, h, spp, depth, pass_cap=pass_cap, seed=33)
     assert_accum_equal(acc, oacc)

@@ -303,6 +303,108 @@ __device__ __forceinline__ uint32_t closest_hit_filtered(const FilterScene &fs, 
     return minIndex;
 }
 
+// ---- camera form, TWO rays per lane -----------------------------------------------------------------
+// The camera form is so cheap (4 FFMA2 per record) that the shared-memory pipe, not the issue port, bounds it: two
+// broadcast LDS.128 are four LSU wavefronts per record and warp, 16 per SM for every 12 issue cycles of its four
+// sub-partitions (ncu: L1/TEX throughput 94 % on primary_hits_kernel with one ray per lane).  Running two camera rays
+// of the same pixel per lane through each loaded record halves the wavefronts per test and doubles the independent
+// FMA chains.
+__device__ __forceinline__ void filter_pair_cam2(const FilterPair *__restrict__ rec, const FilterRay &ra, const FilterRay &rb,
+                                                 uint32_t &maskA, uint32_t &maskB)
+{
+    ulonglong2 const a = *reinterpret_cast<const ulonglong2 *>(rec->cx);
+    ulonglong2 const b = *reinterpret_cast<const ulonglong2 *>(rec->cz);
+    unsigned long long const tca = fma2(b.x, ra.dz, fma2(a.y, ra.dy, fma2(a.x, ra.dx, ra.nod)));
+    unsigned long long const tcb = fma2(b.x, rb.dz, fma2(a.y, rb.dy, fma2(a.x, rb.dx, rb.nod)));
+    unsigned long long const va = fma2(tca, tca, b.y);
+    unsigned long long const vb = fma2(tcb, tcb, b.y);
+    float a0, a1, b0, b1;
+    unpack2(va, a0, a1);
+    unpack2(vb, b0, b1);
+    maskA = __funnelshift_l(__float_as_uint(a0), maskA, 1);
+    maskA = __funnelshift_l(__float_as_uint(a1), maskA, 1);
+    maskB = __funnelshift_l(__float_as_uint(b0), maskB, 1);
+    maskB = __funnelshift_l(__float_as_uint(b1), maskB, 1);
+}
+
+// exact sequence on the candidates parked in c0..c3 (words w0..w0+3 of the span)
+template <typename GeomPtr>
+__device__ __forceinline__ void resolve_candidates(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t w0, const uint32_t *slotIdx,
+                                                   GeomPtr geom, uint32_t n, V3 dir, V3 org, float od, uint32_t &minIndex,
+                                                   float &minDistanceSq, uint32_t &exactEvals)
+{
+    for (;;)
+    {
+        uint32_t ww, bits;
+        if (c0) { ww = 0; bits = c0; }
+        else if (c1) { ww = 1; bits = c1; }
+        else if (c2) { ww = 2; bits = c2; }
+        else if (c3) { ww = 3; bits = c3; }
+        else break;
+        uint32_t const j = __clz(bits);
+        uint32_t const cleared = bits & ~(0x80000000u >> j);
+        if (ww == 0) c0 = cleared;
+        else if (ww == 1) c1 = cleared;
+        else if (ww == 2) c2 = cleared;
+        else c3 = cleared;
+        uint32_t const i = slotIdx[(w0 + ww) * kWordSpheres + j];
+        if (i < n)
+        {
+            exact_sphere<false>(geom[i], i, dir, org, od, minIndex, minDistanceSq);
+            ++exactEvals;
+        }
+    }
+}
+
+// filter_span for two camera rays (A, B) sharing the origin; liveA / liveB as `live` in filter_span
+template <typename GeomPtr>
+__device__ __forceinline__ void filter_span_cam2(const FilterPair *rec, const uint32_t *slotIdx, uint32_t spanSlots, const FilterRay &fa,
+                                                 const FilterRay &fb, GeomPtr geom, uint32_t n, V3 org, V3 dirA, float odA, V3 dirB,
+                                                 float odB, uint32_t &minA, float &distA, uint32_t &minB, float &distB,
+                                                 uint32_t &exactEvals, bool liveA, bool liveB)
+{
+    uint32_t const nWords = (spanSlots + kWordSpheres - 1u) / kWordSpheres;
+    uint32_t const tailQuads = (spanSlots - (nWords - 1u) * kWordSpheres) / kQuadSpheres;
+    uint32_t a0 = 0u, a1 = 0u, a2 = 0u, a3 = 0u, b0 = 0u, b1 = 0u, b2 = 0u, b3 = 0u;
+#pragma unroll 1
+    for (uint32_t w = 0; w < nWords; ++w)
+    {
+        uint32_t maskA = 0xFFFFFFFFu, maskB = 0xFFFFFFFFu;
+        if (w + 1u < nWords || tailQuads == kWordSpheres / kQuadSpheres)
+        {
+#pragma unroll
+            for (uint32_t pp = 0; pp < kWordSpheres / 2; ++pp)
+                filter_pair_cam2(rec + pp, fa, fb, maskA, maskB);
+            rec += kWordSpheres / 2;
+        }
+        else
+        {
+#pragma unroll 1
+            for (uint32_t q = 0; q < tailQuads; ++q)
+            {
+#pragma unroll
+                for (uint32_t pp = 0; pp < kQuadSpheres / 2; ++pp)
+                    filter_pair_cam2(rec + pp, fa, fb, maskA, maskB);
+                rec += kQuadSpheres / 2;
+            }
+            uint32_t const sh = kWordSpheres - kQuadSpheres * tailQuads;
+            maskA = (maskA << sh) | ((1u << sh) - 1u);
+            maskB = (maskB << sh) | ((1u << sh) - 1u);
+        }
+        uint32_t const ca = liveA ? ~maskA : 0u, cb = liveB ? ~maskB : 0u;
+        uint32_t const k = w & (kSuperWords - 1u);
+        if (k == 0u) { a0 = ca; b0 = cb; }
+        else if (k == 1u) { a1 = ca; b1 = cb; }
+        else if (k == 2u) { a2 = ca; b2 = cb; }
+        else { a3 = ca; b3 = cb; }
+        if (k != kSuperWords - 1u && w + 1u != nWords)
+            continue;
+        resolve_candidates(a0, a1, a2, a3, w - k, slotIdx, geom, n, dirA, org, odA, minA, distA, exactEvals);
+        resolve_candidates(b0, b1, b2, b3, w - k, slotIdx, geom, n, dirB, org, odB, minB, distB, exactEvals);
+        a0 = a1 = a2 = a3 = b0 = b1 = b2 = b3 = 0u;
+    }
+}
+
 // the same for a camera ray (org = the eye the records in `fs` were specialised for)
 template <typename GeomPtr>
 __device__ __forceinline__ uint32_t closest_hit_camera(const FilterScene &fs, GeomPtr geom, uint32_t n, V3 dir, V3 org,
@@ -315,6 +417,21 @@ __device__ __forceinline__ uint32_t closest_hit_camera(const FilterScene &fs, Ge
     FilterRay const fr = make_filter_ray_cam(dir, od, fs.epsTCam);
     filter_span<true>(fs.pairs, fs.slotIdx, fs.nSlots, fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
     return minIndex;
+}
+
+// two camera rays of one lane (resident blob)
+template <typename GeomPtr>
+__device__ __forceinline__ void closest_hit_camera2(const FilterScene &fs, GeomPtr geom, uint32_t n, V3 org, V3 dirA, V3 dirB,
+                                                    uint32_t &idxA, uint32_t &idxB, uint32_t &exactEvals, bool liveA, bool liveB)
+{
+    idxA = idxB = n;
+    float distA = FLT_MAX, distB = FLT_MAX;
+    float const odA = vdot(org, dirA), odB = vdot(org, dirB);
+    exact_big_spheres(fs, geom, dirA, org, odA, idxA, distA, exactEvals, liveA);
+    exact_big_spheres(fs, geom, dirB, org, odB, idxB, distB, exactEvals, liveB);
+    FilterRay const fa = make_filter_ray_cam(dirA, odA, fs.epsTCam), fb = make_filter_ray_cam(dirB, odB, fs.epsTCam);
+    filter_span_cam2(fs.pairs, fs.slotIdx, fs.nSlots, fa, fb, geom, n, org, dirA, odA, dirB, odB, idxA, distA, idxB, distB, exactEvals, liveA,
+                     liveB);
 }
 
 } // namespace spt

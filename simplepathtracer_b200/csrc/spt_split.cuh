@@ -56,18 +56,29 @@ __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) primary_hits_ke
     uint32_t exactEvals = 0;
     if (!__any_sync(0xffffffffu, inside))
         return;
-    for (uint32_t s = 0; s < nSamples; ++s) // warp-uniform trip count
+    for (uint32_t s = 0; s < nSamples; s += 2) // warp-uniform trip count; two samples of the pixel per trip
     {
-        Rng rng;
-        rng.key = stream_key(pixKey, p.sampleBegin + s);
-        rng.event = 0;
-        rng.open_event();
-        float xiU, xiV;
-        rng.uniform2(-1.f, 1.f, xiU, xiV);
-        V3 const dir = primary_direction(p.cam, widthF, heightF, x, y, xiU, xiV);
-        uint32_t const idx = closest_hit_camera(fs, geom, p.n, dir, eye, exactEvals, inside);
+        bool const second = s + 1 < nSamples;
+        V3 dir[2];
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+        {
+            Rng rng;
+            rng.key = stream_key(pixKey, p.sampleBegin + s + (second ? uint32_t(k) : 0u));
+            rng.event = 0;
+            rng.open_event();
+            float xiU, xiV;
+            rng.uniform2(-1.f, 1.f, xiU, xiV);
+            dir[k] = primary_direction(p.cam, widthF, heightF, x, y, xiU, xiV);
+        }
+        uint32_t idxA, idxB;
+        closest_hit_camera2(fs, geom, p.n, eye, dir[0], dir[1], idxA, idxB, exactEvals, inside, inside && second);
         if (inside)
-            out[s] = idx < p.n ? uint16_t(idx) : uint16_t(kMissU16);
+        {
+            out[s] = idxA < p.n ? uint16_t(idxA) : uint16_t(kMissU16);
+            if (second)
+                out[s + 1] = idxB < p.n ? uint16_t(idxB) : uint16_t(kMissU16);
+        }
     }
     if (p.counters)
     {

@@ -285,8 +285,12 @@ def run_native_arm(args, wl):
     try:  # measured once per round under ncu --set full and committed; never measured inside a timed run
         t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(f"{args.workload}:{args.variant}")
         if t:
-            traffic = {"dram_bytes_per_launch": t["dram_bytes_read"] + t["dram_bytes_write"], "algorithmic_bytes_per_launch": W * H * 32,
-                       "source": t["capture"]}
+            per = t.get("samples_per_launch_in_capture")
+            chunk = (s1 - s0) / max(trace_launches // 2, 1) if trace_launches > 1 else (s1 - s0)
+            scale = (chunk / per) if (per and trace_launches > 1) else 1.0
+            traffic = {"dram_bytes_per_launch": (t["dram_bytes_read"] + t["dram_bytes_write"]) * scale,
+                       "algorithmic_bytes_per_launch": W * H * 32 + (W * H * chunk * 2 if trace_launches > 1 else 0),
+                       "kernel": t.get("kernel", "trace_megakernel"), "source": t["capture"]}
     except (OSError, ValueError):
         pass
     roofline = {

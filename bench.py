@@ -289,7 +289,7 @@ def run_native_arm(args, wl):
             chunk = (s1 - s0) / max(trace_launches // 2, 1) if trace_launches > 1 else (s1 - s0)
             scale = (chunk / per) if (per and trace_launches > 1) else 1.0
             traffic = {"dram_bytes_per_launch": (t["dram_bytes_read"] + t["dram_bytes_write"]) * scale,
-                       "algorithmic_bytes_per_launch": W * H * 32 + (W * H * chunk * 2 if trace_launches > 1 else 0),
+                       "algorithmic_bytes_per_launch": W * H * 32 + (W * H * chunk * 16 if trace_launches > 1 else 0),
                        "kernel": t.get("kernel", "trace_megakernel"), "source": t["capture"]}
     except (OSError, ValueError):
         pass

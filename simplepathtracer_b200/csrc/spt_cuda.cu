@@ -69,7 +69,7 @@ struct SptContext
     std::vector<double> hostGeom;        // cx, cy, cz, r per SLOT in binary64
     float camEye[3] = {NAN, NAN, NAN};
     float camEpsT = 0.f;
-    uint16_t *dFirstHits = nullptr;
+    float4 *dFirstHits = nullptr;
     size_t firstHitsBytes = 0;
     // context-owned accumulator of the progressive entry points
     float4 *dProgAccum = nullptr;
@@ -325,7 +325,7 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
         bool const streamed = (prm->flags & SPT_FLAG_STREAMED) ||
                               (geomBytes + pairBytes > SPT_RESIDENT_LIMIT_BYTES && !(prm->flags & SPT_FLAG_RESIDENT) && c->filter.nSlots > 0);
         bool const fitsResident = geomBytes + pairBytes <= SPT_RESIDENT_LIMIT_BYTES;
-        bool const split = !(prm->flags & SPT_FLAG_SINGLE_KERNEL) && (streamed || fitsResident) && c->n < 0xFFFFu && c->filter.nSlots > 0;
+        bool const split = !(prm->flags & SPT_FLAG_SINGLE_KERNEL) && (streamed || fitsResident) && c->filter.nSlots > 0;
         size_t const smem = streamed ? size_t(spt::kStreamSmemBytes) : geomBytes + pairBytes;
         if (split)
         {
@@ -340,20 +340,34 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             p.filterCam.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairsCam + c->filter.nSlots / 2);
             p.filterCam.epsTCam = c->camEpsT;
             size_t const pixels = size_t(segW) * segH;
-            size_t const cap = size_t(2) << 30; // staging buffer: at most 2 GiB
+            size_t const cap = size_t(8) << 30; // staging buffer: at most 8 GiB (64 spp of a 3840x2160 render)
             uint32_t const total = prm->sample_end - prm->sample_begin;
-            uint32_t chunk = uint32_t(std::max<size_t>(1, std::min<size_t>(total, cap / (pixels * sizeof(uint16_t)))));
+            uint32_t chunk = uint32_t(std::max<size_t>(1, std::min<size_t>(total, cap / (pixels * sizeof(float4)))));
             if (const char *knob = std::getenv("SPT_SPLIT_CHUNK")) // test knob: force several chunks on small renders
                 chunk = std::max<uint32_t>(1u, std::min<uint32_t>(chunk, uint32_t(std::atoi(knob))));
-            size_t const need = pixels * chunk * sizeof(uint16_t);
-            if (need > c->firstHitsBytes)
+            size_t const pad = 256; // the consumer prefetches four records past the one it reads
+            if (pixels * chunk * sizeof(float4) + pad > c->firstHitsBytes)
             {
                 SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
                 cudaFree(c->dFirstHits);
                 c->dFirstHits = nullptr;
                 c->firstHitsBytes = 0;
-                SPT_CUDA_CHECK(cudaMalloc(&c->dFirstHits, need));
-                c->firstHitsBytes = need;
+                // a device short of memory gets smaller chunks (more launches), not an error
+                for (;;)
+                {
+                    size_t const need = pixels * chunk * sizeof(float4) + pad;
+                    cudaError_t const ce = cudaMalloc(&c->dFirstHits, need);
+                    if (ce == cudaSuccess)
+                    {
+                        c->firstHitsBytes = need;
+                        break;
+                    }
+                    (void)cudaGetLastError();
+                    c->dFirstHits = nullptr;
+                    if (chunk == 1)
+                        return fail(SPT_ERR_CUDA, "cudaMalloc of the first-hit staging buffer failed", ce);
+                    chunk = (chunk + 1) / 2;
+                }
             }
             p.firstHits = c->dFirstHits;
             void (*primary)(const spt::TraceParams) = streamed ? spt::primary_hits_streamed : spt::primary_hits_kernel<2>;

@@ -41,13 +41,14 @@ struct TraceParams
     FilterScene filter;  // pre-filter records (global memory copies)
     float4 *accum;       // width*height (sum r, sum g, sum b, count), row y*width + x (not flipped)
     unsigned long long *counters; // [0] segments [1] samples [2] dropped [3] exact evaluations (may be null)
-    // split rendering (spt_split.cuh): first-hit sphere index of every camera sample of the launch,
-    // [(y - yBegin) * segW + (x - xBegin)][sample - sampleBegin], 0xFFFF = miss
-    uint16_t *firstHits;
+    // split rendering (spt_split.cuh): the camera segment of every sample of the launch as one float4 record
+    // (direction x, y, z, first-hit sphere index as raw bits; kMissIndex = miss),
+    // [(y - yBegin) * segW + (x - xBegin)][sample - sampleBegin]
+    float4 *firstHits;
     FilterScene filterCam; // pre-filter records specialised for the eye (camera form)
 };
 
-constexpr uint32_t kMissU16 = 0xFFFFu;
+constexpr uint32_t kMissIndex = 0xFFFFFFFFu;
 
 constexpr uint32_t kSpecularSafetyCap = 65536u; // the reference would overflow its stack long before
 

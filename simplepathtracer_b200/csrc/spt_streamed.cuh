@@ -137,6 +137,43 @@ __device__ __forceinline__ uint32_t streamed_closest_hit(const FilterScene &fs, 
     return minIndex;
 }
 
+// Two camera rays of one lane (the same pixel's next two samples) through each streamed chunk: the camera form is
+// bound by the shared-memory wavefronts of the record loads, which two rays share (spt_split.cuh).
+__device__ __forceinline__ void streamed_closest_hit_cam2(const FilterScene &fs, const float4 *geom, uint32_t n, V3 org, V3 dirA, V3 dirB,
+                                                          uint32_t &idxA, uint32_t &idxB, StreamRing &R, uint32_t &exactEvals, bool liveA,
+                                                          bool liveB, bool warpLive)
+{
+    constexpr uint32_t kAhead = kStages - 1u;
+    uint32_t const nChunks = (fs.nSlots + kChunkSlots - 1u) / kChunkSlots;
+    if (threadIdx.x == 0)
+        for (uint32_t c = 0; c < kAhead && c < nChunks; ++c)
+            stream_produce(fs, R.ring, R.fullBar, R.emptyBar, R.seq + c, c);
+    idxA = idxB = n;
+    float distA = FLT_MAX, distB = FLT_MAX;
+    float const odA = vdot(org, dirA), odB = vdot(org, dirB);
+    exact_big_spheres(fs, geom, dirA, org, odA, idxA, distA, exactEvals, liveA);
+    exact_big_spheres(fs, geom, dirB, org, odB, idxB, distB, exactEvals, liveB);
+    FilterRay const fa = make_filter_ray_cam(dirA, odA, fs.epsTCam), fb = make_filter_ray_cam(dirB, odB, fs.epsTCam);
+    for (uint32_t c = 0; c < nChunks; ++c)
+    {
+        if (threadIdx.x == 0 && c + kAhead < nChunks)
+            stream_produce(fs, R.ring, R.fullBar, R.emptyBar, R.seq + c + kAhead, c + kAhead);
+        uint32_t const buf = (R.seq + c) % kStages, use = (R.seq + c) / kStages;
+        mbar_wait(R.fullBar + buf, use & 1u);
+        if (warpLive)
+        {
+            const unsigned char *chunk = R.ring + buf * kChunkBytes;
+            uint32_t const span = min(kChunkSlots, fs.nSlots - c * kChunkSlots);
+            filter_span_cam2(reinterpret_cast<const FilterPair *>(chunk), reinterpret_cast<const uint32_t *>(chunk + kChunkRecordBytes), span,
+                             fa, fb, geom, n, org, dirA, odA, dirB, odB, idxA, distA, idxB, distB, exactEvals, liveA, liveB);
+        }
+        __syncwarp();
+        if ((threadIdx.x & 31u) == 0u)
+            mbar_arrive(R.emptyBar + buf);
+    }
+    R.seq += nChunks;
+}
+
 __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_streamed(const __grid_constant__ TraceParams p)
 {
     extern __shared__ __align__(128) unsigned char ring[];

@@ -281,26 +281,29 @@ def run_native_arm(args, wl):
     peak = max(peak_scalar, peak_packed)
     tests_per_launch = ctr["tests"] / args.steps
     achieved = FLOP_PER_TEST * tests_per_launch / (kernel_ms * 1e-3) / 1e12
-    traffic = None
+    traffic = traffic_detail = None
     try:  # measured once per round under ncu --set full and committed; never measured inside a timed run
         t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(f"{args.workload}:{args.variant}")
         if t:
             per = t.get("samples_per_launch_in_capture")
             chunk = (s1 - s0) / max(trace_launches // 2, 1) if trace_launches > 1 else (s1 - s0)
             scale = (chunk / per) if (per and trace_launches > 1) else 1.0
-            traffic = {"dram_bytes_per_launch": (t["dram_bytes_read"] + t["dram_bytes_write"]) * scale,
-                       "algorithmic_bytes_per_launch": W * H * 32 + (W * H * chunk * 16 if trace_launches > 1 else 0),
-                       "kernel": t.get("kernel", "trace_megakernel"), "source": t["capture"]}
+            traffic = (t["dram_bytes_read"] + t["dram_bytes_write"]) * scale  # bytes per launch of the dominant kernel
+            traffic_detail = {"kernel": t.get("kernel", "trace_megakernel"), "dram_bytes_per_launch": traffic,
+                              "algorithmic_bytes_per_launch": W * H * 32 + (W * H * chunk * 16 if trace_launches > 1 else 0),
+                              "source": t["capture"]}
+            if "primary_dram_bytes_write" in t and trace_launches > 1:
+                traffic_detail["primary_hits_dram_bytes_per_launch"] = (t["primary_dram_bytes_read"] + t["primary_dram_bytes_write"]) * scale
     except (OSError, ValueError):
         pass
     roofline = {
         "bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
-        "traffic": traffic,
+        "traffic": traffic, "traffic_detail": traffic_detail,
         "exact_evals_per_segment": ctr["exact"] / max(ctr["segments"], 1),
         "kernel": ("trace_" + args.variant) if (args.variant == "wavefront" or trace_launches == 1)
                   else f"primary_hits_kernel + trace_secondary ({trace_launches // 2} chunk(s) of samples)",
         "kernel_ms": kernel_ms, "kernel_share_of_step": kernel_ms / ms_step,
-        "algorithmic": f"{FLOP_PER_TEST} flop x {tests_per_launch:.4g} ray-sphere tests per launch "
+        "algorithmic": f"{FLOP_PER_TEST} flop x {tests_per_launch:.4g} ray-sphere tests per render (all launches of the step; kernel_ms is their sum) "
                        f"({ctr['segments'] / args.steps:.4g} ray segments x {scene.n} spheres; {ctr['segments'] / max(ctr['samples'], 1):.3f} segments/sample)",
         "peak_source": f"measured in this run: dependent-FMA chains on all SMs, scalar {peak_scalar:.1f} / packed f32x2 {peak_packed:.1f} TFLOP/s "
                        f"(MEASURED_PEAKS.json has no FP32 CUDA-core figure; nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4)",

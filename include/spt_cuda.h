@@ -84,10 +84,11 @@ enum {
     SPT_FLAG_CROSS_CHECK = 4u, /* spt_cuda_closest_hit only: run pre-filter AND strict loop, report 0xFFFFFFFF on disagreement */
     SPT_FLAG_STREAMED = 8u,    /* megakernel: stream the sphere list through a TMA chunk ring in shared memory even when it
                                   would fit whole (the default for lists above SPT_RESIDENT_LIMIT_BYTES) */
-    SPT_FLAG_SPLIT = 32u,      /* megakernel, resident lists (the DEFAULT there): trace the camera segment of every sample in a
-                                  separate, fully convergent kernel with the camera form of the pre-filter (first-hit indices
-                                  staged in HBM, 2 B per sample, in chunks of <= 2 GiB), then run the bounce loop on secondary
-                                  rays only.  Same bits as the single kernel. */
+    SPT_FLAG_SPLIT = 32u,      /* megakernel (the DEFAULT, resident and streamed lists): trace the camera segment of every sample
+                                  in a separate, fully convergent kernel with the camera form of the pre-filter (one float4 record
+                                  per sample -- direction + first-hit index -- staged in HBM in chunks of <= 8 GiB, smaller when
+                                  the device is short of memory), then run the bounce loop on secondary rays only.  Same bits as
+                                  the single kernel. */
     SPT_FLAG_SINGLE_KERNEL = 64u, /* megakernel: do not split; camera and secondary segments in one kernel */
     SPT_FLAG_RESIDENT = 16u    /* megakernel: keep the whole list resident in shared memory whenever it fits at all, even at
                                   the price of fewer CTAs per SM */

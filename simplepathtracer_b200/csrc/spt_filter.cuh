@@ -136,11 +136,10 @@ __device__ __forceinline__ FilterRay make_filter_ray(V3 dir, V3 org, float od, f
     return r;
 }
 
-// one record (two spheres): shifts two FAIL bits into `mask` (sign of min(v, tC))
-__device__ __forceinline__ void filter_pair(const FilterPair *__restrict__ rec, const FilterRay &r, uint32_t &mask)
+// one record (two spheres): shifts two FAIL bits into `mask` (sign of v)
+__device__ __forceinline__ void filter_pair_regs(ulonglong2 a, ulonglong2 b, const FilterRay &r, uint32_t &mask)
 {
-    ulonglong2 const a = *reinterpret_cast<const ulonglong2 *>(rec->cx); // (cx0,cx1) (cy0,cy1)
-    ulonglong2 const b = *reinterpret_cast<const ulonglong2 *>(rec->cz); // (cz0,cz1) (nk0,nk1)
+    // a = (cx0,cx1) (cy0,cy1), b = (cz0,cz1) (nk0,nk1)
     unsigned long long const tc = fma2(b.x, r.dz, fma2(a.y, r.dy, fma2(a.x, r.dx, r.nod)));
     unsigned long long const na = fma2(b.x, r.oz2, fma2(a.y, r.oy2, fma2(a.x, r.ox2, b.y)));
     unsigned long long const v = add2(fma2(tc, tc, na), r.noo);
@@ -155,6 +154,10 @@ __device__ __forceinline__ void filter_pair(const FilterPair *__restrict__ rec, 
     mask = __funnelshift_l(__float_as_uint(v0), mask, 1);
     mask = __funnelshift_l(__float_as_uint(v1), mask, 1);
 #endif
+}
+__device__ __forceinline__ void filter_pair(const FilterPair *__restrict__ rec, const FilterRay &r, uint32_t &mask)
+{
+    filter_pair_regs(*reinterpret_cast<const ulonglong2 *>(rec->cx), *reinterpret_cast<const ulonglong2 *>(rec->cz), r, mask);
 }
 
 // Camera rays all start at the eye E, so everything of v that does not involve the direction is a per-sphere constant of

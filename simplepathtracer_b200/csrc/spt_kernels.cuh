@@ -169,6 +169,49 @@ struct Lane
     uint32_t mode, bounce, specular, sample;
 };
 
+__device__ __forceinline__ void sts128(float4 *ptr, float4 v)
+{
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(smem_addr(ptr)), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 lds128(const float4 *ptr)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(smem_addr(ptr)) : "memory");
+    return v;
+}
+
+// Where the per-pixel running sum (sum r, g, b, sample count) lives while a kernel runs.  Either way the additions are
+// the same float operations in the same order.
+struct AccRegs // in the lane's registers (L.sum, L.count)
+{
+    Lane &L;
+    __device__ __forceinline__ void add(V3 v) const
+    {
+        L.sum = vadd(L.sum, v);
+        L.count = fadd(L.count, 1.f);
+    }
+    __device__ __forceinline__ void count_only() const { L.count = fadd(L.count, 1.f); }
+};
+struct AccShared // in a per-lane float4 slot of shared memory: touched once per finished sample, never held in registers
+{
+    float4 *slot;
+    __device__ __forceinline__ void add(V3 v) const
+    {
+        float4 a = lds128(slot);
+        a.x = fadd(a.x, v.x);
+        a.y = fadd(a.y, v.y);
+        a.z = fadd(a.z, v.z);
+        a.w = fadd(a.w, 1.f);
+        sts128(slot, a);
+    }
+    __device__ __forceinline__ void count_only() const
+    {
+        float4 a = lds128(slot);
+        a.w = fadd(a.w, 1.f);
+        sts128(slot, a);
+    }
+};
+
 // Warp-cooperative rejection sampling of the shell vector (Random.hpp:115-141).
 //
 // Each lane that needs a vector owns a counter-addressable stream (state0): attempt t is a pure function of
@@ -245,9 +288,9 @@ __device__ __forceinline__ V3 coop_shell(bool need, unsigned long long state0, S
 // (Collision.hpp:49-71), ONE rejection-sampled shell vector (Random.hpp:115-127; the loop whose trip count
 // varies most) and ONE final Normalize.  Only the few instructions that differ sit in per-material branches.
 // The arithmetic per lane is exactly the reference's.
-template <typename GeomPtr>
+template <typename GeomPtr, typename Acc>
 __device__ __forceinline__ void shade_step(const TraceParams &p, GeomPtr geom, Lane &L, uint32_t idx, uint32_t &dropped,
-                                           bool live, ShellSlots &slots)
+                                           bool live, ShellSlots &slots, Acc const acc)
 {
     bool const hit = idx < p.n;
     bool const inChain = L.mode == MODE_DIFFUSE;
@@ -267,9 +310,7 @@ __device__ __forceinline__ void shade_step(const TraceParams &p, GeomPtr geom, L
     if (live && !surface)
     {
         // terminal: end of SampleColorDiffuse's chain, or SampleColorSkybox (miss / Material::SKYBOX sphere)
-        V3 const add = inChain ? L.chain : sample_sky(p.cam, L.dir);
-        L.sum = vadd(L.sum, add);
-        L.count = fadd(L.count, 1.f);
+        acc.add(inChain ? L.chain : sample_sky(p.cam, L.dir));
         L.mode = MODE_NEW;
     }
 
@@ -332,10 +373,17 @@ __device__ __forceinline__ void shade_step(const TraceParams &p, GeomPtr geom, L
         }
         else if (L.specular >= kSpecularSafetyCap)
         {
-            L.count = fadd(L.count, 1.f);
+            acc.count_only();
             L.mode = MODE_NEW;
         }
     }
+}
+
+template <typename GeomPtr>
+__device__ __forceinline__ void shade_step(const TraceParams &p, GeomPtr geom, Lane &L, uint32_t idx, uint32_t &dropped,
+                                           bool live, ShellSlots &slots)
+{
+    shade_step(p, geom, L, idx, dropped, live, slots, AccRegs{L});
 }
 
 __device__ __forceinline__ void warp_counter_add(unsigned long long *ctr, unsigned long long v)

@@ -217,15 +217,30 @@ static void rng_uniform2(rng_t *r, float lo, float hi, float *u0, float *u1)
 
 /* GenerateUniformDistInsideSphereVector == GenerateNormalDistInsideSphereVector (Random.hpp:115-141):
  * redraw while Length < radius, i.e. KEEP points of the +-0.5 cube that lie OUTSIDE the 0.5 ball.
- * Counter mode: attempt k takes engine steps 2k (x, y) and 2k+1 (z): any attempt is addressable. */
+ * REFSEQ: three sequential draws per attempt, as the reference.
+ * COUNTER: attempt k is ONE engine step (word k of the event's stream) whose 64 mixed bits are cut into three
+ * fixed-point uniforms -- x = bits 63..43, y = bits 42..22 (21 bits each), z = bits 21..0 (22 bits) -- with
+ * canonical = k * 2^-21 (2^-22) and the reference's map canonical * (max - min) + min; all of it exact in float,
+ * so any attempt is addressable and nothing needs clamping. */
 static v4 rng_shell(rng_t *r)
 {
     float const radius = 0.5f;
     v4 res;
     do {
         float x, y, z;
-        rng_uniform2(r, -radius, radius, &x, &y);
-        z = rng_uniform1(r, -radius, radius);
+        if (r->counter_mode) {
+            uint32_t hi, lo;
+            spo_splitmix_pair(&r->state, &hi, &lo);
+            if (r->ctr)
+                r->ctr->rng_draws += 3;
+            uint32_t const kx = hi >> 11, ky = ((hi << 10) | (lo >> 22)) & 0x1FFFFFu, kz = lo & 0x3FFFFFu;
+            x = (float)kx * 4.76837158203125e-7f * (radius + radius) + -radius;
+            y = (float)ky * 4.76837158203125e-7f * (radius + radius) + -radius;
+            z = (float)kz * 2.384185791015625e-7f * (radius + radius) + -radius;
+        } else {
+            rng_uniform2(r, -radius, radius, &x, &y);
+            z = rng_uniform1(r, -radius, radius);
+        }
         res = v3(x, y, z);
     } while (vlen(res) < radius);
     return res;

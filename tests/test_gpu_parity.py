@@ -373,15 +373,15 @@ def test_config5_first_hit_and_prefilter(tracer, oracle, cam, scene_lattice):
     assert np.array_equal(got, oracle.closest_hit_many(scene_lattice, d, o))
 
 
-@pytest.mark.parametrize("which", ["c4", "c5"])
-def test_full_size_properties(tracer, cam, scene_metal_glass, scene_lattice, which):
+@pytest.mark.parametrize("which", ["c3", "c4", "c5"])
+def test_full_size_properties(tracer, cam, scene_random, scene_metal_glass, scene_lattice, which):
     """At BASELINE's full image sizes the oracle is out of reach; what must still hold: the three code paths
     (pre-filter megakernel, strict-loop megakernel, wavefront) produce identical accumulators, sample ranges
     compose, and count + dropped == spp."""
     import torch
 
-    scene, depth, spp = (scene_metal_glass, 50, 4) if which == "c4" else (scene_lattice, 16, 1)
-    w, h = 1920, 1080
+    scene, depth, spp = {"c3": (scene_random, 50, 4), "c4": (scene_metal_glass, 50, 4), "c5": (scene_lattice, 16, 1)}[which]
+    w, h = (3840, 2160) if which == "c3" else (1920, 1080)
     tracer.set_scene(scene)
     outs = []
     for variant, flags in ((spt.MEGAKERNEL, 0), (spt.MEGAKERNEL, spt.FLAG_SINGLE_KERNEL), (spt.MEGAKERNEL, spt.FLAG_STREAMED),
@@ -398,13 +398,12 @@ def test_full_size_properties(tracer, cam, scene_metal_glass, scene_lattice, whi
         assert torch.equal(outs[0], other)
     cnt = outs[0][..., 3]
     assert float(cnt.max()) == spp and float(cnt.min()) >= 0
-    if spp >= 2:  # sample ranges [0, k) + [k, spp) land on the same sums when added in order on the device
+    if spp >= 2:  # sample ranges [0, k) + [k, spp): the running sums continue from the accumulator, so the bits are the same
         acc = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
         tracer.accumulate(cam, w, h, 0, 1, depth, acc, pass_cap=10, seed=8)
         tracer.accumulate(cam, w, h, 1, spp, depth, acc, pass_cap=10, seed=8)
         torch.cuda.synchronize()
-        assert torch.equal(acc[..., 3], cnt)
-        assert torch.allclose(acc, outs[0], rtol=1e-6, atol=1e-3)
+        assert torch.equal(acc, outs[0])
     tracer.set_stream(None)
 
 

@@ -340,7 +340,9 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             p.filterCam.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairsCam + c->filter.nSlots / 2);
             p.filterCam.epsTCam = c->camEpsT;
             size_t const pixels = size_t(segW) * segH;
-            size_t const cap = size_t(8) << 30; // staging buffer: at most 8 GiB (64 spp of a 3840x2160 render)
+            size_t cap = size_t(8) << 30; // staging buffer: at most 8 GiB (64 spp of a 3840x2160 render)
+            if (const char *knob = std::getenv("SPT_SPLIT_CAP_MIB")) // experiments: staging budget in MiB
+                cap = std::max<size_t>(size_t(1) << 20, size_t(std::atoll(knob)) << 20);
             uint32_t const total = prm->sample_end - prm->sample_begin;
             uint32_t chunk = uint32_t(std::max<size_t>(1, std::min<size_t>(total, cap / (pixels * sizeof(float4)))));
             if (const char *knob = std::getenv("SPT_SPLIT_CHUNK")) // test knob: force several chunks on small renders

@@ -18,7 +18,13 @@ namespace spt
 
 // Block = 8 warps; a warp covers an 8x4 pixel tile (coherent rays), the block a 32x8 tile.
 constexpr int kWarpW = 8, kWarpH = 4;
-constexpr int kBlockWarpsX = 4, kBlockWarpsY = 2;
+#ifndef SPT_BLOCK_WARPS_X
+#define SPT_BLOCK_WARPS_X 4
+#endif
+#ifndef SPT_BLOCK_WARPS_Y
+#define SPT_BLOCK_WARPS_Y 2
+#endif
+constexpr int kBlockWarpsX = SPT_BLOCK_WARPS_X, kBlockWarpsY = SPT_BLOCK_WARPS_Y;
 constexpr int kTileW = kWarpW * kBlockWarpsX; // 32
 constexpr int kTileH = kWarpH * kBlockWarpsY; // 8
 constexpr int kBlockThreads = kTileW * kTileH; // 256
@@ -288,31 +294,51 @@ __device__ __forceinline__ V3 coop_shell(bool need, unsigned long long state0, S
 // (Collision.hpp:49-71), ONE rejection-sampled shell vector (Random.hpp:115-127; the loop whose trip count
 // varies most) and ONE final Normalize.  Only the few instructions that differ sit in per-material branches.
 // The arithmetic per lane is exactly the reference's.
-template <typename GeomPtr, typename Acc>
-__device__ __forceinline__ void shade_step(const TraceParams &p, GeomPtr geom, Lane &L, uint32_t idx, uint32_t &dropped,
-                                           bool live, ShellSlots &slots, Acc const acc)
+// What shade_step's first half decides about a lane: which handler (if any) shades a surface next.
+struct SurfaceKind
+{
+    bool chainGoes, isDiffuse, isMirror, isGlass;
+    __device__ __forceinline__ bool any() const { return chainGoes || isDiffuse || isMirror || isGlass; }
+};
+__device__ __forceinline__ SurfaceKind surface_none() { return SurfaceKind{false, false, false, false}; }
+// the handler TraceAndSampleColor's switch picks for material m (SingleThreadPathTracer.hpp:98-108)
+__device__ __forceinline__ SurfaceKind surface_of_material(uint32_t m) { return SurfaceKind{false, m == 3u, m == 1u, m == 2u}; }
+
+// First half of shade_step: material dispatch / chain control, and the TERMINAL cases (end of SampleColorDiffuse's chain,
+// SampleColorSkybox on a miss or a Material::SKYBOX sphere), which add the sample to the pixel and leave the lane in MODE_NEW.
+template <typename Acc>
+__device__ __forceinline__ SurfaceKind shade_classify(const TraceParams &p, Lane &L, uint32_t idx, bool live, Acc const acc)
 {
     bool const hit = idx < p.n;
     bool const inChain = L.mode == MODE_DIFFUSE;
     uint32_t const m = (live && hit && !inChain) ? uint32_t(__ldg(p.mat + idx)) : 0u;
     // while (--bounceCount && sphereIndex < g_sphereNumber) (SingleThreadPathTracer.hpp:28): the decrement
     // happens whether or not the sphere test is reached
-    bool chainGoes = false;
+    SurfaceKind k = surface_none();
     if (live && inChain)
     {
         --L.bounce;
-        chainGoes = L.bounce != 0u && hit;
+        k.chainGoes = L.bounce != 0u && hit;
     }
-    bool const isDiffuse = live && !inChain && m == 3u, isMirror = live && !inChain && m == 1u,
-               isGlass = live && !inChain && m == 2u;
-    bool const surface = chainGoes || isDiffuse || isMirror || isGlass;
-
-    if (live && !surface)
+    k.isDiffuse = live && !inChain && m == 3u;
+    k.isMirror = live && !inChain && m == 1u;
+    k.isGlass = live && !inChain && m == 2u;
+    if (live && !k.any())
     {
         // terminal: end of SampleColorDiffuse's chain, or SampleColorSkybox (miss / Material::SKYBOX sphere)
         acc.add(inChain ? L.chain : sample_sky(p.cam, L.dir));
         L.mode = MODE_NEW;
     }
+    return k;
+}
+
+// Second half of shade_step: the surface handlers of the lanes `k` names, set up the next segment.
+template <typename GeomPtr, typename Acc>
+__device__ __forceinline__ void shade_surface(const TraceParams &p, GeomPtr geom, Lane &L, uint32_t idx, SurfaceKind const k,
+                                              uint32_t &dropped, ShellSlots &slots, Acc const acc)
+{
+    bool const chainGoes = k.chainGoes, isDiffuse = k.isDiffuse, isMirror = k.isMirror, isGlass = k.isGlass;
+    bool const surface = k.any();
 
     // ---- shared site 1: contact point and normal (every handler starts with these two calls) ----
     float4 s = make_float4(0.f, 0.f, 0.f, 1.f);
@@ -377,6 +403,14 @@ __device__ __forceinline__ void shade_step(const TraceParams &p, GeomPtr geom, L
             L.mode = MODE_NEW;
         }
     }
+}
+
+template <typename GeomPtr, typename Acc>
+__device__ __forceinline__ void shade_step(const TraceParams &p, GeomPtr geom, Lane &L, uint32_t idx, uint32_t &dropped,
+                                           bool live, ShellSlots &slots, Acc const acc)
+{
+    SurfaceKind const k = shade_classify(p, L, idx, live, acc);
+    shade_surface(p, geom, L, idx, k, dropped, slots, acc);
 }
 
 template <typename GeomPtr>

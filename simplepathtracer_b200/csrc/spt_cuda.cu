@@ -340,7 +340,18 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             p.filterCam.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairsCam + c->filter.nSlots / 2);
             p.filterCam.epsTCam = c->camEpsT;
             size_t const pixels = size_t(segW) * segH;
-            size_t cap = size_t(8) << 30; // staging buffer: at most 8 GiB (64 spp of a 3840x2160 render)
+            // Staging budget.  A lane owns its pixel for a whole chunk and the warp waits for its slowest lane, so longer
+            // chunks waste fewer lane-iterations (config 3 on B200: 8 / 16 / 32 / 64 GiB = 5 815 / 5 893 / 5 963 / 6 006
+            // Msamples/s, profiles/r1_ab_chunk_and_cta_shape.txt): up to 64 GiB (512 spp of a 3840x2160 render), but never
+            // more than 45 % of what the device has free.
+            size_t cap = size_t(64) << 30;
+            {
+                size_t freeB = 0, totalB = 0;
+                if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess)
+                    cap = std::min(cap, (freeB + c->firstHitsBytes) / 100 * 45);
+                else
+                    (void)cudaGetLastError();
+            }
             if (const char *knob = std::getenv("SPT_SPLIT_CAP_MIB")) // experiments: staging budget in MiB
                 cap = std::max<size_t>(size_t(1) << 20, size_t(std::atoll(knob)) << 20);
             uint32_t const total = prm->sample_end - prm->sample_begin;
@@ -372,16 +383,21 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
                 }
             }
             p.firstHits = c->dFirstHits;
-            void (*primary)(const spt::TraceParams) = streamed ? spt::primary_hits_streamed : spt::primary_hits_kernel<2>;
-            void (*secondary)(const spt::TraceParams) = streamed ? spt::trace_secondary_streamed : spt::trace_secondary<2>;
+            void (*primary)(const spt::TraceParams) = streamed ? spt::primary_hits_streamed : spt::primary_hits_kernel<2, spt::SplitShape>;
+            void (*secondary)(const spt::TraceParams) = streamed ? spt::trace_secondary_streamed : spt::trace_secondary<2, spt::SplitShape>;
+            // the resident kernels run smaller CTAs than the rest (spt_split.cuh, SplitShape)
+            dim3 const sGrid = streamed ? grid
+                                        : dim3((segW + spt::SplitShape::kTileW - 1) / spt::SplitShape::kTileW,
+                                               (segH + spt::SplitShape::kTileH - 1) / spt::SplitShape::kTileH);
+            dim3 const sBlock(streamed ? spt::kBlockThreads : spt::SplitShape::kThreads);
             SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
             SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
             for (uint32_t s0 = prm->sample_begin; s0 < prm->sample_end; s0 += chunk)
             {
                 p.sampleBegin = s0;
                 p.sampleEnd = std::min(prm->sample_end, s0 + chunk);
-                primary<<<grid, block, smem, c->stream>>>(p);
-                secondary<<<grid, block, smem, c->stream>>>(p);
+                primary<<<sGrid, sBlock, smem, c->stream>>>(p);
+                secondary<<<sGrid, sBlock, smem, c->stream>>>(p);
                 c->timing.launches += 2;
             }
             c->timing.launches -= 1; // the common tail below counts one

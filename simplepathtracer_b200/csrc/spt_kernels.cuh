@@ -28,6 +28,16 @@ constexpr int kBlockWarpsX = SPT_BLOCK_WARPS_X, kBlockWarpsY = SPT_BLOCK_WARPS_Y
 constexpr int kTileW = kWarpW * kBlockWarpsX; // 32
 constexpr int kTileH = kWarpH * kBlockWarpsY; // 8
 constexpr int kBlockThreads = kTileW * kTileH; // 256
+// CTA shape in warps (each warp an 8x4 pixel tile).  The resident split kernels (spt_split.cuh) take it as a template
+// parameter; every other kernel uses the default above.
+template <int WX, int WY>
+struct BlockShape
+{
+    static constexpr int kWarpsX = WX, kWarpsY = WY;
+    static constexpr int kTileW = kWarpW * WX, kTileH = kWarpH * WY;
+    static constexpr int kThreads = kTileW * kTileH;
+};
+using DefaultShape = BlockShape<kBlockWarpsX, kBlockWarpsY>;
 #ifndef SPT_MIN_BLOCKS
 #define SPT_MIN_BLOCKS 4 // resident blocks per SM the register allocation aims at
 #endif
@@ -429,13 +439,14 @@ __device__ __forceinline__ void warp_counter_add(unsigned long long *ctr, unsign
 }
 
 // pixel of this lane inside the segment: warps tile 8x4, blocks 32x8
+template <typename S = DefaultShape>
 __device__ __forceinline__ void lane_pixel(const TraceParams &p, uint32_t &x, uint32_t &y, bool &inside)
 {
     uint32_t const lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t const lx = (lane & (kWarpW - 1)) + (warp % kBlockWarpsX) * kWarpW;
-    uint32_t const ly = (lane / kWarpW) + (warp / kBlockWarpsX) * kWarpH;
-    x = p.xBegin + blockIdx.x * kTileW + lx;
-    y = p.yBegin + blockIdx.y * kTileH + ly;
+    uint32_t const lx = (lane & (kWarpW - 1)) + (warp % S::kWarpsX) * kWarpW;
+    uint32_t const ly = (lane / kWarpW) + (warp / S::kWarpsX) * kWarpH;
+    x = p.xBegin + blockIdx.x * S::kTileW + lx;
+    y = p.yBegin + blockIdx.y * S::kTileH + ly;
     inside = x < p.xEnd && y < p.yEnd;
 }
 

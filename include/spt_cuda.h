@@ -86,7 +86,7 @@ enum {
                                   would fit whole (the default for lists above SPT_RESIDENT_LIMIT_BYTES) */
     SPT_FLAG_SPLIT = 32u,      /* megakernel (the DEFAULT, resident and streamed lists): trace the camera segment of every sample
                                   in a separate, fully convergent kernel with the camera form of the pre-filter (one float4 record
-                                  per sample -- direction + first-hit index -- staged in HBM in chunks of <= 8 GiB, smaller when
+                                  per sample -- direction + first-hit index -- staged in HBM in chunks of <= 64 GiB, smaller when
                                   the device is short of memory), then run the bounce loop on secondary rays only.  Same bits as
                                   the single kernel. */
     SPT_FLAG_SINGLE_KERNEL = 64u, /* megakernel: do not split; camera and secondary segments in one kernel */

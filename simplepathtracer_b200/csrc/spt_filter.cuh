@@ -198,6 +198,36 @@ __device__ __forceinline__ FilterRay make_filter_ray_cam(V3 dir, float od, float
 // only the quads (4 records) that exist.  The masks of up to kSuperWords words are parked in registers and
 // the divergent candidate loop runs once per super-word, so lanes with candidates in different words of the
 // same super-word are served in the same trips.
+// exact sequence on the candidates parked in c0..c3: c_k holds the mask of word (wEnd - 1 - k) of the span.  Leaves all
+// four masks zero.  Lanes without candidates idle here (the only divergent part of the closest hit).
+template <typename GeomPtr>
+__device__ __forceinline__ void resolve_candidates(uint32_t &c0, uint32_t &c1, uint32_t &c2, uint32_t &c3, uint32_t wEnd, const uint32_t *slotIdx,
+                                                   GeomPtr geom, uint32_t n, V3 dir, V3 org, float od, uint32_t &minIndex,
+                                                   float &minDistanceSq, uint32_t &exactEvals)
+{
+    for (;;)
+    {
+        uint32_t k, bits;
+        if (c0) { k = 0; bits = c0; }
+        else if (c1) { k = 1; bits = c1; }
+        else if (c2) { k = 2; bits = c2; }
+        else if (c3) { k = 3; bits = c3; }
+        else break;
+        uint32_t const j = __clz(bits);
+        uint32_t const cleared = bits & ~(0x80000000u >> j);
+        if (k == 0) c0 = cleared;
+        else if (k == 1) c1 = cleared;
+        else if (k == 2) c2 = cleared;
+        else c3 = cleared;
+        uint32_t const i = slotIdx[(wEnd - 1u - k) * kWordSpheres + j];
+        if (i < n) // padding records can only show up for NaN rays
+        {
+            exact_sphere<false>(geom[i], i, dir, org, od, minIndex, minDistanceSq);
+            ++exactEvals;
+        }
+    }
+}
+
 template <bool CAM = false, typename GeomPtr>
 __device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_t *slotIdx, uint32_t spanSlots, const FilterRay &fr,
                                             GeomPtr geom, uint32_t n, V3 dir, V3 org, float od, uint32_t &minIndex,
@@ -205,12 +235,14 @@ __device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_
 {
     uint32_t const nWords = (spanSlots + kWordSpheres - 1u) / kWordSpheres;
     uint32_t const tailQuads = (spanSlots - (nWords - 1u) * kWordSpheres) / kQuadSpheres; // 1..4 quads in the last word
-    uint32_t c0 = 0u, c1 = 0u, c2 = 0u, c3 = 0u; // candidate masks of the current super-word
+    uint32_t const nFull = tailQuads == kWordSpheres / kQuadSpheres ? nWords : nWords - 1u; // words with all 16 records
+    // candidate masks of the last kSuperWords words filtered, newest in c0 (a shift register: no per-word selects)
+    uint32_t c0 = 0u, c1 = 0u, c2 = 0u, c3 = 0u;
 #pragma unroll 1
-    for (uint32_t w = 0; w < nWords; ++w) // everything about w is warp-uniform
+    for (uint32_t w = 0; w < nWords;) // everything about w is warp-uniform
     {
         uint32_t mask = 0xFFFFFFFFu; // all "fail"
-        if (w + 1u < nWords || tailQuads == kWordSpheres / kQuadSpheres)
+        if (w < nFull)
         {
 #pragma unroll
             for (uint32_t pp = 0; pp < kWordSpheres / 2; ++pp)
@@ -222,7 +254,7 @@ __device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_
             }
             rec += kWordSpheres / 2;
         }
-        else
+        else // the partial last word: only the quads (4 records) that exist
         {
 #pragma unroll 1
             for (uint32_t q = 0; q < tailQuads; ++q)
@@ -240,37 +272,13 @@ __device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_
             uint32_t const sh = kWordSpheres - kQuadSpheres * tailQuads; // 8, 16 or 24 missing slots: fail bits
             mask = (mask << sh) | ((1u << sh) - 1u);
         }
-        uint32_t const cw = live ? ~mask : 0u; // bit (31 - j) set <=> slot j of the word is a candidate
-        uint32_t const k = w & (kSuperWords - 1u);
-        if (k == 0u) c0 = cw;
-        else if (k == 1u) c1 = cw;
-        else if (k == 2u) c2 = cw;
-        else c3 = cw;
-        if (k != kSuperWords - 1u && w + 1u != nWords)
-            continue;
-        // exact sequence on this lane's candidates; lanes without any idle here (the only divergent part)
-        uint32_t const w0 = w - k;
-        for (;;)
-        {
-            uint32_t ww, bits;
-            if (c0) { ww = 0; bits = c0; }
-            else if (c1) { ww = 1; bits = c1; }
-            else if (c2) { ww = 2; bits = c2; }
-            else if (c3) { ww = 3; bits = c3; }
-            else break;
-            uint32_t const j = __clz(bits);
-            uint32_t const cleared = bits & ~(0x80000000u >> j);
-            if (ww == 0) c0 = cleared;
-            else if (ww == 1) c1 = cleared;
-            else if (ww == 2) c2 = cleared;
-            else c3 = cleared;
-            uint32_t const i = slotIdx[(w0 + ww) * kWordSpheres + j];
-            if (i < n) // padding records can only show up for NaN rays
-            {
-                exact_sphere<false>(geom[i], i, dir, org, od, minIndex, minDistanceSq);
-                ++exactEvals;
-            }
-        }
+        c3 = c2;
+        c2 = c1;
+        c1 = c0;
+        c0 = live ? ~mask : 0u; // bit (31 - j) set <=> slot j of the word is a candidate
+        ++w;
+        if ((w & (kSuperWords - 1u)) == 0u || w == nWords)
+            resolve_candidates(c0, c1, c2, c3, w, slotIdx, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals);
     }
 }
 
@@ -330,35 +338,6 @@ __device__ __forceinline__ void filter_pair_cam2(const FilterPair *__restrict__ 
     maskB = __funnelshift_l(__float_as_uint(b1), maskB, 1);
 }
 
-// exact sequence on the candidates parked in c0..c3 (words w0..w0+3 of the span)
-template <typename GeomPtr>
-__device__ __forceinline__ void resolve_candidates(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t w0, const uint32_t *slotIdx,
-                                                   GeomPtr geom, uint32_t n, V3 dir, V3 org, float od, uint32_t &minIndex,
-                                                   float &minDistanceSq, uint32_t &exactEvals)
-{
-    for (;;)
-    {
-        uint32_t ww, bits;
-        if (c0) { ww = 0; bits = c0; }
-        else if (c1) { ww = 1; bits = c1; }
-        else if (c2) { ww = 2; bits = c2; }
-        else if (c3) { ww = 3; bits = c3; }
-        else break;
-        uint32_t const j = __clz(bits);
-        uint32_t const cleared = bits & ~(0x80000000u >> j);
-        if (ww == 0) c0 = cleared;
-        else if (ww == 1) c1 = cleared;
-        else if (ww == 2) c2 = cleared;
-        else c3 = cleared;
-        uint32_t const i = slotIdx[(w0 + ww) * kWordSpheres + j];
-        if (i < n)
-        {
-            exact_sphere<false>(geom[i], i, dir, org, od, minIndex, minDistanceSq);
-            ++exactEvals;
-        }
-    }
-}
-
 // filter_span for two camera rays (A, B) sharing the origin; liveA / liveB as `live` in filter_span
 template <typename GeomPtr>
 __device__ __forceinline__ void filter_span_cam2(const FilterPair *rec, const uint32_t *slotIdx, uint32_t spanSlots, const FilterRay &fa,
@@ -368,12 +347,13 @@ __device__ __forceinline__ void filter_span_cam2(const FilterPair *rec, const ui
 {
     uint32_t const nWords = (spanSlots + kWordSpheres - 1u) / kWordSpheres;
     uint32_t const tailQuads = (spanSlots - (nWords - 1u) * kWordSpheres) / kQuadSpheres;
+    uint32_t const nFull = tailQuads == kWordSpheres / kQuadSpheres ? nWords : nWords - 1u;
     uint32_t a0 = 0u, a1 = 0u, a2 = 0u, a3 = 0u, b0 = 0u, b1 = 0u, b2 = 0u, b3 = 0u;
 #pragma unroll 1
-    for (uint32_t w = 0; w < nWords; ++w)
+    for (uint32_t w = 0; w < nWords;)
     {
         uint32_t maskA = 0xFFFFFFFFu, maskB = 0xFFFFFFFFu;
-        if (w + 1u < nWords || tailQuads == kWordSpheres / kQuadSpheres)
+        if (w < nFull)
         {
 #pragma unroll
             for (uint32_t pp = 0; pp < kWordSpheres / 2; ++pp)
@@ -394,17 +374,14 @@ __device__ __forceinline__ void filter_span_cam2(const FilterPair *rec, const ui
             maskA = (maskA << sh) | ((1u << sh) - 1u);
             maskB = (maskB << sh) | ((1u << sh) - 1u);
         }
-        uint32_t const ca = liveA ? ~maskA : 0u, cb = liveB ? ~maskB : 0u;
-        uint32_t const k = w & (kSuperWords - 1u);
-        if (k == 0u) { a0 = ca; b0 = cb; }
-        else if (k == 1u) { a1 = ca; b1 = cb; }
-        else if (k == 2u) { a2 = ca; b2 = cb; }
-        else { a3 = ca; b3 = cb; }
-        if (k != kSuperWords - 1u && w + 1u != nWords)
-            continue;
-        resolve_candidates(a0, a1, a2, a3, w - k, slotIdx, geom, n, dirA, org, odA, minA, distA, exactEvals);
-        resolve_candidates(b0, b1, b2, b3, w - k, slotIdx, geom, n, dirB, org, odB, minB, distB, exactEvals);
-        a0 = a1 = a2 = a3 = b0 = b1 = b2 = b3 = 0u;
+        a3 = a2; a2 = a1; a1 = a0; a0 = liveA ? ~maskA : 0u;
+        b3 = b2; b2 = b1; b1 = b0; b0 = liveB ? ~maskB : 0u;
+        ++w;
+        if ((w & (kSuperWords - 1u)) == 0u || w == nWords)
+        {
+            resolve_candidates(a0, a1, a2, a3, w, slotIdx, geom, n, dirA, org, odA, minA, distA, exactEvals);
+            resolve_candidates(b0, b1, b2, b3, w, slotIdx, geom, n, dirB, org, odB, minB, distB, exactEvals);
+        }
     }
 }
 

@@ -5,8 +5,8 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 ... bench.py --gpus N ...
 
 One "step" = one complete render of the workload (every pixel, every sample, reduce across GPUs,
-normalise + gamma + pack RGB8).  Samples are range-sharded across ranks; the one
-collective is an NCCL sum-reduce of the float4 accumulators to rank 0.
+normalise + gamma + pack RGB8).  Ranks share a render by interleaved 8-row bands of pixels (or by sample ranges,
+--partition samples); the one collective is an NCCL sum-reduce of the float4 accumulators to rank 0.
 
   value    : W*H*spp / step time with scene and accumulators resident in HBM (CUDA events, max over ranks)
   e2e      : same metric through the host-buffer C-ABI path: scene upload (H2D) + render + RGB8 image back (D2H)
@@ -198,8 +198,14 @@ def run_native_arm(args, wl):
     W, H, spp, depth = wl["width"], wl["height"], args.spp or wl["spp"], wl["depth"]
     from simplepathtracer_b200 import sharding
 
-    # sample-range sharding: rank r renders samples [s0, s1) of every pixel
-    s0, s1 = sharding.sample_range(rank, world, spp)
+    # pixel partition (default): rank r renders every sample of the 8-row bands b with b % world == r -- full-length
+    # chunks of samples on every rank, disjoint pixels; --partition samples: rank r renders samples [s0, s1) of every pixel
+    if args.partition == "bands":
+        s0, s1 = 0, spp
+        bands = sharding.band_params(rank, world) if world > 1 else None
+    else:
+        s0, s1 = sharding.sample_range(rank, world, spp)
+        bands = None
 
     pt = spt.PathTracer(local)
     # one explicit stream for torch fills, our kernels and the timing events
@@ -218,7 +224,8 @@ def run_native_arm(args, wl):
         accum.zero_()
         if ev:
             ev[0].record()
-        pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, flags=spt.FLAG_COUNTERS | args.flags, variant=variant)
+        pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, flags=spt.FLAG_COUNTERS | args.flags, variant=variant,
+                      bands=bands)
         if ev:
             ev[1].record()
         launches[0] += 1
@@ -288,9 +295,11 @@ def run_native_arm(args, wl):
             per = t.get("samples_per_launch_in_capture")
             chunk = (s1 - s0) / max(trace_launches // 2, 1) if trace_launches > 1 else (s1 - s0)
             scale = (chunk / per) if (per and trace_launches > 1) else 1.0
+            share = (1.0 / world) if bands else 1.0  # this rank's share of the pixels
+            scale *= share
             traffic = (t["dram_bytes_read"] + t["dram_bytes_write"]) * scale  # bytes per launch of the dominant kernel
             traffic_detail = {"kernel": t.get("kernel", "trace_megakernel"), "dram_bytes_per_launch": traffic,
-                              "algorithmic_bytes_per_launch": W * H * 32 + (W * H * chunk * 16 if trace_launches > 1 else 0),
+                              "algorithmic_bytes_per_launch": (W * H * 32 + (W * H * chunk * 16 if trace_launches > 1 else 0)) * share,
                               "source": t["capture"]}
             if "primary_dram_bytes_write" in t and trace_launches > 1:
                 traffic_detail["primary_hits_dram_bytes_per_launch"] = (t["primary_dram_bytes_read"] + t["primary_dram_bytes_write"]) * scale
@@ -319,7 +328,7 @@ def run_native_arm(args, wl):
             pt.render(cam, W, H, spp, depth, pass_cap=PASS_CAP, seed=SEED, rgb8=rgb_host.numpy(), variant=variant, flags=args.flags)  # D2H inside
         else:
             accum.zero_()
-            pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, variant=variant, flags=args.flags)
+            pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, variant=variant, flags=args.flags, bands=bands)
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
                 pt.resolve(accum, W, H, rgb_dev)
@@ -349,7 +358,8 @@ def run_native_arm(args, wl):
             "data": "synthetic",
             "config": {"workload": f"{args.workload}: {wl['desc']}" + (f" [spp overridden to {spp}]" if args.spp else ""),
                        "spheres": scene.n, "width": W, "height": H, "spp": spp, "depth": depth, "pass_cap": PASS_CAP,
-                       "variant": args.variant, "sharding": f"sample ranges over {world} rank(s) + NCCL sum-reduce of float4 accumulators",
+                       "variant": args.variant, "sharding": (f"interleaved 8-row bands of pixels over {world} rank(s)" if args.partition == "bands" else f"sample ranges over {world} rank(s)")
+                                   + " + NCCL sum-reduce of float4 accumulators",
                        "l2": f"float4 accumulator {W * H * 16 / 1e6:.1f} MB per step vs 126 MB L2; kernel is compute-bound, scene staged in shared memory"},
             "e2e": e2e, "gpu_launches": launches_native, "roofline": roofline, "cpu_baseline": cpu, "clocks": clock_info,
             "device": info["name"], "sm_count": info["sm_count"], "counters": ctr,
@@ -390,6 +400,7 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (debug only; invalidates the headline)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--variant", default="megakernel", choices=["megakernel", "wavefront"])
+    ap.add_argument("--partition", default="bands", choices=["bands", "samples"], help="how N > 1 ranks share a render (sharding.py)")
     ap.add_argument("--flags", type=int, default=0, help="extra SPT_FLAG_* bits for the trace launches (experiments)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]

@@ -107,7 +107,14 @@ typedef struct SptParams {
     uint64_t seed;                     /* counter-based RNG seed (replaces Random.hpp:88-89's clock seed) */
     uint32_t variant;                  /* SPT_VARIANT_* */
     uint32_t flags;                    /* SPT_FLAG_* */
+    uint32_t band_count, band_index;   /* band_count <= 1: every row of the segment.  Otherwise the segment is cut into
+                                          bands of SPT_BAND_ROWS rows (band b = rows [yBegin + 8 b, yBegin + 8 b + 8)) and
+                                          the call renders only the bands with b % band_count == band_index: the
+                                          interleaved pixel partition for several GPUs (disjoint pixels, so summing the
+                                          per-GPU accumulators reproduces the single-GPU bits).  The reference's analogue
+                                          is RenderImageParallelMain's static tile grid (Renderer.hpp:264-274). */
 } SptParams;
+#define SPT_BAND_ROWS 8u
 
 typedef struct SptCounters {
     uint64_t segments; /* closest-hit calls (one per ray segment) */

@@ -139,6 +139,8 @@ class _CParams(C.Structure):
         ("seed", C.c_uint64),
         ("variant", C.c_uint32),
         ("flags", C.c_uint32),
+        ("band_count", C.c_uint32),
+        ("band_index", C.c_uint32),
     ]
 
 
@@ -308,8 +310,9 @@ class PathTracer:
         self._check(self.L.spt_cuda_set_scene(self.h, C.byref(cs)))
         self.scene = sc
 
-    def _params(self, width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags) -> _CParams:
-        return _CParams(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags)
+    def _params(self, width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags, bands=None) -> _CParams:
+        count, index = bands if bands else (0, 0)  # (band_count, band_index): interleaved 8-row bands, include/spt_cuda.h
+        return _CParams(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags, count, index)
 
     def render(self, cam, width, height, spp, depth, pass_cap=0, seed=1, seg=None, sample_begin=0, variant=MEGAKERNEL,
                flags=0, rgb8: Optional[np.ndarray] = None, want_accum: bool = False):
@@ -324,10 +327,11 @@ class PathTracer:
         return rgb8, accum
 
     def accumulate(self, cam, width, height, sample_begin, sample_end, depth, d_accum, pass_cap=0, seed=1, seg=None,
-                   variant=MEGAKERNEL, flags=0):
-        """Adds samples [sample_begin, sample_end) into a DEVICE float4 accumulator (async)."""
+                   variant=MEGAKERNEL, flags=0, bands=None):
+        """Adds samples [sample_begin, sample_end) into a DEVICE float4 accumulator (async).  bands = (count, index)
+        restricts the call to the 8-row bands b of the segment with b % count == index."""
         cm = _ccam(Camera.of(cam))
-        p = self._params(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags)
+        p = self._params(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags, bands)
         self._check(self.L.spt_cuda_accumulate(self.h, C.byref(cm), C.byref(p), _seg(seg, width, height), C.c_void_p(_devptr(d_accum))))
 
     def resolve(self, d_accum, width, height, d_rgb8, seg=None):
@@ -339,10 +343,11 @@ class PathTracer:
         self._check(self.L.spt_cuda_progressive_begin(self.h, width, height))
         self._prog = (width, height)
 
-    def progressive_add(self, cam, sample_begin, sample_end, depth, pass_cap=0, seed=1, seg=None, variant=MEGAKERNEL, flags=0):
+    def progressive_add(self, cam, sample_begin, sample_end, depth, pass_cap=0, seed=1, seg=None, variant=MEGAKERNEL, flags=0,
+                        bands=None):
         width, height = self._prog
         cm = _ccam(Camera.of(cam))
-        p = self._params(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags)
+        p = self._params(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags, bands)
         self._check(self.L.spt_cuda_progressive_add(self.h, C.byref(cm), C.byref(p), _seg(seg, width, height)))
 
     def progressive_image(self, seg=None, want_accum=False, rgb8: Optional[np.ndarray] = None):

@@ -250,8 +250,19 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
     uint32_t const segW = seg.xEnd - seg.xBegin, segH = seg.yEnd - seg.yBegin;
     if (segW == 0 || segH == 0 || prm->sample_end <= prm->sample_begin)
         return SPT_OK;
+    // interleaved row bands (SptParams.band_count / band_index): the grid covers only this call's bands
+    uint32_t const bandCount = prm->band_count > 1u ? prm->band_count : 1u;
+    uint32_t const bandIndex = prm->band_count > 1u ? prm->band_index : 0u;
+    if (bandIndex >= bandCount)
+        return fail(SPT_ERR_INVALID, "band_index must be below band_count");
+    uint32_t const nBands = (segH + SPT_BAND_ROWS - 1u) / SPT_BAND_ROWS;
+    uint32_t const myBands = nBands > bandIndex ? (nBands - bandIndex + bandCount - 1u) / bandCount : 0u;
+    if (myBands == 0)
+        return SPT_OK;
 
     spt::TraceParams p{};
+    p.bandCount = bandCount;
+    p.bandIndex = bandIndex;
     fill_camera(p.cam, cam);
     p.width = prm->width;
     p.height = prm->height;
@@ -272,7 +283,8 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
     p.accum = dAccum;
     p.counters = (prm->flags & SPT_FLAG_COUNTERS) ? c->dCounters : nullptr;
 
-    dim3 const grid((segW + spt::kTileW - 1) / spt::kTileW, (segH + spt::kTileH - 1) / spt::kTileH);
+    static_assert(spt::kTileH == SPT_BAND_ROWS && spt::SplitShape::kTileH == SPT_BAND_ROWS, "a band is one tile row");
+    dim3 const grid((segW + spt::kTileW - 1) / spt::kTileW, myBands);
     dim3 const block(spt::kBlockThreads);
     size_t const geomBytes = size_t(c->n) * sizeof(float4);
     size_t const pairBytes = spt::filter_blob_bytes(c->filter.nSlots); // records + slot->index map
@@ -339,7 +351,7 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             p.filterCam.pairs = c->dPairsCam;
             p.filterCam.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairsCam + c->filter.nSlots / 2);
             p.filterCam.epsTCam = c->camEpsT;
-            size_t const pixels = size_t(segW) * segH;
+            size_t const pixels = size_t(segW) * std::min<size_t>(segH, size_t(myBands) * SPT_BAND_ROWS); // rows the launch covers
             // Staging budget.  A lane owns its pixel for a whole chunk and the warp waits for its slowest lane, so longer
             // chunks waste fewer lane-iterations (config 3 on B200: 8 / 16 / 32 / 64 GiB = 5 815 / 5 893 / 5 963 / 6 006
             // Msamples/s, profiles/r1_ab_chunk_and_cta_shape.txt): up to 64 GiB (512 spp of a 3840x2160 render), but never
@@ -386,9 +398,7 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             void (*primary)(const spt::TraceParams) = streamed ? spt::primary_hits_streamed : spt::primary_hits_kernel<2, spt::SplitShape>;
             void (*secondary)(const spt::TraceParams) = streamed ? spt::trace_secondary_streamed : spt::trace_secondary<2, spt::SplitShape>;
             // the resident kernels run smaller CTAs than the rest (spt_split.cuh, SplitShape)
-            dim3 const sGrid = streamed ? grid
-                                        : dim3((segW + spt::SplitShape::kTileW - 1) / spt::SplitShape::kTileW,
-                                               (segH + spt::SplitShape::kTileH - 1) / spt::SplitShape::kTileH);
+            dim3 const sGrid = streamed ? grid : dim3((segW + spt::SplitShape::kTileW - 1) / spt::SplitShape::kTileW, myBands);
             dim3 const sBlock(streamed ? spt::kBlockThreads : spt::SplitShape::kThreads);
             SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
             SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));

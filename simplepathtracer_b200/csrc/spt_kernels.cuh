@@ -49,6 +49,7 @@ struct TraceParams
     uint32_t yBegin, yEnd, xBegin, xEnd;
     uint32_t sampleBegin, sampleEnd;
     uint32_t depth, passCap;
+    uint32_t bandCount, bandIndex; // row r of the grid's tiles is band (r * bandCount + bandIndex) of the segment (SptParams)
     uint64_t seed;
     uint32_t n;
     const float4 *geom;  // (cx, cy, cz, r)
@@ -446,9 +447,17 @@ __device__ __forceinline__ void lane_pixel(const TraceParams &p, uint32_t &x, ui
     uint32_t const lx = (lane & (kWarpW - 1)) + (warp % S::kWarpsX) * kWarpW;
     uint32_t const ly = (lane / kWarpW) + (warp / S::kWarpsX) * kWarpH;
     x = p.xBegin + blockIdx.x * S::kTileW + lx;
-    y = p.yBegin + blockIdx.y * S::kTileH + ly;
+    y = p.yBegin + (blockIdx.y * p.bandCount + p.bandIndex) * S::kTileH + ly;
     inside = x < p.xEnd && y < p.yEnd;
 }
+// row of this lane among the rows the LAUNCH covers (== y - yBegin unless the call renders interleaved bands)
+template <typename S = DefaultShape>
+__device__ __forceinline__ uint32_t lane_row_local()
+{
+    uint32_t const lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    return blockIdx.y * S::kTileH + (lane / kWarpW) + (warp / S::kWarpsX) * kWarpH;
+}
+static_assert(kTileH == 8 && BlockShape<2, 2>::kTileH == 8, "SPT_BAND_ROWS is one tile row of every tracing kernel");
 
 // STAGE: what is staged into shared memory by TMA bulk copies at kernel start (every lane of a warp then
 // reads the same address: a broadcast).  2 = exact geometry + pre-filter records, 1 = pre-filter records only

@@ -81,7 +81,9 @@ __global__ void __launch_bounds__(kBlockThreads, 2) trace_wavefront(const __grid
 
     uint32_t const tid = threadIdx.x;
     uint32_t const segW = p.xEnd - p.xBegin, segH = p.yEnd - p.yBegin;
-    uint32_t const tilesX = (segW + kTileW - 1) / kTileW, tilesY = (segH + kTileH - 1) / kTileH;
+    uint32_t const nBands = (segH + kTileH - 1) / kTileH; // tile rows of the segment; this launch takes every bandCount-th
+    uint32_t const tilesX = (segW + kTileW - 1) / kTileW,
+                   tilesY = nBands > p.bandIndex ? (nBands - p.bandIndex + p.bandCount - 1) / p.bandCount : 0u;
     float const widthF = __uint2float_rn(p.width), heightF = __uint2float_rn(p.height);
     uint32_t segments = 0, dropped = 0, exactEvals = 0, samplesDone = 0;
 
@@ -97,7 +99,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) trace_wavefront(const __grid
         // slot <-> pixel, same 8x4-per-warp layout as the megakernel
         uint32_t const lane = tid & 31u, warp = tid >> 5;
         uint32_t const px = p.xBegin + (tile % tilesX) * kTileW + (lane & (kWarpW - 1)) + (warp % kBlockWarpsX) * kWarpW;
-        uint32_t const py = p.yBegin + (tile / tilesX) * kTileH + (lane / kWarpW) + (warp / kBlockWarpsX) * kWarpH;
+        uint32_t const py = p.yBegin + ((tile / tilesX) * p.bandCount + p.bandIndex) * kTileH + (lane / kWarpW) + (warp / kBlockWarpsX) * kWarpH;
         bool const inside = px < p.xEnd && py < p.yEnd;
         uint32_t const pixel = py * p.width + px;
         uint64_t const pixKey = pixel_key(p.seed, pixel);

@@ -3,13 +3,14 @@
 Every (pixel, sample) is independent under the counter-based RNG, and the scene (<= 672 KB) is replicated,
 so the path shards with no exchange inside the tracing kernel.  Two partitions are offered:
 
-* ``sample_range``  -- rank r traces samples [r*spp/G, (r+1)*spp/G) of EVERY pixel.  Perfectly balanced
-  (sky and sphere-dense image regions cost differently, so static tile splits are not); the per-rank float4
-  accumulators (sum r, sum g, sum b, count) are then combined by ONE sum-reduce to rank 0
-  (``reduce_accumulators``: NCCL over NVLink on the GPUs, gloo in the CPU tests).
-* ``row_bands``     -- rank r owns the 8-row bands b with b % G == r (interleaved, for spp < G).  The regions are
-  disjoint, so the same sum-reduce of zero-initialised accumulators is a gather with no arithmetic, and the
-  result is bit-identical to the single-GPU render.
+* ``row_bands``     -- rank r owns the 8-row bands b with b % G == r (interleaved: 270 bands at 2160 rows, so sky and
+  sphere-dense regions spread evenly) and traces ALL samples of its pixels in ONE call (``SptParams.band_count`` /
+  ``band_index``).  The regions are disjoint, so the sum-reduce of zero-initialised accumulators to rank 0
+  (``reduce_accumulators``: NCCL over NVLink on the GPUs, gloo in the CPU tests) is a gather with no arithmetic and
+  the result is bit-identical to the single-GPU render.  The default: a lane of the tracing kernels owns its pixel
+  for a whole chunk of samples, and full-length chunks waste fewer lane-iterations than 1/G-length ones.
+* ``sample_range``  -- rank r traces samples [r*spp/G, (r+1)*spp/G) of EVERY pixel; the per-rank accumulators
+  (sum r, sum g, sum b, count) are combined by the same reduce, which now adds G partial sums per pixel.
 
 The reference's analogue is the static threadCount x threadCount tile grid of RenderImageParallelMain
 (/root/reference/include/Renderer.hpp:264-274).  This module is host-side plumbing: it never computes a pixel.
@@ -41,9 +42,16 @@ def row_bands(rank: int, world: int, height: int, width: int, band_rows: int = B
     return segs
 
 
+def band_params(rank: int, world: int) -> Tuple[int, int]:
+    """(band_count, band_index) of ``SptParams`` for rank `rank` of `world`."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError(f"rank {rank} outside world {world}")
+    return world, rank
+
+
 def choose_partition(world: int, spp: int) -> str:
-    """Sample ranges whenever every rank gets at least one sample, otherwise interleaved row bands."""
-    return "samples" if spp >= world else "bands"
+    """Interleaved row bands (full-length sample chunks on every rank, single-GPU bits)."""
+    return "bands"
 
 
 def reduce_accumulators(accum, dst: int = 0, group=None) -> None:
@@ -67,11 +75,10 @@ def accumulate_sharded(tracer, cam, width: int, height: int, spp: int, depth: in
             return 1
         return 0
     if partition == "bands":
-        # contiguous runs of bands cannot be merged (they interleave), so one launch per band; used only when spp < G
-        n = 0
-        for seg in row_bands(rank, world, height, width):
-            tracer.accumulate(cam, width, height, 0, spp, depth, accum, pass_cap=pass_cap, seed=seed, seg=seg, variant=variant,
-                              flags=flags)
-            n += 1
-        return n
+        # one call: the library's grid covers only this rank's bands (SptParams.band_count / band_index)
+        if rank * BAND_ROWS >= height or spp <= 0:
+            return 0
+        tracer.accumulate(cam, width, height, 0, spp, depth, accum, pass_cap=pass_cap, seed=seed, variant=variant, flags=flags,
+                          bands=band_params(rank, world))
+        return 1
     raise ValueError(f"unknown partition {partition!r}")

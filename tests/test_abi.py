@@ -36,7 +36,7 @@ def test_struct_sizes_match_header():
     # natural C layout of the structs in include/spt_cuda.h on LP64
     assert ctypes.sizeof(binding.Segment) == 16
     assert ctypes.sizeof(binding._CCamera) == 96
-    assert ctypes.sizeof(binding._CParams) == 40
+    assert ctypes.sizeof(binding._CParams) == 48  # band_count, band_index appended
     assert ctypes.sizeof(binding._CScene) == 48
     assert ctypes.sizeof(binding.Counters) == 40
     assert ctypes.sizeof(binding.Timing) == 16

@@ -497,3 +497,38 @@ def test_split_render_segment_and_other_camera(tracer, oracle, scene_random):
         _, acc = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=3, seg=seg, want_accum=True, flags=spt.FLAG_SPLIT)
         oacc, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, pass_cap=10, seed=3, seg=seg)
         assert_accum_equal(acc, oacc)
+
+
+# ----------------------------------------------------------------------------- interleaved row bands (multi-GPU pixel partition)
+@pytest.mark.parametrize("variant,flags", [(spt.MEGAKERNEL, 0), (spt.MEGAKERNEL, spt.FLAG_SINGLE_KERNEL), (spt.MEGAKERNEL, spt.FLAG_STREAMED),
+                                           (spt.MEGAKERNEL, spt.FLAG_STRICT_LOOP), (spt.WAVEFRONT, 0)])
+def test_row_bands_compose_to_the_full_render(tracer, oracle, cam, scene_random, variant, flags, monkeypatch):
+    """SptParams.band_count / band_index: the calls of G 'ranks' touch disjoint 8-row bands and together leave the bits of
+    one full render (what the multi-GPU partition relies on), on a ragged segment, for every kernel family."""
+    import torch
+
+    monkeypatch.setenv("SPT_SPLIT_CHUNK", "3")  # several chunks of samples per call
+    tracer.set_scene(scene_random)
+    tracer.set_stream(torch.cuda.current_stream().cuda_stream)  # torch's fills and our kernels in one stream order
+    w, h, spp, depth = 150, 93, 5, 8
+    seg = (3, 90, 7, 141)  # 87 rows: 11 bands, the last one 7 rows
+    full = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+    tracer.accumulate(cam, w, h, 0, spp, depth, full, pass_cap=10, seed=12, seg=seg, variant=variant, flags=flags)
+    for world in (2, 3, 16):  # 16 > 11 bands: some ranks own nothing
+        total = torch.zeros_like(full)
+        for rank in range(world):
+            part = torch.zeros_like(full)
+            tracer.accumulate(cam, w, h, 0, spp, depth, part, pass_cap=10, seed=12, seg=seg, variant=variant, flags=flags,
+                              bands=(world, rank))
+            torch.cuda.synchronize()
+            rows = torch.nonzero(part[..., 3].sum(dim=1)).flatten().tolist()
+            assert all(((y - seg[0]) // 8) % world == rank for y in rows)
+            assert not torch.any((part[..., 3] > 0) & (total[..., 3] > 0))
+            total += part
+        assert torch.equal(total, full)
+    torch.cuda.synchronize()
+    oacc, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, pass_cap=10, seed=12, seg=seg)
+    assert_accum_equal(full.cpu().numpy(), oacc)
+    with pytest.raises(spt.SptError):
+        tracer.accumulate(cam, w, h, 0, spp, depth, full, bands=(2, 2))
+    tracer.set_stream(None)

@@ -42,8 +42,11 @@ def test_row_bands_partition_the_image():
 
 
 def test_choose_partition():
-    assert sharding.choose_partition(8, 1024) == "samples"
+    assert sharding.choose_partition(8, 1024) == "bands"
     assert sharding.choose_partition(8, 4) == "bands"
+    assert sharding.band_params(3, 8) == (8, 3)
+    with pytest.raises(ValueError):
+        sharding.band_params(8, 8)
 
 
 class OracleTracer:
@@ -54,12 +57,17 @@ class OracleTracer:
 
         self.o, self.scene = Oracle(), scene
 
-    def accumulate(self, cam, width, height, s0, s1, depth, accum, pass_cap=0, seed=1, seg=None, variant=0, flags=0):
+    def accumulate(self, cam, width, height, s0, s1, depth, accum, pass_cap=0, seed=1, seg=None, variant=0, flags=0, bands=None):
         import torch
 
-        part, _ = self.o.render_accum(self.scene, cam, width, height, s1 - s0, depth, pass_cap=pass_cap, seed=seed, seg=seg,
-                                      sample_begin=s0)
-        accum += torch.from_numpy(np.ascontiguousarray(part).reshape(height, width, 4))
+        # SptParams.band_count / band_index (include/spt_cuda.h): the 8-row bands b of the segment with b % count == index
+        y0, y1, x0, x1 = seg if seg is not None else (0, height, 0, width)
+        count, index = bands if bands and bands[0] > 1 else (1, 0)
+        for b in range(index, (y1 - y0 + sharding.BAND_ROWS - 1) // sharding.BAND_ROWS, count):
+            band = (y0 + b * sharding.BAND_ROWS, min(y0 + (b + 1) * sharding.BAND_ROWS, y1), x0, x1)
+            part, _ = self.o.render_accum(self.scene, cam, width, height, s1 - s0, depth, pass_cap=pass_cap, seed=seed, seg=band,
+                                          sample_begin=s0)
+            accum += torch.from_numpy(np.ascontiguousarray(part).reshape(height, width, 4))
 
 
 def _worker(rank, world, port, partition, out_dir):

@@ -36,6 +36,9 @@ namespace spt
 #ifndef SPT_FILTER_TC
 #define SPT_FILTER_TC 0 // 1: the pre-filter also tests the sign of tC (one more FMNMX per sphere, fewer candidates)
 #endif
+#ifndef SPT_WORD_UNROLL2
+#define SPT_WORD_UNROLL2 1 // the single-ray word loop takes two full words per trip while it can (+0.6 .. 1.0 % on config 3; 0: one)
+#endif
 constexpr float kBigRadius = 64.f;
 constexpr float kBigCentre = 4096.f;
 constexpr uint32_t kWordSpheres = 32;                // one mask word
@@ -195,10 +198,12 @@ __device__ __forceinline__ FilterRay make_filter_ray_cam(V3 dir, float od, float
 //
 // Loop shape: ONE rolled loop over mask words whose body is 16 unrolled records (32 slots), so the hot code is
 // ~230 instructions that stay in the instruction cache however many warps are in it; the last word runs
-// only the quads (4 records) that exist.  The masks of up to kSuperWords words are parked in registers and
-// the divergent candidate loop runs once per super-word, so lanes with candidates in different words of the
-// same super-word are served in the same trips.
-// exact sequence on the candidates parked in c0..c3: c_k holds the mask of word (wEnd - 1 - k) of the span.  Leaves all
+// only the quads (4 records) that exist.  The masks of up to kSuperWords words are parked in registers -- a shift
+// register with the newest word in c0, so no select on the word index is needed -- and the divergent candidate
+// loop (resolve_candidates) runs once per super-word, so lanes with candidates in different words of the same
+// super-word are served in the same trips.
+//
+// resolve_candidates: the exact sequence on the candidates parked in c0..c3: c_k holds the mask of word (wEnd - 1 - k) of the span.  Leaves all
 // four masks zero.  Lanes without candidates idle here (the only divergent part of the closest hit).
 template <typename GeomPtr>
 __device__ __forceinline__ void resolve_candidates(uint32_t &c0, uint32_t &c1, uint32_t &c2, uint32_t &c3, uint32_t wEnd, const uint32_t *slotIdx,
@@ -242,39 +247,69 @@ __device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_
     for (uint32_t w = 0; w < nWords;) // everything about w is warp-uniform
     {
         uint32_t mask = 0xFFFFFFFFu; // all "fail"
-        if (w < nFull)
+#if SPT_WORD_UNROLL2
+        if (w + 2u <= nFull) // two full words per trip: the loop control is paid once per 64 slots
         {
+            uint32_t mask0 = 0xFFFFFFFFu;
 #pragma unroll
             for (uint32_t pp = 0; pp < kWordSpheres / 2; ++pp)
+            {
+                if (CAM)
+                    filter_pair_cam(rec + pp, fr, mask0);
+                else
+                    filter_pair(rec + pp, fr, mask0);
+            }
+#pragma unroll
+            for (uint32_t pp = kWordSpheres / 2; pp < kWordSpheres; ++pp)
             {
                 if (CAM)
                     filter_pair_cam(rec + pp, fr, mask);
                 else
                     filter_pair(rec + pp, fr, mask);
             }
-            rec += kWordSpheres / 2;
+            rec += kWordSpheres;
+            c3 = c1;
+            c2 = c0;
+            c1 = live ? ~mask0 : 0u;
+            ++w;
         }
-        else // the partial last word: only the quads (4 records) that exist
+        else
+#endif
         {
-#pragma unroll 1
-            for (uint32_t q = 0; q < tailQuads; ++q)
+            if (w < nFull)
             {
 #pragma unroll
-                for (uint32_t pp = 0; pp < kQuadSpheres / 2; ++pp)
+                for (uint32_t pp = 0; pp < kWordSpheres / 2; ++pp)
                 {
                     if (CAM)
                         filter_pair_cam(rec + pp, fr, mask);
                     else
                         filter_pair(rec + pp, fr, mask);
                 }
-                rec += kQuadSpheres / 2;
+                rec += kWordSpheres / 2;
             }
-            uint32_t const sh = kWordSpheres - kQuadSpheres * tailQuads; // 8, 16 or 24 missing slots: fail bits
-            mask = (mask << sh) | ((1u << sh) - 1u);
+            else // the partial last word: only the quads (4 records) that exist
+            {
+#pragma unroll 1
+                for (uint32_t q = 0; q < tailQuads; ++q)
+                {
+#pragma unroll
+                    for (uint32_t pp = 0; pp < kQuadSpheres / 2; ++pp)
+                    {
+                        if (CAM)
+                            filter_pair_cam(rec + pp, fr, mask);
+                        else
+                            filter_pair(rec + pp, fr, mask);
+                    }
+                    rec += kQuadSpheres / 2;
+                }
+                uint32_t const sh = kWordSpheres - kQuadSpheres * tailQuads; // 8, 16 or 24 missing slots: fail bits
+                mask = (mask << sh) | ((1u << sh) - 1u);
+            }
+            c3 = c2;
+            c2 = c1;
+            c1 = c0;
         }
-        c3 = c2;
-        c2 = c1;
-        c1 = c0;
         c0 = live ? ~mask : 0u; // bit (31 - j) set <=> slot j of the word is a candidate
         ++w;
         if ((w & (kSuperWords - 1u)) == 0u || w == nWords)

@@ -5,8 +5,8 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 ... bench.py --gpus N ...
 
 One "step" = one complete render of the workload (every pixel, every sample, reduce across GPUs,
-normalise + gamma + pack RGB8).  Ranks share a render by interleaved 8-row bands of pixels (or by sample ranges,
---partition samples); the one collective is an NCCL sum-reduce of the float4 accumulators to rank 0.
+normalise + gamma + pack RGB8).  Ranks share a render by sample ranges (or by interleaved 8-row bands of pixels,
+--partition bands); the one collective is an NCCL sum-reduce of the float4 accumulators to rank 0.
 
   value    : W*H*spp / step time with scene and accumulators resident in HBM (CUDA events, max over ranks)
   e2e      : same metric through the host-buffer C-ABI path: scene upload (H2D) + render + RGB8 image back (D2H)
@@ -198,8 +198,9 @@ def run_native_arm(args, wl):
     W, H, spp, depth = wl["width"], wl["height"], args.spp or wl["spp"], wl["depth"]
     from simplepathtracer_b200 import sharding
 
-    # pixel partition (default): rank r renders every sample of the 8-row bands b with b % world == r -- full-length
-    # chunks of samples on every rank, disjoint pixels; --partition samples: rank r renders samples [s0, s1) of every pixel
+    # sample ranges (default): rank r renders samples [s0, s1) of every pixel, so every rank launches the full grid;
+    # --partition bands: rank r renders every sample of the 8-row bands b with b % world == r (disjoint pixels, single-GPU
+    # bits, but 1/world of the CTAs per launch: slower at 8 GPUs)
     if args.partition == "bands":
         s0, s1 = 0, spp
         bands = sharding.band_params(rank, world) if world > 1 else None
@@ -400,7 +401,7 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (debug only; invalidates the headline)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--variant", default="megakernel", choices=["megakernel", "wavefront"])
-    ap.add_argument("--partition", default="bands", choices=["bands", "samples"], help="how N > 1 ranks share a render (sharding.py)")
+    ap.add_argument("--partition", default="samples", choices=["samples", "bands"], help="how N > 1 ranks share a render (sharding.py)")
     ap.add_argument("--flags", type=int, default=0, help="extra SPT_FLAG_* bits for the trace launches (experiments)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]

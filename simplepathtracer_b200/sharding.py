@@ -3,14 +3,16 @@
 Every (pixel, sample) is independent under the counter-based RNG, and the scene (<= 672 KB) is replicated,
 so the path shards with no exchange inside the tracing kernel.  Two partitions are offered:
 
-* ``row_bands``     -- rank r owns the 8-row bands b with b % G == r (interleaved: 270 bands at 2160 rows, so sky and
-  sphere-dense regions spread evenly) and traces ALL samples of its pixels in ONE call (``SptParams.band_count`` /
-  ``band_index``).  The regions are disjoint, so the sum-reduce of zero-initialised accumulators to rank 0
-  (``reduce_accumulators``: NCCL over NVLink on the GPUs, gloo in the CPU tests) is a gather with no arithmetic and
-  the result is bit-identical to the single-GPU render.  The default: a lane of the tracing kernels owns its pixel
-  for a whole chunk of samples, and full-length chunks waste fewer lane-iterations than 1/G-length ones.
-* ``sample_range``  -- rank r traces samples [r*spp/G, (r+1)*spp/G) of EVERY pixel; the per-rank accumulators
-  (sum r, sum g, sum b, count) are combined by the same reduce, which now adds G partial sums per pixel.
+* ``sample_range``  -- rank r traces samples [r*spp/G, (r+1)*spp/G) of EVERY pixel.  Balanced by construction (sky
+  and sphere-dense image regions cost differently) and every rank launches the full grid of CTAs; the per-rank float4
+  accumulators (sum r, sum g, sum b, count) are then combined by ONE sum-reduce to rank 0
+  (``reduce_accumulators``: NCCL over NVLink on the GPUs, gloo in the CPU tests).  The default.
+* ``row_bands``     -- rank r owns the 8-row bands b with b % G == r (interleaved) and traces ALL samples of its pixels
+  in ONE call (``SptParams.band_count`` / ``band_index``).  The regions are disjoint, so the same sum-reduce of
+  zero-initialised accumulators is a gather with no arithmetic and the result is bit-identical to the single-GPU
+  render.  Used when spp < G; measured on 8 B200s it is slower than sample ranges at 1024 spp (a rank's grid shrinks to
+  1/G of the CTAs, 6.9 instead of 55 waves per launch, and the tail of each launch weighs accordingly: 40.5 against
+  51.4 Gsamples/s).
 
 The reference's analogue is the static threadCount x threadCount tile grid of RenderImageParallelMain
 (/root/reference/include/Renderer.hpp:264-274).  This module is host-side plumbing: it never computes a pixel.
@@ -50,8 +52,8 @@ def band_params(rank: int, world: int) -> Tuple[int, int]:
 
 
 def choose_partition(world: int, spp: int) -> str:
-    """Interleaved row bands (full-length sample chunks on every rank, single-GPU bits)."""
-    return "bands"
+    """Sample ranges whenever every rank gets at least one sample, otherwise interleaved row bands."""
+    return "samples" if spp >= world else "bands"
 
 
 def reduce_accumulators(accum, dst: int = 0, group=None) -> None:

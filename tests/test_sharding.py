@@ -42,7 +42,7 @@ def test_row_bands_partition_the_image():
 
 
 def test_choose_partition():
-    assert sharding.choose_partition(8, 1024) == "bands"
+    assert sharding.choose_partition(8, 1024) == "samples"
     assert sharding.choose_partition(8, 4) == "bands"
     assert sharding.band_params(3, 8) == (8, 3)
     with pytest.raises(ValueError):

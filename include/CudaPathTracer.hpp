@@ -65,7 +65,11 @@ inline SptContext *Acquire()
     State &s = GetState();
     std::lock_guard<std::mutex> g(s.lock);
     if (!s.ctx)
+    {
+        if (spt_cuda_abi_version() != SPT_ABI_VERSION) // this TU and the library disagree about the struct layouts
+            throw std::runtime_error("CudaPathTracer: libspt_cuda.so was built from another revision of spt_cuda.h");
         Check(spt_cuda_create(&s.ctx, s.device), "spt_cuda_create");
+    }
     if (!s.sceneUploaded)
     {
         std::vector<uint8_t> mats(g_sphereNumber);

@@ -200,6 +200,11 @@ SPT_API int spt_cuda_measure_fp32_peak(SptContext *ctx, float *tflops_scalar, fl
 SPT_API const char *spt_cuda_last_error(void);
 SPT_API const char *spt_cuda_version(void);
 
+/* Layout revision of the structs above.  A caller compiled against another revision of this header must not call in
+   (revision 2 appended band_count / band_index to SptParams): compare with SPT_ABI_VERSION once after loading. */
+#define SPT_ABI_VERSION 2u
+SPT_API uint32_t spt_cuda_abi_version(void);
+
 #ifdef __cplusplus
 }
 #endif

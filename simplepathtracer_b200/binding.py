@@ -15,6 +15,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_NAME = "libspt_cuda.so"
 
+ABI_VERSION = 2  # SPT_ABI_VERSION of include/spt_cuda.h
 MEGAKERNEL, WAVEFRONT = 0, 1
 FLAG_STRICT_LOOP, FLAG_COUNTERS, FLAG_CROSS_CHECK, FLAG_STREAMED, FLAG_RESIDENT, FLAG_SPLIT, FLAG_SINGLE_KERNEL = 1, 2, 4, 8, 16, 32, 64
 SKYBOX, REFLECTIVE, REFRACTIVE, DIFFUSE = 0, 1, 2, 3  # include/Definitions.hpp:7-13
@@ -172,7 +173,7 @@ EXPORTS = [
     "spt_cuda_render", "spt_cuda_accumulate", "spt_cuda_resolve", "spt_cuda_synchronize", "spt_cuda_first_hit",
     "spt_cuda_progressive_begin", "spt_cuda_progressive_add", "spt_cuda_progressive_image", "spt_cuda_progressive_load",
     "spt_cuda_closest_hit", "spt_cuda_get_counters", "spt_cuda_reset_counters", "spt_cuda_get_timing",
-    "spt_cuda_measure_fp32_peak", "spt_cuda_last_error", "spt_cuda_version",
+    "spt_cuda_measure_fp32_peak", "spt_cuda_last_error", "spt_cuda_version", "spt_cuda_abi_version",
 ]
 HOST_EXPORTS = [
     "spt_host_init_spheres", "spt_host_generate_spheres", "spt_host_generate_metal_glass", "spt_host_generate_lattice",
@@ -193,6 +194,9 @@ def load_library():
         raise SptError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (needs nvcc). "
                        "There is no CPU fallback.")
     L = C.CDLL(path)
+    # struct layouts below are revision ABI_VERSION of include/spt_cuda.h: a library built from another revision is refused
+    if not hasattr(L, "spt_cuda_abi_version") or (setattr(L.spt_cuda_abi_version, "restype", C.c_uint32) or L.spt_cuda_abi_version()) != ABI_VERSION:
+        raise SptError(f"{path} was built from another revision of include/spt_cuda.h (want ABI {ABI_VERSION}): rebuild it")
     L.spt_cuda_last_error.restype = C.c_char_p
     L.spt_cuda_version.restype = C.c_char_p
     L.spt_cuda_create.argtypes = [C.POINTER(C.c_void_p), C.c_int]

@@ -454,6 +454,7 @@ extern "C"
 
 const char *spt_cuda_last_error(void) { return g_lastError.c_str(); }
 const char *spt_cuda_version(void) { return "simplepathtracer_b200 0.1 (sm_100a)"; }
+uint32_t spt_cuda_abi_version(void) { return SPT_ABI_VERSION; }
 
 int spt_cuda_create(SptContext **out, int device)
 {

@@ -42,8 +42,38 @@ def test_struct_sizes_match_header():
     assert ctypes.sizeof(binding.Timing) == 16
 
 
+def test_struct_layouts_match_the_c_compiler(tmp_path):
+    """sizeof / offsetof as gcc sees include/spt_cuda.h against the ctypes mirror, field by field."""
+    import shutil
+    import subprocess
+
+    if not shutil.which("gcc"):
+        pytest.skip("no gcc")
+    structs = {"SptSegment": binding.Segment, "SptCamera": binding._CCamera, "SptParams": binding._CParams, "SptScene": binding._CScene,
+               "SptCounters": binding.Counters, "SptTiming": binding.Timing, "SptDeviceInfo": binding.DeviceInfo}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "spt_cuda.h"', "int main(void) {",
+             'printf("abi %u\\n", (unsigned)SPT_ABI_VERSION);']
+    for cname, cls in structs.items():
+        lines.append(f'printf("{cname} %zu\\n", sizeof({cname}));')
+        for fname, _ in cls._fields_:
+            lines.append(f'printf("{cname}.{fname} %zu\\n", offsetof({cname}, {fname}));')
+    lines.append("return 0; }")
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    got = dict(line.split() for line in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    assert int(got["abi"]) == binding.ABI_VERSION
+    for cname, cls in structs.items():
+        assert int(got[cname]) == ctypes.sizeof(cls), cname
+        for fname, _ in cls._fields_:
+            assert int(got[f"{cname}.{fname}"]) == getattr(cls, fname).offset, f"{cname}.{fname}"
+
+
 def test_version_string(lib):
     assert b"sm_100a" in lib.spt_cuda_version()
+    lib.spt_cuda_abi_version.restype = ctypes.c_uint32
+    assert lib.spt_cuda_abi_version() == binding.ABI_VERSION
 
 
 def test_no_cpu_fallback_without_device(lib):

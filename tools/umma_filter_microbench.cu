@@ -2,7 +2,9 @@
 // iteration: groundwork for DESIGN.md section 9, item 1.  Ran on B200 at the very end of round 1
 // (profiles/r1_microbench_umma_filter.txt): self-check clean (no true hit missed, 0.107 candidates for 0.103 true hits per
 // ray, worst error 19 u(A^2+B^2)); 1 973 cycles per iteration with one CTA per SM (the whole chain is serial inside a CTA),
-// 4.07 T (ray, sphere) pairs/s with two -- above the 3.72 T pairs/s that 100 % of the issue slots would give the FFMA2 loop.
+// 4.07 .. 4.91 T (ray, sphere) pairs/s with two -- above the 3.72 T pairs/s that 100 % of the issue slots would give the FFMA2
+// loop.  -DUMMA_CHUNKED=1 (five 32-slot chunks through two 32-column accumulators, 64 TMEM columns per CTA) is correct too but
+// slower: ~650 cycles per mma -> commit -> wait -> ld round trip, 4.36 T pairs/s with four CTAs per SM.
 //
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o umma_filter_microbench tools/umma_filter_microbench.cu
 //   ./umma_filter_microbench [ctas_per_sm=2] [iters=200]      (256 TMEM columns per CTA: two CTAs fit an SM, more serialise on tcgen05.alloc)
@@ -34,7 +36,10 @@
 constexpr int kRays = 128;   // M: rays per CTA (one per thread, one TMEM lane each)
 constexpr int kSlots = 160;  // N: filter slots (multiple of 16 for M = 128)
 constexpr int kK = 40;       // inner dimension
-constexpr int kTmemCols = 256; // power of two >= kSlots
+#ifndef UMMA_CHUNKED
+#define UMMA_CHUNKED 0 // 1: the list in five 32-slot chunks through two 32-column accumulators (64 TMEM columns per CTA, so more
+#endif                 //    CTAs fit an SM); the MMA of chunk c + 2 is issued as soon as every warp has read chunk c
+constexpr int kTmemCols = UMMA_CHUNKED ? 64 : 256; // power of two >= the accumulator columns
 constexpr uint32_t kABytes = kRays * kK * 4, kBBytes = kSlots * kK * 4;
 constexpr uint32_t kALbo = (kRays / 8) * 128, kBLbo = (kSlots / 8) * 128, kSbo = 128;
 
@@ -48,6 +53,42 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t addr, uint32_t lbo, uint3
 }
 // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32, A = B = TF32, both K-major, dense
 constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(kSlots >> 3) << 17) | (uint32_t(kRays >> 4) << 24);
+constexpr uint32_t kIdescChunk = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(32 >> 3) << 17) | (uint32_t(kRays >> 4) << 24); // N = 32
+
+__device__ __forceinline__ void umma_tf32(uint32_t tmemD, uint64_t ad, uint64_t bd, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmemD), "l"(ad), "l"(bd), "r"(idesc), "r"(accumulate)
+                 : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar)
+{
+    // arrives on the barrier when every MMA issued so far is complete (implies tcgen05.fence::before_thread_sync)
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// 32 consecutive accumulator columns of this thread's TMEM lane -> sign bits (bit 31 - j set <=> column j >= 0)
+__device__ __forceinline__ uint32_t tmem_signs32(uint32_t taddr, float *dump)
+{
+    uint32_t v[32];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+                   "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+                   "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+                   "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    uint32_t mask = 0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+        mask = __funnelshift_l(v[j], mask, 1); // sign bit = fail
+    if (dump)
+        for (int j = 0; j < 32; ++j)
+            dump[j] = __uint_as_float(v[j]);
+    return ~mask;
+}
 
 __device__ __forceinline__ void split_tf32(float x, float &hi, float &lo)
 {
@@ -78,7 +119,7 @@ __global__ void __launch_bounds__(kRays) umma_filter(const float *__restrict__ b
     extern __shared__ __align__(128) unsigned char smem[];
     float *sB = reinterpret_cast<float *>(smem);
     float *sA = reinterpret_cast<float *>(smem + kBBytes);
-    __shared__ __align__(8) uint64_t mmaBar;
+    __shared__ __align__(8) uint64_t mmaBar[2];
     __shared__ uint32_t tmemBase;
     uint32_t const tid = threadIdx.x, warp = tid >> 5;
 
@@ -87,7 +128,8 @@ __global__ void __launch_bounds__(kRays) umma_filter(const float *__restrict__ b
         reinterpret_cast<float4 *>(sB)[i] = reinterpret_cast<const float4 *>(bmat)[i];
     if (tid == 0)
     {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&mmaBar)));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&mmaBar[0])));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&mmaBar[1])));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0)
@@ -103,6 +145,7 @@ __global__ void __launch_bounds__(kRays) umma_filter(const float *__restrict__ b
     uint32_t const rayIdx = (blockIdx.x * kRays + tid) % raysTotal;
     Ray const ray = rays[rayIdx];
     uint32_t m0 = 0, m1 = 0, m2 = 0, m3 = 0, m4 = 0;
+    uint32_t phase = 0; // bit b = parity the next wait on mmaBar[b] uses
     long long const t0 = clock64();
     for (uint32_t it = 0; it < iters; ++it)
     {
@@ -132,56 +175,62 @@ __global__ void __launch_bounds__(kRays) umma_filter(const float *__restrict__ b
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy stores -> visible to the tensor core
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); // earlier tcgen05.ld of this thread are done with TMEM
         __syncthreads();
+        uint32_t const aBase = smem_u32(sA), bBase = smem_u32(sB);
+        uint32_t const lanes = tmem + ((warp * 32u) << 16); // this warp's 32 TMEM lanes = its 32 rays
+        bool const dumping = vdump && it == 0 && blockIdx.x * kRays + tid < raysTotal;
+        uint32_t m[5];
+#if UMMA_CHUNKED
+        auto issue_chunk = [&](uint32_t c) { // elected thread: chunk c (slots 32 c .. 32 c + 31) into accumulator c & 1
+#pragma unroll
+            for (int ks = 0; ks < kK / 8; ++ks)
+                umma_tf32(tmem + (c & 1u) * 32u, umma_desc(aBase + uint32_t(ks) * 2u * kALbo, kALbo, kSbo),
+                          umma_desc(bBase + uint32_t(ks) * 2u * kBLbo + c * 4u * kSbo, kBLbo, kSbo), kIdescChunk, ks > 0 ? 1u : 0u);
+            umma_commit(smem_u32(&mmaBar[c & 1u]));
+        };
         if (tid == 0)
         {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            uint32_t const aBase = smem_u32(sA), bBase = smem_u32(sB);
+            issue_chunk(0);
+            issue_chunk(1);
+        }
+#pragma unroll
+        for (uint32_t c = 0; c < kSlots / 32; ++c)
+        {
+            uint32_t const b = c & 1u;
+            mbar_wait(smem_u32(&mmaBar[b]), (phase >> b) & 1u);
+            phase ^= 1u << b;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            m[c] = tmem_signs32(lanes + b * 32u, dumping ? vdump + size_t(rayIdx) * kSlots + c * 32 : nullptr);
+            if (c + 2 < kSlots / 32)
+            {
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncthreads(); // every warp has read accumulator b
+                if (tid == 0)
+                {
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    issue_chunk(c + 2);
+                }
+            }
+        }
+#else
+        if (tid == 0)
+        {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
             for (int ks = 0; ks < kK / 8; ++ks) // one UMMA K step = 8 TF32 = two 16-byte chunks
-            {
-                uint64_t const ad = umma_desc(aBase + uint32_t(ks) * 2u * kALbo, kALbo, kSbo);
-                uint64_t const bd = umma_desc(bBase + uint32_t(ks) * 2u * kBLbo, kBLbo, kSbo);
-                uint32_t const accumulate = ks > 0 ? 1u : 0u;
-                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                             "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-                             ::"r"(tmem), "l"(ad), "l"(bd), "r"(kIdesc), "r"(accumulate)
-                             : "memory");
-            }
-            // arrives on the barrier when the five MMAs are complete (implies tcgen05.fence::before_thread_sync)
-            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&mmaBar)) : "memory");
+                umma_tf32(tmem, umma_desc(aBase + uint32_t(ks) * 2u * kALbo, kALbo, kSbo),
+                          umma_desc(bBase + uint32_t(ks) * 2u * kBLbo, kBLbo, kSbo), kIdesc, ks > 0 ? 1u : 0u);
+            umma_commit(smem_u32(&mmaBar[0]));
         }
-        mbar_wait(smem_u32(&mmaBar), it & 1u);
+        mbar_wait(smem_u32(&mmaBar[0]), phase & 1u);
+        phase ^= 1u;
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-
-        // ---- epilogue: this warp's 32 lanes (rays) x 160 columns; only the signs are wanted ----
-        uint32_t const lanes = tmem + ((warp * 32u) << 16);
+        // epilogue: this warp's 32 lanes x 160 columns; only the signs are wanted
 #pragma unroll
         for (int w = 0; w < kSlots / 32; ++w)
-        {
-            uint32_t v[32];
-            asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                         "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                         "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-                           "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-                           "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-                           "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                         : "r"(lanes + uint32_t(w) * 32u));
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            uint32_t mask = 0;
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-                mask = __funnelshift_l(v[j], mask, 1); // sign bit = fail
-            mask = ~mask;
-            if (w == 0) m0 |= mask;
-            else if (w == 1) m1 |= mask;
-            else if (w == 2) m2 |= mask;
-            else if (w == 3) m3 |= mask;
-            else m4 |= mask;
-            if (vdump && it == 0 && blockIdx.x * kRays + tid < raysTotal)
-                for (int j = 0; j < 32; ++j)
-                    vdump[size_t(rayIdx) * kSlots + w * 32 + j] = __uint_as_float(v[j]);
-        }
+            m[w] = tmem_signs32(lanes + uint32_t(w) * 32u, dumping ? vdump + size_t(rayIdx) * kSlots + w * 32 : nullptr);
+#endif
+        m0 |= m[0]; m1 |= m[1]; m2 |= m[2]; m3 |= m[3]; m4 |= m[4];
     }
     long long const t1 = clock64();
     if (blockIdx.x * kRays + tid < raysTotal)

@@ -118,6 +118,9 @@ def main():
     report("fp32 FFMA chains (shipped)", v32.astype(np.float64))
     shipped_slack = 96 * U * (A2B2 + r64[:, None] ** 2)
     print(f"{'':34s} shipped slack 96u(A^2+B^2+r^2): candidates/ray {((v_x + shipped_slack > 1e-3)).sum() / a.rays:.3f}")
+    for mult in (160, 256, 512):  # what a worst-case bound for the tensor-core form would ask for
+        sl = mult * U * (A2B2 + r64[:, None] ** 2)
+        print(f"{'':34s} slack {mult}u(A^2+B^2+r^2): candidates/ray {((v_x + sl > 1e-3)).sum() / a.rays:.3f}")
 
     Ch, Cl = split(C)
     k_sph = (-(np.sum(C64 ** 2, axis=1) - r64 ** 2)).astype(np.float32)

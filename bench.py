@@ -165,7 +165,10 @@ def run_reference_arm(args, wl):
         "impl": "reference", "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": float(np.mean(t_steps)) * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {wl['desc']} (bounded sample per step: {sample['sample']})"},
+        # the native arm's workload, word for word; what a step of THIS arm actually renders is in `sample`
+        "config": {"workload": f"{args.workload}: {wl['desc']}", "spheres": load_scene(wl["scene"]).n, "width": wl["width"],
+                   "height": wl["height"], "spp": wl["spp"], "depth": wl["depth"], "pass_cap": PASS_CAP,
+                   "sample": f"bounded sample per step: {sample['sample']}"},
         "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": sample["cores"], "kind": sample["kind"], "sample": sample["sample"]},
         "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,

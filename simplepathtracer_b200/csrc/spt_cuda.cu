@@ -5,6 +5,7 @@
 #include "spt_wavefront.cuh"
 #include "spt_streamed.cuh"
 #include "spt_split.cuh"
+#include "spt_tensor_filter.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -78,6 +79,10 @@ struct SptContext
     void *dProbe = nullptr;
     size_t probeBytes = 0;
     size_t maxSmemOptin = 0;
+#if SPT_TENSOR_FILTER
+    float *dTensorB = nullptr; // sphere matrix of the tensor-core filter (spt_tensor_host.hpp)
+    uint32_t tensorRows = 0;
+#endif
 };
 
 namespace
@@ -402,12 +407,31 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             dim3 const sBlock(streamed ? spt::kBlockThreads : spt::SplitShape::kThreads);
             SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
             SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+            size_t smem2 = smem;
+            dim3 sGrid2 = sGrid, sBlock2 = sBlock;
+#if SPT_TENSOR_FILTER
+            // experimental build: the resident bounce kernel takes its discriminants from the tensor core unless SPT_TENSOR=0
+            {
+                const char *knob = std::getenv("SPT_TENSOR");
+                if (!streamed && c->dTensorB && !(knob && knob[0] == '0'))
+                {
+                    p.tensorB = c->dTensorB;
+                    p.tensorRows = c->tensorRows;
+                    secondary = spt::trace_secondary_tc;
+                    sGrid2 = dim3((segW + spt::TensorShape::kTileW - 1) / spt::TensorShape::kTileW, myBands);
+                    sBlock2 = dim3(spt::TensorShape::kThreads);
+                    smem2 = ((geomBytes + pairBytes + 127) & ~size_t(127)) + spt::tensor_b_bytes(c->tensorRows) +
+                            size_t(spt::kTensorTiles) * spt::kTensorABytes;
+                    SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem2)));
+                }
+            }
+#endif
             for (uint32_t s0 = prm->sample_begin; s0 < prm->sample_end; s0 += chunk)
             {
                 p.sampleBegin = s0;
                 p.sampleEnd = std::min(prm->sample_end, s0 + chunk);
                 primary<<<sGrid, sBlock, smem, c->stream>>>(p);
-                secondary<<<sGrid, sBlock, smem, c->stream>>>(p);
+                secondary<<<sGrid2, sBlock2, smem2, c->stream>>>(p);
                 c->timing.launches += 2;
             }
             c->timing.launches -= 1; // the common tail below counts one
@@ -509,6 +533,9 @@ void spt_cuda_destroy(SptContext *c)
     cudaFree(c->dProgRgb);
     cudaFree(c->dPairsCam);
     cudaFree(c->dFirstHits);
+#if SPT_TENSOR_FILTER
+    cudaFree(c->dTensorB);
+#endif
     for (auto &e : c->ev)
         if (e)
             cudaEventDestroy(e);
@@ -598,6 +625,18 @@ int spt_cuda_set_scene(SptContext *c, const SptScene *s)
             c->hostGeom[4 * k + 3] = std::fabs(double(s->radii[i]));
         }
     }
+#if SPT_TENSOR_FILTER
+    cudaFree(c->dTensorB);
+    c->dTensorB = nullptr;
+    c->tensorRows = spt::tensor_rows(nSlots);
+    if (nSlots > 0)
+    {
+        std::vector<float> B;
+        spt::build_tensor_matrix(c->hostGeom, nSlots, B);
+        SPT_CUDA_CHECK(cudaMalloc(&c->dTensorB, B.size() * sizeof(float)));
+        SPT_CUDA_CHECK(cudaMemcpy(c->dTensorB, B.data(), B.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
+#endif
     cudaFree(c->dPairsCam);
     c->dPairsCam = nullptr;
     c->camEye[0] = c->camEye[1] = c->camEye[2] = NAN;

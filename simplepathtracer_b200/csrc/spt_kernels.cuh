@@ -63,6 +63,10 @@ struct TraceParams
     // [(y - yBegin) * segW + (x - xBegin)][sample - sampleBegin]
     float4 *firstHits;
     FilterScene filterCam; // pre-filter records specialised for the eye (camera form)
+#if SPT_TENSOR_FILTER
+    const float *tensorB;  // spt_tensor_filter.cuh: the sphere matrix in UMMA canonical layout
+    uint32_t tensorRows;   // its rows: the slots it covers padded to a multiple of 16
+#endif
 };
 
 constexpr uint32_t kMissIndex = 0xFFFFFFFFu;

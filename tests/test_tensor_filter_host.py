@@ -1,0 +1,81 @@
+"""Groundwork for the tensor-core pre-filter: EXPERIMENTAL code that the shipped library does
+not contain (-DSPT_TENSOR_FILTER=1 builds only).  What can be checked without a GPU is checked here:
+
+* tools/tensor_filter_check.cpp -- the sphere-matrix builder the experimental build uses, the ray rows restated operation for
+  operation, the UMMA canonical layout and two accumulator models that bracket the tensor core: no pair the reference's
+  separately rounded sequence accepts may be filtered out, and the error must stay inside the slack;
+* the experimental variant still compiles for sm_100a, and the DEFAULT build's device code does not change with it
+  (the macro really is off).
+"""
+import os
+import shutil
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def checker(tmp_path_factory):
+    out = str(tmp_path_factory.mktemp("tfc") / "tensor_filter_check")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-frounding-math", "-ffp-contract=off", "-o", out,
+                    os.path.join(ROOT, "tools", "tensor_filter_check.cpp")], check=True)
+    return out
+
+
+def write_scene(path, centers, radii):
+    g = np.concatenate([np.asarray(centers, np.float32).reshape(-1, 3), np.asarray(radii, np.float32).reshape(-1, 1)], axis=1)
+    with open(path, "wb") as f:
+        f.write(struct.pack("<I", len(g)))
+        f.write(np.ascontiguousarray(g, np.float32).tobytes())
+
+
+def run(checker, scene, rays):
+    r = subprocess.run([checker, scene, str(rays)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stdout.strip().endswith("OK"), r.stdout + r.stderr
+    return r.stdout
+
+
+def test_config3_scene_no_true_hit_filtered_out(checker, tmp_path):
+    z = np.load(os.path.join(ROOT, "tests", "golden", "scene_random_seed1.npz"))
+    scene = str(tmp_path / "scene.bin")
+    write_scene(scene, z["centers"].reshape(-1, 4)[:, :3], z["radii"])
+    out = run(checker, scene, 4096)
+    assert "128 on the tensor core, 128 matrix rows" in out  # 152 slots: the last 24 stay with the FFMA2 loop
+
+
+def test_short_list_is_padded_to_sixteen_rows(checker, tmp_path):
+    # 21 spheres -> 24 slots -> 32 matrix rows, the padding never a candidate; includes a negative radius (the hollow glass
+    # sphere of the reference's scenes) and centres far from the origin
+    rng = np.random.default_rng(3)
+    cen = rng.uniform(-300, 300, size=(21, 3))
+    rad = rng.uniform(0.2, 6.0, size=21)
+    rad[5] = -rad[5]
+    scene = str(tmp_path / "small.bin")
+    write_scene(scene, cen, rad)
+    out = run(checker, scene, 2048)
+    assert "24 slots (24 on the tensor core, 32 matrix rows)" in out
+
+
+@pytest.mark.skipif(shutil.which("nvcc") is None or shutil.which("cuobjdump") is None, reason="needs the CUDA toolchain")
+def test_experimental_variant_compiles_and_default_device_code_is_untouched(tmp_path):
+    import simplepathtracer_b200 as spt
+
+    shipped = spt.build_library()
+    variant = str(tmp_path / "tensor.so")
+    r = subprocess.run([os.path.join(ROOT, "tools", "build_variant.sh"), variant, "-DSPT_TENSOR_FILTER=1"], capture_output=True, text=True)
+    assert r.returncode == 0 and os.path.exists(variant), r.stderr[-2000:]
+
+    def kernels(path):
+        out = subprocess.run(["cuobjdump", "-sass", path], capture_output=True, text=True, check=True).stdout
+        return {line.split()[-1] for line in out.splitlines() if line.strip().startswith("Function :")}
+
+    base, exp = kernels(shipped), kernels(variant)
+    tc = {k for k in exp if "trace_secondary_tc" in k}
+    assert tc and not any("trace_secondary_tc" in k for k in base)
+    assert exp - tc == base  # the variant only ADDS the experimental kernel
+    sass = subprocess.run(["cuobjdump", "-sass", "-fun", next(iter(tc)), variant], capture_output=True, text=True).stdout
+    assert "UTCMMA" in sass or "UTCHMMA" in sass or "TCMMA" in sass, "no tcgen05.mma in the experimental kernel"

@@ -79,3 +79,23 @@ def test_experimental_variant_compiles_and_default_device_code_is_untouched(tmp_
     assert exp - tc == base  # the variant only ADDS the experimental kernel
     sass = subprocess.run(["cuobjdump", "-sass", "-fun", next(iter(tc)), variant], capture_output=True, text=True).stdout
     assert "UTCMMA" in sass or "UTCHMMA" in sass or "TCMMA" in sass, "no tcgen05.mma in the experimental kernel"
+
+
+def test_gpu_harness_and_scene_exporter_build(tmp_path):
+    """tools/tensor_filter_ab.cpp (the C A/B harness next round's first GPU call runs) compiles against include/spt_cuda.h, and
+    tools/export_scene.py writes the layout it reads: n | SptCamera (96 B) | centers4 | radii | colors4 | fuzz | materials."""
+    import sys
+
+    exe = str(tmp_path / "tensor_filter_ab")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-I", os.path.join(ROOT, "include"), "-o", exe,
+                    os.path.join(ROOT, "tools", "tensor_filter_ab.cpp"), "-ldl"], check=True)
+    scene = str(tmp_path / "c3.bin")
+    subprocess.run([sys.executable, os.path.join(ROOT, "tools", "export_scene.py"), scene], check=True, capture_output=True)
+    raw = open(scene, "rb").read()
+    (n,) = struct.unpack_from("<I", raw)
+    z = np.load(os.path.join(ROOT, "tests", "golden", "scene_random_seed1.npz"))
+    assert n == len(z["radii"]) and len(raw) == 4 + 96 + n * (16 + 4 + 16 + 4 + 1)
+    assert np.array_equal(np.frombuffer(raw, np.float32, n * 4, 4 + 96), z["centers"].astype(np.float32).ravel())
+    assert np.array_equal(np.frombuffer(raw, np.uint8, n, 4 + 96 + n * 40), z["materials"])
+    # without a library argument the harness refuses (exit 2) instead of touching a GPU
+    assert subprocess.run([exe]).returncode == 2

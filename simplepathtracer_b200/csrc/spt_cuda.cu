@@ -421,7 +421,7 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
                     sGrid2 = dim3((segW + spt::TensorShape::kTileW - 1) / spt::TensorShape::kTileW, myBands);
                     sBlock2 = dim3(spt::TensorShape::kThreads);
                     smem2 = ((geomBytes + pairBytes + 127) & ~size_t(127)) + spt::tensor_b_bytes(c->tensorRows) +
-                            size_t(spt::kTensorTiles) * spt::kTensorABytes;
+                            size_t(spt::kTensorAcc) * spt::kTensorABytes;
                     SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem2)));
                 }
             }

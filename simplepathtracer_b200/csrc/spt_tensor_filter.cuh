@@ -13,6 +13,9 @@
 // (profiles/r1_microbench_umma_filter.txt: no true hit missed; 4.1 - 4.9 T (ray, sphere) pairs/s).  THIS kernel compiles and its
 // host half is checked on the CPU, but it has not run on a GPU yet (round 1 had no GPU minutes left): DESIGN.md section 9, item 1.
 // Budget per SM with two tiles per CTA and two CTAs: 16 warps, 4 x 128 = 512 tensor-memory columns, ~180 KB shared memory.
+// Measured (profiles/r1_ab_tensor_filter.txt): bit-identical, but 9 % slower than the FFMA2 kernel on config 3 -- 16 warps per SM
+// do not hide the latencies 32 did.  Hence the time-shared variant below (-DSPT_TENSOR_TILES=4 -DSPT_TENSOR_ACC=2: 32 warps per SM
+// at 64 registers, the tiles of a CTA taking turns on two accumulators), which compiles (4 bytes of spill) and has NOT run yet.
 #pragma once
 
 #if SPT_TENSOR_FILTER
@@ -26,9 +29,19 @@ namespace spt
 #ifndef SPT_TENSOR_TILES
 #define SPT_TENSOR_TILES 2
 #endif
+#ifndef SPT_TENSOR_ACC
+#define SPT_TENSOR_ACC SPT_TENSOR_TILES
+#endif
 constexpr int kTensorTiles = SPT_TENSOR_TILES;
-static_assert(kTensorTiles == 1 || kTensorTiles == 2, "one or two ray tiles per CTA");
-using TensorShape = BlockShape<2 * kTensorTiles, 2>; // 16x8 or 32x8 pixels
+// Accumulators (128 tensor-memory columns + one ray matrix each) per CTA.  Equal to the tile count: every tile owns one.  Fewer:
+// the tiles TIME-SHARE them -- an accumulator is busy only from the row stores to the last tcgen05.ld of an iteration, a fraction
+// of it -- which is how more than 16 warps per SM fit behind 512 columns (-DSPT_TENSOR_TILES=4 -DSPT_TENSOR_ACC=2: two CTAs of
+// sixteen warps at 64 registers).
+constexpr int kTensorAcc = SPT_TENSOR_ACC;
+constexpr bool kTensorTimeShared = kTensorAcc < kTensorTiles;
+static_assert(kTensorTiles == 1 || kTensorTiles == 2 || kTensorTiles == 4, "one, two or four ray tiles per CTA");
+static_assert((kTensorAcc == 1 || kTensorAcc == 2 || kTensorAcc == 4) && kTensorAcc <= kTensorTiles, "accumulators per CTA");
+using TensorShape = BlockShape<2 * kTensorTiles, 2>; // 16x8, 32x8 or 64x8 pixels
 static_assert(TensorShape::kThreads == int(kTensorRays) * kTensorTiles, "one thread per tensor-memory lane");
 
 // UMMA shared-memory descriptor, K-major, SWIZZLE_NONE: start >> 4 in [0,14), LBO >> 4 in [16,30), SBO >> 4 in [32,46), version 1
@@ -95,10 +108,51 @@ __device__ __forceinline__ uint32_t tmem_signs32(uint32_t taddr)
     return ~mask;
 }
 
+// accumulator bookkeeping of a CTA whose tiles time-share them (kTensorTimeShared)
+struct TensorPool
+{
+    uint32_t freeMask;            // bit a set <=> accumulator a is free
+    uint32_t holder[4];           // per tile: the accumulator its current iteration holds (written by the tile's first thread)
+    uint32_t readers[4];          // per accumulator: warps of the holding tile that have finished reading it
+};
+// first thread of a tile: take a free accumulator (spins; holders never wait on anything but their own tile, so it frees up)
+__device__ __forceinline__ uint32_t pool_acquire(TensorPool *pool)
+{
+    for (;;)
+    {
+        uint32_t const m = *reinterpret_cast<volatile uint32_t *>(&pool->freeMask);
+        if (m)
+        {
+            uint32_t const a = uint32_t(__ffs(int(m))) - 1u;
+            if (atomicCAS(&pool->freeMask, m, m & ~(1u << a)) == m)
+                return a;
+        }
+        else
+            __nanosleep(100);
+    }
+}
+// every warp of the holding tile, once its tcgen05.ld have completed: the last of the four hands the accumulator back
+__device__ __forceinline__ void pool_release(TensorPool *pool, uint32_t a)
+{
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncwarp();
+    if ((threadIdx.x & 31u) == 0u)
+    {
+        __threadfence_block();
+        if (atomicAdd(&pool->readers[a], 1u) == kTensorRays / 32u - 1u)
+        {
+            atomicExch(&pool->readers[a], 0u);
+            __threadfence_block();
+            atomicOr(&pool->freeMask, 1u << a);
+        }
+    }
+}
+
 // what a ray tile needs to run the tensor filter
 struct TensorFilter
 {
-    float *sA;       // the tile's rows (kTensorABytes), 128-byte aligned
+    float *sA;       // the tile's rows (kTensorABytes), 128-byte aligned; time-shared: ray matrix of accumulator 0
+    TensorPool *pool; // time-shared accumulators only
     uint32_t bAddr;  // shared-memory address of the sphere matrix
     uint32_t bLbo;
     uint32_t rows;   // of the sphere matrix = N: multiple of 16, <= kTensorCols
@@ -138,17 +192,29 @@ __device__ __forceinline__ uint32_t closest_hit_tensor(const FilterScene &fs, Ge
     float minDistanceSq = FLT_MAX;
     float const od = vdot(org, dir);
     uint32_t const lane = threadIdx.x & (kTensorRays - 1u);
-    tensor_store_ray(T.sA, lane, dir, org, od);
+    float *sA = T.sA;
+    uint32_t tmem = T.tmem, held = 0u;
+    if (kTensorTimeShared)
+    {
+        if (lane == 0)
+            T.pool->holder[T.tile] = pool_acquire(T.pool);
+        __syncwarp(); // bar.sync is warp-aligned: the spinning lane has to be back
+        tile_sync(T.tile);
+        held = *reinterpret_cast<volatile uint32_t *>(&T.pool->holder[T.tile]);
+        sA += held * (kTensorABytes / 4u);
+        tmem += held * kTensorCols;
+    }
+    tensor_store_ray(sA, lane, dir, org, od);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> visible to the tensor core
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); // this thread's earlier tcgen05.ld are done with the accumulator
     tile_sync(T.tile);
     if (lane == 0)
     {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        uint32_t const aAddr = smem_addr(T.sA), idesc = umma_idesc_tf32(kTensorRays, T.rows);
+        uint32_t const aAddr = smem_addr(sA), idesc = umma_idesc_tf32(kTensorRays, T.rows);
 #pragma unroll
         for (uint32_t ks = 0; ks < kTensorK / 8u; ++ks) // one UMMA K step = 8 TF32 = two 16-byte chunks
-            umma_tf32(T.tmem, umma_desc(aAddr + ks * 2u * kTensorALbo, kTensorALbo, 128u),
+            umma_tf32(tmem, umma_desc(aAddr + ks * 2u * kTensorALbo, kTensorALbo, 128u),
                       umma_desc(T.bAddr + ks * 2u * T.bLbo, T.bLbo, 128u), idesc, ks > 0u ? 1u : 0u);
         umma_commit(T.bar);
     }
@@ -165,7 +231,7 @@ __device__ __forceinline__ uint32_t closest_hit_tensor(const FilterScene &fs, Ge
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
     // ---- this warp's 32 lanes: sign bits per 32-slot word (at most four: one resolution round), then the exact sequence ----
-    uint32_t const lanes = T.tmem + ((((threadIdx.x >> 5) & 3u) * 32u) << 16);
+    uint32_t const lanes = tmem + ((((threadIdx.x >> 5) & 3u) * 32u) << 16);
     uint32_t const nWords = (T.slots + 31u) / 32u;
     uint32_t c0 = 0u, c1 = 0u, c2 = 0u, c3 = 0u;
 #pragma unroll 1
@@ -181,19 +247,22 @@ __device__ __forceinline__ uint32_t closest_hit_tensor(const FilterScene &fs, Ge
         c1 = c0;
         c0 = live ? cw : 0u;
     }
+    if (kTensorTimeShared)
+        pool_release(T.pool, held); // the masks are in registers: the accumulator is free while the candidates are resolved
     resolve_candidates(c0, c1, c2, c3, nWords, fs.slotIdx, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals);
     return minIndex;
 }
 
 // trace_secondary<2, S> with closest_hit_tensor.  Dynamic shared memory: [geometry | filter blob | pad to 128 | sphere matrix |
-// kTensorTiles ray matrices].  Each ray tile's loop is tile-uniform (barrier inside the closest hit).
-__global__ void __launch_bounds__(TensorShape::kThreads, 2) trace_secondary_tc(const __grid_constant__ TraceParams p)
+// kTensorAcc ray matrices].  Each ray tile's loop is tile-uniform (barrier inside the closest hit).
+__global__ void __launch_bounds__(TensorShape::kThreads, kTensorTimeShared ? 512 / (kTensorCols * kTensorAcc) : 2) trace_secondary_tc(const __grid_constant__ TraceParams p)
 {
     using S = TensorShape;
     extern __shared__ __align__(128) unsigned char smemTensor[];
     __shared__ __align__(8) uint64_t mbar;
     __shared__ __align__(8) uint64_t mmaBar[kTensorTiles];
     __shared__ uint32_t tmemBase;
+    __shared__ TensorPool pool;
     __shared__ ShellSlots shellSlots[S::kThreads / 32];
     ShellSlots &slots = shellSlots[threadIdx.x >> 5];
     __shared__ LaneStashT<S::kThreads> stash;
@@ -212,12 +281,15 @@ __global__ void __launch_bounds__(TensorShape::kThreads, 2) trace_secondary_tc(c
     {
         for (int t = 0; t < kTensorTiles; ++t)
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&mmaBar[t])));
+        pool.freeMask = (1u << kTensorAcc) - 1u;
+        for (int a = 0; a < 4; ++a)
+            pool.readers[a] = pool.holder[a] = 0u;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if ((threadIdx.x >> 5) == 0)
     {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(&tmemBase)),
-                     "n"(kTensorCols * kTensorTiles));
+                     "n"(kTensorCols * kTensorAcc));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // the sphere matrix was written with generic stores
@@ -226,12 +298,13 @@ __global__ void __launch_bounds__(TensorShape::kThreads, 2) trace_secondary_tc(c
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     TensorFilter T;
     T.tile = threadIdx.x / kTensorRays;
-    T.sA = reinterpret_cast<float *>(smemTensor + bOff + bBytes + T.tile * kTensorABytes);
+    T.sA = reinterpret_cast<float *>(smemTensor + bOff + bBytes + (kTensorTimeShared ? 0u : T.tile * kTensorABytes));
+    T.pool = &pool;
     T.bAddr = smem_addr(smemTensor + bOff);
     T.bLbo = tensor_b_lbo(p.tensorRows);
     T.rows = p.tensorRows;
     T.slots = tensor_slots(p.filter.nSlots);
-    T.tmem = tmemBase + T.tile * kTensorCols;
+    T.tmem = tmemBase + (kTensorTimeShared ? 0u : T.tile * kTensorCols);
     T.bar = smem_addr(&mmaBar[T.tile]);
     T.phase = 0u;
 
@@ -318,7 +391,7 @@ __global__ void __launch_bounds__(TensorShape::kThreads, 2) trace_secondary_tc(c
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads(); // both tiles are done with tensor memory
     if ((threadIdx.x >> 5) == 0)
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmemBase), "n"(kTensorCols * kTensorTiles));
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmemBase), "n"(kTensorCols * kTensorAcc));
 }
 
 } // namespace spt

@@ -81,6 +81,22 @@ def test_experimental_variant_compiles_and_default_device_code_is_untouched(tmp_
     assert "UTCMMA" in sass or "UTCHMMA" in sass or "TCMMA" in sass, "no tcgen05.mma in the experimental kernel"
 
 
+@pytest.mark.skipif(shutil.which("nvcc") is None, reason="needs the CUDA toolchain")
+def test_time_shared_variant_fits_sixty_four_registers(tmp_path):
+    # four ray tiles taking turns on two accumulators: 2 CTAs x 16 warps per SM only if ptxas stays within 64 registers
+    variant = str(tmp_path / "tensor42.so")
+    r = subprocess.run([os.path.join(ROOT, "tools", "build_variant.sh"), variant, "-DSPT_TENSOR_FILTER=1", "-DSPT_TENSOR_TILES=4",
+                        "-DSPT_TENSOR_ACC=2", "-Xptxas", "-v"], capture_output=True, text=True)
+    assert r.returncode == 0 and os.path.exists(variant), r.stderr[-2000:]
+    lines = r.stderr.splitlines()
+    at = next(i for i, l in enumerate(lines) if "Compiling entry function" in l and "trace_secondary_tc" in l)
+    info = " ".join(lines[at:at + 4])
+    import re
+
+    assert int(re.search(r"Used (\d+) registers", info).group(1)) <= 64, info
+    assert int(re.search(r"(\d+) bytes spill stores", info).group(1)) <= 16, info
+
+
 def test_gpu_harness_and_scene_exporter_build(tmp_path):
     """tools/tensor_filter_ab.cpp (the C A/B harness next round's first GPU call runs) compiles against include/spt_cuda.h, and
     tools/export_scene.py writes the layout it reads: n | SptCamera (96 B) | centers4 | radii | colors4 | fuzz | materials."""

@@ -2,7 +2,10 @@
 # GPU session for the EXPERIMENTAL tensor-core bounce kernel (spt_tensor_filter.cuh).
 #   here (no GPU needed):  tools/build_variant.sh build_ab/base.so
 #                          tools/build_variant.sh build_ab/tensor.so  -DSPT_TENSOR_FILTER=1
-#                          tools/build_variant.sh build_ab/tensor1.so -DSPT_TENSOR_FILTER=1 -DSPT_TENSOR_TILES=1     (optional)
+#                          tools/build_variant.sh build_ab/tensor42.so -DSPT_TENSOR_FILTER=1 -DSPT_TENSOR_TILES=4 -DSPT_TENSOR_ACC=2
+#                          tools/build_variant.sh build_ab/tensor21.so -DSPT_TENSOR_FILTER=1 -DSPT_TENSOR_TILES=2 -DSPT_TENSOR_ACC=1
+#                            (time-shared accumulators, 32 / 24 warps per SM at 64 registers: NOT run yet -- the harness below is
+#                             their first contact, each under its own timeout; a variant that fails is dropped, the rest go on)
 #                          g++ -O2 -std=c++17 -I include -o build_ab/tensor_filter_ab tools/tensor_filter_ab.cpp -ldl
 #                          python tools/export_scene.py build_ab/c3_scene.bin
 #   then:                  gpurun --timeout 1200 -- tools/tensor_filter_gpu.sh
@@ -14,21 +17,22 @@
 #    everything above has exited 0 without ncu.  Numbers printed under ncu are not measurements.
 set -u
 mkdir -p gpurun_out
-for lib in build_ab/tensor.so build_ab/tensor1.so; do
+good=
+for lib in build_ab/tensor.so build_ab/tensor42.so build_ab/tensor21.so; do
   [ -f "$lib" ] || continue
   out=gpurun_out/ab_$(basename "$lib" .so)_c3.txt
   timeout 60 build_ab/tensor_filter_ab "$lib" build_ab/c3_scene.bin 3840 2160 64 50 3 > "$out" 2>&1
   rc=$?; echo "rc=$rc" >> "$out"; tail -9 "$out"
-  [ $rc -eq 0 ] || exit $rc
+  [ $rc -eq 0 ] && good="$good $lib"
 done
-for lib in build_ab/tensor.so build_ab/tensor1.so; do
-  [ -f "$lib" ] || continue
+[ -n "$good" ] || exit 1
+for lib in $good; do
   log=gpurun_out/pytest_$(basename "$lib" .so).log
   SPT_CUDA_LIB=$PWD/$lib timeout 420 python -m pytest tests -m gpu -x -q > "$log" 2>&1
   rc=$?; echo "pytest rc=$rc ($lib)" | tee -a "$log"; tail -3 "$log"
   [ $rc -eq 0 ] || exit $rc
 done
-libs="build_ab/base.so build_ab/tensor.so"; [ -f build_ab/tensor1.so ] && libs="$libs build_ab/tensor1.so"
+libs="build_ab/base.so$good"
 tools/ab_run.sh c3 gpurun_out/ab_tensor_c3.txt $libs $libs
 tools/ab_run.sh c4 gpurun_out/ab_tensor_c4.txt $libs
 # one launch of each bounce kernel at 1920x1080, 32 spp (ncu replays a kernel ~40 times: keep it short)

@@ -47,6 +47,23 @@ def test_config3_scene_no_true_hit_filtered_out(checker, tmp_path):
     assert "128 on the tensor core, 128 matrix rows" in out  # 152 slots: the last 24 stay with the FFMA2 loop
 
 
+@pytest.mark.parametrize("name", ["scene_random_seed2", "scene_init_seed1"])
+def test_other_golden_scenes(checker, tmp_path, name):
+    z = np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))
+    scene = str(tmp_path / "scene.bin")
+    write_scene(scene, z["centers"].reshape(-1, 4)[:, :3], z["radii"])
+    run(checker, scene, 2048)
+
+
+def test_centres_and_radii_near_the_filter_limits(checker, tmp_path):
+    # |C| up to ~4000 (kBigCentre 4096) and radii up to 60 (kBigRadius 64): the error scales with A^2 + B^2 + r^2 and so does the slack
+    rng = np.random.default_rng(9)
+    scene = str(tmp_path / "far.bin")
+    write_scene(scene, rng.uniform(-2300, 2300, size=(120, 3)), rng.uniform(0.5, 60, size=120))
+    out = run(checker, scene, 2048)
+    assert "120 slots (120 on the tensor core, 128 matrix rows)" in out
+
+
 def test_short_list_is_padded_to_sixteen_rows(checker, tmp_path):
     # 21 spheres -> 24 slots -> 32 matrix rows, the padding never a candidate; includes a negative radius (the hollow glass
     # sphere of the reference's scenes) and centres far from the origin

@@ -37,6 +37,10 @@ constexpr int kTensorTiles = SPT_TENSOR_TILES;
 // the tiles TIME-SHARE them -- an accumulator is busy only from the row stores to the last tcgen05.ld of an iteration, a fraction
 // of it -- which is how more than 16 warps per SM fit behind 512 columns (-DSPT_TENSOR_TILES=4 -DSPT_TENSOR_ACC=2: two CTAs of
 // sixteen warps at 64 registers).
+#ifndef SPT_TENSOR_MERGED_BARRIER
+#define SPT_TENSOR_MERGED_BARRIER 0 // 1: the loop's "any lane of the tile alive?" reduction rides on a barrier the closest hit has anyway
+#endif
+constexpr bool kTensorMergedBarrier = SPT_TENSOR_MERGED_BARRIER != 0;
 constexpr int kTensorAcc = SPT_TENSOR_ACC;
 constexpr bool kTensorTimeShared = kTensorAcc < kTensorTiles;
 static_assert(kTensorTiles == 1 || kTensorTiles == 2 || kTensorTiles == 4, "one, two or four ray tiles per CTA");
@@ -184,10 +188,13 @@ __device__ __forceinline__ void tensor_store_ray(float *sA, uint32_t lane, V3 di
 
 // FindClosestIntersectionSphere with the discriminant of the first T.slots slots from the tensor core.  Must be called by ALL
 // threads of the ray tile (a tile-wide barrier inside); `live` = false marks a lane that only keeps the others company.
+// kTensorMergedBarrier: `alive` (the lane has a path in flight or samples left) is OR-reduced over the tile on the first barrier;
+// when nobody is, anyAlive comes back false, nothing was traced and the caller leaves its loop (tile-uniformly).
 template <typename GeomPtr>
 __device__ __forceinline__ uint32_t closest_hit_tensor(const FilterScene &fs, GeomPtr geom, uint32_t n, V3 dir, V3 org, TensorFilter &T,
-                                                       uint32_t &exactEvals, bool live)
+                                                       uint32_t &exactEvals, bool live, bool alive, bool &anyAlive)
 {
+    anyAlive = true;
     uint32_t minIndex = n;
     float minDistanceSq = FLT_MAX;
     float const od = vdot(org, dir);
@@ -199,15 +206,31 @@ __device__ __forceinline__ uint32_t closest_hit_tensor(const FilterScene &fs, Ge
         if (lane == 0)
             T.pool->holder[T.tile] = pool_acquire(T.pool);
         __syncwarp(); // bar.sync is warp-aligned: the spinning lane has to be back
-        tile_sync(T.tile);
+        if (kTensorMergedBarrier)
+            anyAlive = tile_sync_or(T.tile, alive);
+        else
+            tile_sync(T.tile);
         held = *reinterpret_cast<volatile uint32_t *>(&T.pool->holder[T.tile]);
+        if (!anyAlive)
+        {
+            if (lane == 0)
+                atomicOr(&T.pool->freeMask, 1u << held); // taken but never used
+            return n;
+        }
         sA += held * (kTensorABytes / 4u);
         tmem += held * kTensorCols;
     }
     tensor_store_ray(sA, lane, dir, org, od);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> visible to the tensor core
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); // this thread's earlier tcgen05.ld are done with the accumulator
-    tile_sync(T.tile);
+    if (kTensorMergedBarrier && !kTensorTimeShared)
+    {
+        anyAlive = tile_sync_or(T.tile, alive);
+        if (!anyAlive)
+            return n;
+    }
+    else
+        tile_sync(T.tile);
     if (lane == 0)
     {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -366,12 +389,15 @@ __global__ void __launch_bounds__(TensorShape::kThreads, kTensorTimeShared ? 512
             kind = fk;
             idx = h;
         }
-        if (!tile_sync_or(T.tile, live)) // tile-uniform: the closest hit below has a tile-wide barrier
+        if (!kTensorMergedBarrier && !tile_sync_or(T.tile, live)) // tile-uniform: the closest hit below has a tile-wide barrier
             break;
         shade_surface(p, geom, L, idx, kind, dropped, slots, acc); // warp collective (coop_shell); every warp of the tile is here
         bool const needTrace = live && L.mode != MODE_NEW;
         stash_lane(stash, L);
-        idx = closest_hit_tensor(fs, geom, p.n, L.dir, L.org, T, exactEvals, needTrace);
+        bool anyAlive;
+        idx = closest_hit_tensor(fs, geom, p.n, L.dir, L.org, T, exactEvals, needTrace, live, anyAlive);
+        if (!anyAlive) // kTensorMergedBarrier only: every lane of the tile has finished its pixel
+            break;
         unstash_lane(stash, L);
         segments += needTrace ? 1u : 0u;
         traced = needTrace;

@@ -4,7 +4,9 @@
 #                          tools/build_variant.sh build_ab/tensor.so  -DSPT_TENSOR_FILTER=1
 #                          tools/build_variant.sh build_ab/tensor42.so -DSPT_TENSOR_FILTER=1 -DSPT_TENSOR_TILES=4 -DSPT_TENSOR_ACC=2
 #                          tools/build_variant.sh build_ab/tensor21.so -DSPT_TENSOR_FILTER=1 -DSPT_TENSOR_TILES=2 -DSPT_TENSOR_ACC=1
-#                            (time-shared accumulators, 32 / 24 warps per SM at 64 registers: NOT run yet -- the harness below is
+#                          tools/build_variant.sh build_ab/tensorm.so   -DSPT_TENSOR_FILTER=1 -DSPT_TENSOR_MERGED_BARRIER=1
+#                          tools/build_variant.sh build_ab/tensor42m.so -DSPT_TENSOR_FILTER=1 -DSPT_TENSOR_TILES=4 -DSPT_TENSOR_ACC=2 -DSPT_TENSOR_MERGED_BARRIER=1
+#                            (time-shared accumulators, 32 / 24 warps per SM at 64 registers; one tile barrier less per iteration: NOT run yet -- the harness below is
 #                             their first contact, each under its own timeout; a variant that fails is dropped, the rest go on)
 #                          g++ -O2 -std=c++17 -I include -o build_ab/tensor_filter_ab tools/tensor_filter_ab.cpp -ldl
 #                          python tools/export_scene.py build_ab/c3_scene.bin
@@ -18,7 +20,7 @@
 set -u
 mkdir -p gpurun_out
 good=
-for lib in build_ab/tensor.so build_ab/tensor42.so build_ab/tensor21.so; do
+for lib in build_ab/tensor.so build_ab/tensorm.so build_ab/tensor42.so build_ab/tensor42m.so build_ab/tensor21.so; do
   [ -f "$lib" ] || continue
   out=gpurun_out/ab_$(basename "$lib" .so)_c3.txt
   timeout 60 build_ab/tensor_filter_ab "$lib" build_ab/c3_scene.bin 3840 2160 64 50 3 > "$out" 2>&1

@@ -81,6 +81,7 @@ struct SptContext
     size_t maxSmemOptin = 0;
 #if SPT_TENSOR_FILTER
     float *dTensorB = nullptr; // sphere matrix of the tensor-core filter (spt_tensor_host.hpp)
+    float *dTensorBCam = nullptr; // its camera form, rebuilt with the camera blob when the eye changes
     uint32_t tensorRows = 0;
 #endif
 };
@@ -206,6 +207,17 @@ int ensure_camera_blob(SptContext *c, const float eye[3])
     SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream)); // an earlier launch may still read the previous camera's records
     if (!blob.empty())
         SPT_CUDA_CHECK(cudaMemcpy(c->dPairsCam, blob.data(), blob.size(), cudaMemcpyHostToDevice));
+#if SPT_TENSOR_FILTER
+    if (nSlots > 0)
+    {
+        std::vector<float> B;
+        double const e[3] = {ex, ey, ez};
+        spt::build_tensor_matrix_cam(c->hostGeom, nSlots, e, B);
+        if (!c->dTensorBCam)
+            SPT_CUDA_CHECK(cudaMalloc(&c->dTensorBCam, B.size() * sizeof(float)));
+        SPT_CUDA_CHECK(cudaMemcpy(c->dTensorBCam, B.data(), B.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
+#endif
     c->camEye[0] = eye[0];
     c->camEye[1] = eye[1];
     c->camEye[2] = eye[2];
@@ -407,8 +419,8 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             dim3 const sBlock(streamed ? spt::kBlockThreads : spt::SplitShape::kThreads);
             SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
             SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-            size_t smem2 = smem;
-            dim3 sGrid2 = sGrid, sBlock2 = sBlock;
+            size_t smem2 = smem, smem1 = smem;
+            dim3 sGrid2 = sGrid, sBlock2 = sBlock, sGrid1 = sGrid, sBlock1 = sBlock;
 #if SPT_TENSOR_FILTER
             // experimental build: the resident bounce kernel takes its discriminants from the tensor core unless SPT_TENSOR=0
             {
@@ -424,13 +436,26 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
                             size_t(spt::kTensorAcc) * spt::kTensorABytes;
                     SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem2)));
                 }
+                // ... and the camera kernel unless SPT_TENSOR_PRIMARY=0
+                knob = std::getenv("SPT_TENSOR_PRIMARY");
+                if (!streamed && c->dTensorBCam && !(knob && knob[0] == '0'))
+                {
+                    p.tensorBCam = c->dTensorBCam;
+                    p.tensorRows = c->tensorRows;
+                    primary = spt::primary_hits_tc;
+                    sGrid1 = dim3((segW + spt::TensorShape::kTileW - 1) / spt::TensorShape::kTileW, myBands);
+                    sBlock1 = dim3(spt::TensorShape::kThreads);
+                    smem1 = ((geomBytes + pairBytes + 127) & ~size_t(127)) + spt::tensor_b_bytes_cam(c->tensorRows) +
+                            size_t(spt::kTensorAcc) * spt::kTensorABytesCam;
+                    SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem1)));
+                }
             }
 #endif
             for (uint32_t s0 = prm->sample_begin; s0 < prm->sample_end; s0 += chunk)
             {
                 p.sampleBegin = s0;
                 p.sampleEnd = std::min(prm->sample_end, s0 + chunk);
-                primary<<<sGrid, sBlock, smem, c->stream>>>(p);
+                primary<<<sGrid1, sBlock1, smem1, c->stream>>>(p);
                 secondary<<<sGrid2, sBlock2, smem2, c->stream>>>(p);
                 c->timing.launches += 2;
             }
@@ -535,6 +560,7 @@ void spt_cuda_destroy(SptContext *c)
     cudaFree(c->dFirstHits);
 #if SPT_TENSOR_FILTER
     cudaFree(c->dTensorB);
+    cudaFree(c->dTensorBCam);
 #endif
     for (auto &e : c->ev)
         if (e)
@@ -627,7 +653,8 @@ int spt_cuda_set_scene(SptContext *c, const SptScene *s)
     }
 #if SPT_TENSOR_FILTER
     cudaFree(c->dTensorB);
-    c->dTensorB = nullptr;
+    cudaFree(c->dTensorBCam); // sized by the scene; ensure_camera_blob rebuilds it (camEye is reset below)
+    c->dTensorB = c->dTensorBCam = nullptr;
     c->tensorRows = spt::tensor_rows(nSlots);
     if (nSlots > 0)
     {

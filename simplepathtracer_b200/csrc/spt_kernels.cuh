@@ -66,6 +66,7 @@ struct TraceParams
 #if SPT_TENSOR_FILTER
     const float *tensorB;  // spt_tensor_filter.cuh: the sphere matrix in UMMA canonical layout
     uint32_t tensorRows;   // its rows: the slots it covers padded to a multiple of 16
+    const float *tensorBCam; // the camera form of the matrix for this launch's eye (primary_hits_tc)
 #endif
 };
 

@@ -16,6 +16,9 @@
 // Measured (profiles/r1_ab_tensor_filter.txt): bit-identical, but 9 % slower than the FFMA2 kernel on config 3 -- 16 warps per SM
 // do not hide the latencies 32 did.  Hence the time-shared variant below (-DSPT_TENSOR_TILES=4 -DSPT_TENSOR_ACC=2: 32 warps per SM
 // at 64 registers, the tiles of a CTA taking turns on two accumulators), which compiles (4 bytes of spill) and has NOT run yet.
+// Also NOT run yet: primary_hits_tc, the camera kernel in the same mould (camera form: K = 32, six products of the direction +
+// the constant).  It should suit the tensor core better than the bounce kernel does: convergent by construction, no shading
+// between closest hits, and ~500 issue cycles per 32 rays instead of ~840 for the FFMA2 camera loop alone.
 #pragma once
 
 #if SPT_TENSOR_FILTER
@@ -186,11 +189,32 @@ __device__ __forceinline__ void tensor_store_ray(float *sA, uint32_t lane, V3 di
     }
 }
 
-// FindClosestIntersectionSphere with the discriminant of the first T.slots slots from the tensor core.  Must be called by ALL
+// Camera form (spt_tensor_host.hpp, build_tensor_matrix_cam): the six products of the direction, head / tail.  Chunks 6 and 7 of
+// a row are constants, written once per launch by tensor_init_rows_cam.
+__device__ __forceinline__ void tensor_store_ray_cam(float *sA, uint32_t lane, V3 dir)
+{
+    float const f[6] = {fmul(dir.x, dir.x), fmul(dir.x, dir.y), fmul(dir.x, dir.z), fmul(dir.y, dir.y), fmul(dir.y, dir.z), fmul(dir.z, dir.z)};
+    float *row = sA + (lane >> 3) * 32 + (lane & 7) * 4;
+#pragma unroll
+    for (int c = 0; c < 6; ++c)
+    {
+        float const h = __uint_as_float(__float_as_uint(f[c]) & 0xFFFFE000u), l = fsub(f[c], h);
+        sts128(reinterpret_cast<float4 *>(row + c * (kTensorALbo / 4)), make_float4(h, l, h, l));
+    }
+}
+__device__ __forceinline__ void tensor_init_rows_cam(float *sA, uint32_t lane)
+{
+    float *row = sA + (lane >> 3) * 32 + (lane & 7) * 4;
+    sts128(reinterpret_cast<float4 *>(row + 6 * (kTensorALbo / 4)), make_float4(1.f, 1.f, 0.f, 0.f));
+    sts128(reinterpret_cast<float4 *>(row + 7 * (kTensorALbo / 4)), make_float4(0.f, 0.f, 0.f, 0.f));
+}
+
+// FindClosestIntersectionSphere with the discriminant of the first T.slots slots from the tensor core.  CAM: the camera form
+// (org = the eye the matrix and `fs` were specialised for).  Must be called by ALL
 // threads of the ray tile (a tile-wide barrier inside); `live` = false marks a lane that only keeps the others company.
 // kTensorMergedBarrier: `alive` (the lane has a path in flight or samples left) is OR-reduced over the tile on the first barrier;
 // when nobody is, anyAlive comes back false, nothing was traced and the caller leaves its loop (tile-uniformly).
-template <typename GeomPtr>
+template <bool CAM = false, typename GeomPtr>
 __device__ __forceinline__ uint32_t closest_hit_tensor(const FilterScene &fs, GeomPtr geom, uint32_t n, V3 dir, V3 org, TensorFilter &T,
                                                        uint32_t &exactEvals, bool live, bool alive, bool &anyAlive)
 {
@@ -217,10 +241,13 @@ __device__ __forceinline__ uint32_t closest_hit_tensor(const FilterScene &fs, Ge
                 atomicOr(&T.pool->freeMask, 1u << held); // taken but never used
             return n;
         }
-        sA += held * (kTensorABytes / 4u);
+        sA += held * ((CAM ? kTensorABytesCam : kTensorABytes) / 4u);
         tmem += held * kTensorCols;
     }
-    tensor_store_ray(sA, lane, dir, org, od);
+    if (CAM)
+        tensor_store_ray_cam(sA, lane, dir);
+    else
+        tensor_store_ray(sA, lane, dir, org, od);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> visible to the tensor core
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); // this thread's earlier tcgen05.ld are done with the accumulator
     if (kTensorMergedBarrier && !kTensorTimeShared)
@@ -236,7 +263,7 @@ __device__ __forceinline__ uint32_t closest_hit_tensor(const FilterScene &fs, Ge
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         uint32_t const aAddr = smem_addr(sA), idesc = umma_idesc_tf32(kTensorRays, T.rows);
 #pragma unroll
-        for (uint32_t ks = 0; ks < kTensorK / 8u; ++ks) // one UMMA K step = 8 TF32 = two 16-byte chunks
+        for (uint32_t ks = 0; ks < (CAM ? kTensorKCam : kTensorK) / 8u; ++ks) // one UMMA K step = 8 TF32 = two 16-byte chunks
             umma_tf32(tmem, umma_desc(aAddr + ks * 2u * kTensorALbo, kTensorALbo, 128u),
                       umma_desc(T.bAddr + ks * 2u * T.bLbo, T.bLbo, 128u), idesc, ks > 0u ? 1u : 0u);
         umma_commit(T.bar);
@@ -245,9 +272,9 @@ __device__ __forceinline__ uint32_t closest_hit_tensor(const FilterScene &fs, Ge
     exact_big_spheres(fs, geom, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
     if (fs.nSlots > T.slots) // T.slots == kTensorCols here: a whole number of words
     {
-        FilterRay const fr = make_filter_ray(dir, org, od, fs.amax);
-        filter_span(fs.pairs + T.slots / 2u, fs.slotIdx + T.slots, fs.nSlots - T.slots, fr, geom, n, dir, org, od, minIndex, minDistanceSq,
-                    exactEvals, live);
+        FilterRay const fr = CAM ? make_filter_ray_cam(dir, od, fs.epsTCam) : make_filter_ray(dir, org, od, fs.amax);
+        filter_span<CAM>(fs.pairs + T.slots / 2u, fs.slotIdx + T.slots, fs.nSlots - T.slots, fr, geom, n, dir, org, od, minIndex,
+                         minDistanceSq, exactEvals, live);
     }
     tensor_mbar_wait(T.bar, T.phase);
     T.phase ^= 1u;
@@ -416,6 +443,103 @@ __global__ void __launch_bounds__(TensorShape::kThreads, kTensorTimeShared ? 512
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads(); // both tiles are done with tensor memory
+    if ((threadIdx.x >> 5) == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmemBase), "n"(kTensorCols * kTensorAcc));
+}
+
+// primary_hits_kernel<2, S> with the camera form on the tensor core: one camera sample per lane and trip (the FFMA2 kernel takes
+// two, to halve its shared-memory traffic -- no such traffic here), every tile of the CTA in step with itself only.  The loop
+// is convergent by construction (same trip count for every lane), which is what the tile barriers want.  Dynamic shared
+// memory: [geometry | camera filter blob | pad to 128 | camera sphere matrix | kTensorAcc ray matrices].
+__global__ void __launch_bounds__(TensorShape::kThreads, kTensorTimeShared ? 512 / (kTensorCols * kTensorAcc) : 2) primary_hits_tc(const __grid_constant__ TraceParams p)
+{
+    using S = TensorShape;
+    extern __shared__ __align__(128) unsigned char smemTensor[];
+    __shared__ __align__(8) uint64_t mbar;
+    __shared__ __align__(8) uint64_t mmaBar[kTensorTiles];
+    __shared__ uint32_t tmemBase;
+    __shared__ TensorPool pool;
+
+    uint32_t const geomBytes = p.n * uint32_t(sizeof(float4));
+    uint32_t const blobBytes = filter_blob_bytes(p.filterCam.nSlots);
+    stage_scene_tma(smemTensor, p.geom, geomBytes, smemTensor + geomBytes, p.filterCam.pairs, blobBytes, &mbar);
+    const float4 *geom = reinterpret_cast<const float4 *>(smemTensor);
+    FilterScene fs = p.filterCam;
+    rebase_filter(fs, smemTensor + geomBytes);
+    uint32_t const bOff = (geomBytes + blobBytes + 127u) & ~127u;
+    uint32_t const bBytes = tensor_b_bytes_cam(p.tensorRows);
+    for (uint32_t i = threadIdx.x; i < bBytes / 16u; i += S::kThreads)
+        reinterpret_cast<float4 *>(smemTensor + bOff)[i] = __ldg(reinterpret_cast<const float4 *>(p.tensorBCam) + i);
+    float *aBase = reinterpret_cast<float *>(smemTensor + bOff + bBytes);
+    for (uint32_t i = threadIdx.x; i < kTensorRays * uint32_t(kTensorAcc); i += S::kThreads) // constant chunks of every ray matrix
+        tensor_init_rows_cam(aBase + (i / kTensorRays) * (kTensorABytesCam / 4u), i % kTensorRays);
+    if (threadIdx.x == 0)
+    {
+        for (int t = 0; t < kTensorTiles; ++t)
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&mmaBar[t])));
+        pool.freeMask = (1u << kTensorAcc) - 1u;
+        for (int a = 0; a < 4; ++a)
+            pool.readers[a] = pool.holder[a] = 0u;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if ((threadIdx.x >> 5) == 0)
+    {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(&tmemBase)),
+                     "n"(kTensorCols * kTensorAcc));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    TensorFilter T;
+    T.tile = threadIdx.x / kTensorRays;
+    T.sA = aBase + (kTensorTimeShared ? 0u : T.tile * (kTensorABytesCam / 4u));
+    T.pool = &pool;
+    T.bAddr = smem_addr(smemTensor + bOff);
+    T.bLbo = tensor_b_lbo(p.tensorRows);
+    T.rows = p.tensorRows;
+    T.slots = tensor_slots(p.filterCam.nSlots);
+    T.tmem = tmemBase + (kTensorTimeShared ? 0u : T.tile * kTensorCols);
+    T.bar = smem_addr(&mmaBar[T.tile]);
+    T.phase = 0u;
+
+    uint32_t x, y;
+    bool inside;
+    lane_pixel<S>(p, x, y, inside);
+    uint32_t const pixel = y * p.width + x;
+    float const widthF = __uint2float_rn(p.width), heightF = __uint2float_rn(p.height);
+    uint64_t const pixKey = pixel_key(p.seed, pixel);
+    V3 const eye = v3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
+    uint32_t const nSamples = p.sampleEnd - p.sampleBegin;
+    float4 *out = p.firstHits + (size_t(lane_row_local<S>()) * (p.xEnd - p.xBegin) + (x - p.xBegin)) * nSamples;
+    uint32_t exactEvals = 0;
+    if (tile_sync_or(T.tile, inside)) // a tile wholly outside the image has nothing to do (tile-uniform)
+    {
+        for (uint32_t s = 0; s < nSamples; ++s) // the same trip count for every lane of the tile
+        {
+            Rng rng;
+            rng.key = stream_key(pixKey, p.sampleBegin + s);
+            rng.event = 0;
+            rng.open_event();
+            float xiU, xiV;
+            rng.uniform2(-1.f, 1.f, xiU, xiV);
+            V3 const dir = primary_direction(p.cam, widthF, heightF, x, y, xiU, xiV);
+            bool anyAlive;
+            uint32_t const idx = closest_hit_tensor<true>(fs, geom, p.n, dir, eye, T, exactEvals, inside, true, anyAlive);
+            if (inside)
+                out[s] = first_hit_record(dir, idx, p.n);
+        }
+    }
+    if (p.counters)
+    {
+        __syncwarp();
+        warp_counter_add(p.counters + 0, inside ? nSamples : 0u);
+        warp_counter_add(p.counters + 1, inside ? nSamples : 0u);
+        warp_counter_add(p.counters + 3, exactEvals);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
     if ((threadIdx.x >> 5) == 0)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmemBase), "n"(kTensorCols * kTensorAcc));
 }

@@ -29,13 +29,16 @@ constexpr uint32_t kTensorRays = 128;      // M: one ray tile = four warps, one 
 constexpr uint32_t kTensorCols = 128;      // N <= this: accumulator columns per ray tile (four tiles fill an SM's 512)
 constexpr uint32_t kTensorK = 40;
 constexpr double kTensorSlackU = 384.0 / 16777216.0;
+constexpr uint32_t kTensorKCam = 32;       // camera form: six products + the constant = 28 K slots, padded to a multiple of 8
 constexpr uint32_t kTensorABytes = kTensorRays * kTensorK * 4u;
+constexpr uint32_t kTensorABytesCam = kTensorRays * kTensorKCam * 4u;
 constexpr uint32_t kTensorALbo = (kTensorRays / 8u) * 128u;
 
 // slots the tensor core takes (the first ones; the rest, if any, stay with the FFMA2 loop) and the rows of its matrix
 SPT_TENSOR_HD inline uint32_t tensor_slots(uint32_t nSlots) { return nSlots < kTensorCols ? nSlots : kTensorCols; }
 SPT_TENSOR_HD inline uint32_t tensor_rows(uint32_t nSlots) { return (tensor_slots(nSlots) + 15u) / 16u * 16u; }
 SPT_TENSOR_HD inline uint32_t tensor_b_bytes(uint32_t rows) { return rows * kTensorK * 4u; }
+SPT_TENSOR_HD inline uint32_t tensor_b_bytes_cam(uint32_t rows) { return rows * kTensorKCam * 4u; }
 SPT_TENSOR_HD inline uint32_t tensor_b_lbo(uint32_t rows) { return (rows / 8u) * 128u; }
 // float index of element (row, k) in a canonical matrix of `rows` rows
 SPT_TENSOR_HD inline uint32_t tensor_elem(uint32_t rows, uint32_t row, uint32_t k)
@@ -89,6 +92,37 @@ inline void build_tensor_matrix(const std::vector<double> &hostGeom, uint32_t nS
             float h, l;
             tf32_split(g[c], c == 9, h, l);
             float const q[4] = {h, c < 9 ? h : l, c < 9 ? l : 1.f, c < 9 ? l : 1.f};
+            for (uint32_t e = 0; e < 4; ++e)
+                B[tensor_elem(rows, s, 4 * c + e)] = q[e];
+        }
+    }
+}
+
+// Camera form (all rays start at the eye E): with C' = C - E in binary64,
+//   v = (C'.D)^2 - (|C'|^2 - r^2) + S - 1e-3 = sum_{i<=j} (c_ij C'_i C'_j)(D_i D_j) + k',   S = kTensorSlackU (|C|^2 + r^2 + |E|^2):
+// six factors + the constant.  Sphere row: chunk c < 6 = (h, h, l, l) of factor c, chunk 6 = (k'_h, k'_l, 0, 0), chunk 7 = 0;
+// ray row: chunk c < 6 = (h, l, h, l) of D_i D_j, chunk 6 = (1, 1, 0, 0), chunk 7 = 0 (chunks 6 and 7 never change).
+inline void build_tensor_matrix_cam(const std::vector<double> &hostGeom, uint32_t nSlots, const double eye[3], std::vector<float> &B)
+{
+    uint32_t const used = tensor_slots(nSlots), rows = tensor_rows(nSlots);
+    B.assign(size_t(rows) * kTensorKCam, 0.f);
+    double const e2 = eye[0] * eye[0] + eye[1] * eye[1] + eye[2] * eye[2];
+    for (uint32_t s = 0; s < rows; ++s)
+    {
+        double g[7] = {0, 0, 0, 0, 0, 0, -1e30}; // never a candidate
+        if (s < used && hostGeom[4 * s + 3] >= 0.0)
+        {
+            double const cx = hostGeom[4 * s], cy = hostGeom[4 * s + 1], cz = hostGeom[4 * s + 2], r = hostGeom[4 * s + 3];
+            double const x = cx - eye[0], y = cy - eye[1], z = cz - eye[2];
+            double const a2 = cx * cx + cy * cy + cz * cz;
+            g[0] = x * x, g[1] = 2 * x * y, g[2] = 2 * x * z, g[3] = y * y, g[4] = 2 * y * z, g[5] = z * z;
+            g[6] = -(x * x + y * y + z * z - r * r) + kTensorSlackU * (a2 + r * r + e2) - double(1e-3f);
+        }
+        for (uint32_t c = 0; c < 7; ++c)
+        {
+            float h, l;
+            tf32_split(g[c], c == 6, h, l);
+            float const q[4] = {h, c < 6 ? h : l, c < 6 ? l : 0.f, c < 6 ? l : 0.f};
             for (uint32_t e = 0; e < 4; ++e)
                 B[tensor_elem(rows, s, 4 * c + e)] = q[e];
         }

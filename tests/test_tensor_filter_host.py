@@ -33,8 +33,8 @@ def write_scene(path, centers, radii):
         f.write(np.ascontiguousarray(g, np.float32).tobytes())
 
 
-def run(checker, scene, rays):
-    r = subprocess.run([checker, scene, str(rays)], capture_output=True, text=True, timeout=300)
+def run(checker, scene, rays, *extra):
+    r = subprocess.run([checker, scene, str(rays), *map(str, extra)], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and r.stdout.strip().endswith("OK"), r.stdout + r.stderr
     return r.stdout
 
@@ -45,6 +45,19 @@ def test_config3_scene_no_true_hit_filtered_out(checker, tmp_path):
     write_scene(scene, z["centers"].reshape(-1, 4)[:, :3], z["radii"])
     out = run(checker, scene, 4096)
     assert "128 on the tensor core, 128 matrix rows" in out  # 152 slots: the last 24 stay with the FFMA2 loop
+
+
+@pytest.mark.parametrize("eye", [None, (300.5, -2.0, -1800.0)])
+def test_camera_form_no_true_hit_filtered_out(checker, tmp_path, eye):
+    # primary_hits_tc: six products of the direction + the constant (K = 32), matrix specialised for the eye; the default camera
+    # of the reference, and an eye far from the scene (slack scales with |E|^2)
+    z = np.load(os.path.join(ROOT, "tests", "golden", "scene_random_seed1.npz"))
+    cam = np.load(os.path.join(ROOT, "tests", "golden", "camera_default.npz"))
+    scene = str(tmp_path / "scene.bin")
+    write_scene(scene, z["centers"].reshape(-1, 4)[:, :3], z["radii"])
+    e = [float(v) for v in cam["eye"][:3]] if eye is None else list(eye)
+    out = run(checker, scene, 4096, "cam", *e)
+    assert "camera form" in out and "K = 32" in out
 
 
 @pytest.mark.parametrize("name", ["scene_random_seed2", "scene_init_seed1"])
@@ -91,10 +104,10 @@ def test_experimental_variant_compiles_and_default_device_code_is_untouched(tmp_
         return {line.split()[-1] for line in out.splitlines() if line.strip().startswith("Function :")}
 
     base, exp = kernels(shipped), kernels(variant)
-    tc = {k for k in exp if "trace_secondary_tc" in k}
-    assert tc and not any("trace_secondary_tc" in k for k in base)
-    assert exp - tc == base  # the variant only ADDS the experimental kernel
-    sass = subprocess.run(["cuobjdump", "-sass", "-fun", next(iter(tc)), variant], capture_output=True, text=True).stdout
+    tc = {k for k in exp if "trace_secondary_tc" in k or "primary_hits_tc" in k}
+    assert len(tc) == 2 and not any(k in base for k in tc)
+    assert exp - tc == base  # the variant only ADDS the experimental kernels
+    sass = subprocess.run(["cuobjdump", "-sass", variant], capture_output=True, text=True).stdout
     assert "UTCMMA" in sass or "UTCHMMA" in sass or "TCMMA" in sass, "no tcgen05.mma in the experimental kernel"
 
 

@@ -1,6 +1,7 @@
 // tensor_filter_ab.cpp -- smallest possible GPU check of an EXPERIMENTAL -DSPT_TENSOR_FILTER=1 build of the library (no
-// Python, starts in a second): renders two synthetic scenes through the C ABI twice from the SAME library -- bounce kernel on
-// the tensor core (default of that build) and on the FFMA2 loop (SPT_TENSOR=0) -- and compares the accumulators byte for byte.
+// Python, starts in a second): renders two synthetic scenes through the C ABI four times from the SAME library -- bounce kernel
+// and camera kernel each on the tensor core (default of that build) or on the FFMA2 loop (SPT_TENSOR=0 / SPT_TENSOR_PRIMARY=0) --
+// and compares the accumulators byte for byte against the all-FFMA2 render.
 //   g++ -O2 -std=c++17 -I include -o build_ab/tensor_filter_ab tools/tensor_filter_ab.cpp -ldl
 //   timeout 30 build_ab/tensor_filter_ab build_ab/tensor.so [scene.bin width height spp depth reps]   (tools/export_scene.py)
 #include "spt_cuda.h"
@@ -13,6 +14,14 @@
 #include <dlfcn.h>
 #include <random>
 #include <vector>
+
+// modes: (bounce kernel, camera kernel) on the tensor core; the last one is the shipped path
+static const char *const kModes[4][3] = {{"1", "1", "tensor+tensor"}, {"1", "0", "tensor+ffma2 "}, {"0", "1", "ffma2 +tensor"}, {"0", "0", "ffma2 +ffma2 "}};
+static void set_mode(int m)
+{
+    setenv("SPT_TENSOR", kModes[m][0], 1);
+    setenv("SPT_TENSOR_PRIMARY", kModes[m][1], 1);
+}
 
 #define LOAD(name) auto name = reinterpret_cast<decltype(&::name)>(dlsym(h, #name)); if (!name) { std::printf("missing %s\n", #name); return 2; }
 
@@ -68,11 +77,11 @@ int main(int argc, char **argv)
         prm.width = 200, prm.height = 100, prm.depth = 8, prm.pass_cap = 0, prm.sample_begin = 0, prm.sample_end = 6, prm.seed = 99;
         prm.variant = SPT_VARIANT_MEGAKERNEL, prm.flags = SPT_FLAG_COUNTERS;
         SptSegment seg{0, prm.height, 0, prm.width};
-        std::vector<float> acc[2];
+        std::vector<float> acc[4];
         std::vector<uint8_t> rgb(size_t(prm.width) * prm.height * 3);
-        for (int pass = 0; pass < 2; ++pass)
+        for (int pass = 0; pass < 4; ++pass)
         {
-            setenv("SPT_TENSOR", pass == 0 ? "1" : "0", 1);
+            set_mode(pass);
             acc[pass].assign(size_t(prm.width) * prm.height * 4, 0.f);
             spt_cuda_reset_counters(ctx);
             auto const t0 = std::chrono::steady_clock::now();
@@ -82,17 +91,21 @@ int main(int argc, char **argv)
             SptCounters cn{};
             spt_cuda_get_timing(ctx, &tm);
             spt_cuda_get_counters(ctx, &cn);
-            std::printf("n=%u %s rc=%d wall %.1f ms trace %.3f ms segments %llu exact %llu%s%s\n", n, pass == 0 ? "tensor" : "ffma2 ", rc, ms,
+            std::printf("n=%u %s rc=%d wall %.1f ms trace %.3f ms segments %llu exact %llu%s%s\n", n, kModes[pass][2], rc, ms,
                         tm.trace_ms, (unsigned long long)cn.segments, (unsigned long long)cn.exact, rc ? " : " : "", rc ? spt_cuda_last_error() : "");
             std::fflush(stdout);
             if (rc)
                 return 1;
         }
-        size_t diff = 0;
-        for (size_t i = 0; i < acc[0].size(); ++i)
-            diff += std::memcmp(&acc[0][i], &acc[1][i], 4) != 0;
-        std::printf("n=%u accumulators: %zu of %zu words differ -> %s\n", n, diff, acc[0].size(), diff ? "MISMATCH" : "bit-identical");
-        bad += diff != 0;
+        for (int pass = 0; pass < 3; ++pass)
+        {
+            size_t diff = 0;
+            for (size_t i = 0; i < acc[3].size(); ++i)
+                diff += std::memcmp(&acc[pass][i], &acc[3][i], 4) != 0;
+            std::printf("n=%u %s vs shipped path: %zu of %zu words differ -> %s\n", n, kModes[pass][2], diff, acc[3].size(),
+                        diff ? "MISMATCH" : "bit-identical");
+            bad += diff != 0;
+        }
     }
     // ---- optional timing A/B on a scene file (tools/export_scene.py): argv = lib scene.bin width height spp depth reps ----
     if (argc >= 8)
@@ -116,13 +129,13 @@ int main(int argc, char **argv)
         prm.depth = uint32_t(std::atoi(argv[6])), prm.pass_cap = 10, prm.seed = 1, prm.variant = SPT_VARIANT_MEGAKERNEL;
         int const reps = std::atoi(argv[7]);
         SptSegment seg{0, prm.height, 0, prm.width};
-        std::vector<float> acc[2];
+        std::vector<float> acc[4];
         std::vector<uint8_t> rgb(size_t(prm.width) * prm.height * 3);
         double const samples = double(prm.width) * prm.height * prm.sample_end;
         for (int rep = 0; rep < reps; ++rep)
-            for (int pass = 0; pass < 2; ++pass)
+            for (int pass = 0; pass < 4; ++pass)
             {
-                setenv("SPT_TENSOR", pass == 0 ? "1" : "0", 1);
+                set_mode(pass);
                 acc[pass].assign(size_t(prm.width) * prm.height * 4, 0.f);
                 if (spt_cuda_render(ctx, &cam, &prm, seg, rgb.data(), acc[pass].data()))
                 {
@@ -131,15 +144,19 @@ int main(int argc, char **argv)
                 }
                 SptTiming tm{};
                 spt_cuda_get_timing(ctx, &tm);
-                std::printf("rep %d %s n=%u %ux%u spp %u depth %u: trace %.3f ms = %.1f Msamples/s\n", rep, pass == 0 ? "tensor" : "ffma2 ", n,
+                std::printf("rep %d %s n=%u %ux%u spp %u depth %u: trace %.3f ms = %.1f Msamples/s\n", rep, kModes[pass][2], n,
                             prm.width, prm.height, prm.sample_end, prm.depth, tm.trace_ms, samples / tm.trace_ms * 1e-3);
                 std::fflush(stdout);
             }
-        size_t diff = 0;
-        for (size_t i = 0; i < acc[0].size(); ++i)
-            diff += std::memcmp(&acc[0][i], &acc[1][i], 4) != 0;
-        std::printf("scene file: %zu of %zu words differ -> %s\n", diff, acc[0].size(), diff ? "MISMATCH" : "bit-identical");
-        bad += diff != 0;
+        for (int pass = 0; pass < 3; ++pass)
+        {
+            size_t diff = 0;
+            for (size_t i = 0; i < acc[3].size(); ++i)
+                diff += std::memcmp(&acc[pass][i], &acc[3][i], 4) != 0;
+            std::printf("scene file, %s vs shipped path: %zu of %zu words differ -> %s\n", kModes[pass][2], diff, acc[3].size(),
+                        diff ? "MISMATCH" : "bit-identical");
+            bad += diff != 0;
+        }
     }
     spt_cuda_destroy(ctx);
     std::printf(bad ? "FAIL\n" : "OK\n");

@@ -3,6 +3,7 @@
 //
 //   g++ -O2 -std=c++17 -frounding-math -ffp-contract=off -o /tmp/tfc tools/tensor_filter_check.cpp && /tmp/tfc scene.bin [rays]
 //
+// With `cam ex ey ez` appended: the camera form (primary_hits_tc): all rays from the eye, build_tensor_matrix_cam, K = 32.
 // scene.bin: uint32 n, then n x (cx, cy, cz, r) float32 (tests/test_tensor_filter_host.py writes it from the golden scene).
 //
 // What it does, for `rays` secondary-like rays (origins on sphere surfaces and on the ground, directions normalised in fp32):
@@ -23,6 +24,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <random>
+#include <string>
 
 using namespace spt;
 
@@ -92,6 +94,22 @@ void store_ray(float *sA, uint32_t lane, const float *dir, const float *org, flo
     }
 }
 
+// tensor_store_ray_cam + tensor_init_rows_cam, operation for operation
+void store_ray_cam(float *sA, uint32_t lane, const float *dir)
+{
+    float const f[6] = {fmul(dir[0], dir[0]), fmul(dir[0], dir[1]), fmul(dir[0], dir[2]), fmul(dir[1], dir[1]), fmul(dir[1], dir[2]), fmul(dir[2], dir[2])};
+    float *row = sA + (lane >> 3) * 32 + (lane & 7) * 4;
+    for (int c = 0; c < 6; ++c)
+    {
+        float const h = tf32_trunc(f[c]), l = fsub(f[c], h);
+        float *d = row + c * (kTensorALbo / 4);
+        d[0] = h, d[1] = l, d[2] = h, d[3] = l;
+    }
+    float *d6 = row + 6 * (kTensorALbo / 4), *d7 = row + 7 * (kTensorALbo / 4);
+    d6[0] = d6[1] = 1.f, d6[2] = d6[3] = 0.f;
+    d7[0] = d7[1] = d7[2] = d7[3] = 0.f;
+}
+
 float trunc_to_float(double x) // binary64 -> fp32 toward zero
 {
     float f = float(x);
@@ -105,7 +123,7 @@ int main(int argc, char **argv)
 {
     if (argc < 2)
     {
-        std::fprintf(stderr, "usage: %s scene.bin [rays]\n", argv[0]);
+        std::fprintf(stderr, "usage: %s scene.bin [rays [cam ex ey ez]]\n", argv[0]);
         return 2;
     }
     FILE *fp = std::fopen(argv[1], "rb");
@@ -117,6 +135,12 @@ int main(int argc, char **argv)
         return 2;
     std::fclose(fp);
     uint32_t const nRays = argc > 2 ? uint32_t(std::atoi(argv[2])) : 4096u;
+    // camera form: every ray starts at the eye, matrix from build_tensor_matrix_cam, K = 32
+    bool const cam = argc > 6 && std::string(argv[3]) == "cam";
+    double const eyeD[3] = {cam ? std::atof(argv[4]) : 0.0, cam ? std::atof(argv[5]) : 0.0, cam ? std::atof(argv[6]) : 0.0};
+    float const eyeF[3] = {float(eyeD[0]), float(eyeD[1]), float(eyeD[2])};
+    double const eyeX[3] = {double(eyeF[0]), double(eyeF[1]), double(eyeF[2])}; // the library sees the fp32 eye
+    uint32_t const K = cam ? kTensorKCam : kTensorK;
 
     // filter slots: the rule of build_filter (spt_cuda.cu)
     std::vector<uint32_t> slotIdx;
@@ -135,22 +159,25 @@ int main(int argc, char **argv)
         hostGeom[4 * k + 3] = std::fabs(double(geom[4 * slotIdx[k] + 3]));
     }
     std::vector<float> B;
-    build_tensor_matrix(hostGeom, nSlots, B);
+    if (cam)
+        build_tensor_matrix_cam(hostGeom, nSlots, eyeX, B);
+    else
+        build_tensor_matrix(hostGeom, nSlots, B);
     uint32_t const rows = tensor_rows(nSlots), used = tensor_slots(nSlots);
-    if (B.size() != size_t(rows) * kTensorK || rows % 16u || rows > kTensorCols || used > rows)
+    if (B.size() != size_t(rows) * K || rows % 16u || rows > kTensorCols || used > rows)
     {
         std::printf("FAIL: matrix shape\n");
         return 1;
     }
     // every sphere entry must already be a TF32 value, and the constant column must not round below its binary64 value
     for (uint32_t s = 0; s < rows; ++s)
-        for (uint32_t k = 0; k < kTensorK; ++k)
+        for (uint32_t k = 0; k < K; ++k)
             if (tf32_trunc(B[tensor_elem(rows, s, k)]) != B[tensor_elem(rows, s, k)])
             {
                 std::printf("FAIL: B(%u,%u) is not a TF32 value\n", s, k);
                 return 1;
             }
-    for (uint32_t s = 0; s < used; ++s)
+    for (uint32_t s = 0; s < used && !cam; ++s)
     {
         if (hostGeom[4 * s + 3] < 0.0)
             continue;
@@ -196,6 +223,12 @@ int main(int argc, char **argv)
                 for (double &c : o)
                     c *= 40.0;
             double d[3] = {nrm[0] + uni(rng) - 0.5, nrm[1] + uni(rng) - 0.5, nrm[2] + uni(rng) - 0.5};
+            if (cam) // a pinhole at the eye looking down +z, 90 degrees wide as the reference's (SingleThreadPathTracer.hpp:125-128)
+            {
+                for (int e = 0; e < 3; ++e)
+                    o[e] = eyeX[e];
+                d[0] = -1.0 + 2.0 * uni(rng), d[1] = -1.0 + 2.0 * uni(rng), d[2] = 1.0;
+            }
             if (lane % 5u == 0u) // and some rays aimed at a sphere centre (grazing and head-on hits both occur)
             {
                 uint32_t const k = uint32_t(uni(rng) * double(slotIdx.size())) % uint32_t(slotIdx.size());
@@ -211,7 +244,10 @@ int main(int argc, char **argv)
                 orgs[lane][e] = float(o[e]);
             }
             ods[lane] = dot3(orgs[lane], dirs[lane]);
-            store_ray(A.data(), lane, dirs[lane], orgs[lane], ods[lane]);
+            if (cam)
+                store_ray_cam(A.data(), lane, dirs[lane]);
+            else
+                store_ray(A.data(), lane, dirs[lane], orgs[lane], ods[lane]);
         }
         for (uint32_t lane = 0; lane < kTensorRays; ++lane)
         {
@@ -224,7 +260,7 @@ int main(int argc, char **argv)
                 // the tensor core: operands truncated to TF32, exact products
                 float accRz = 0.f;
                 double accF64 = 0.0;
-                for (uint32_t k = 0; k < kTensorK; ++k)
+                for (uint32_t k = 0; k < K; ++k)
                 {
                     double const prod = double(tf32_trunc(A[tensor_elem(kTensorRays, lane, k)])) * double(B[tensor_elem(rows, s, k)]);
                     accRz = trunc_to_float(double(accRz) + prod);
@@ -258,6 +294,8 @@ int main(int argc, char **argv)
         }
     }
     double const rays = double((nRays + kTensorRays - 1) / kTensorRays * kTensorRays);
+    if (cam)
+        std::printf("camera form, eye (%g, %g, %g), K = %u\n", eyeX[0], eyeX[1], eyeX[2], K);
     std::printf("%u spheres, %u slots (%u on the tensor core, %u matrix rows), %.0f rays, %llu pairs\n", n, nSlots, used, rows, rays, pairs);
     std::printf("accepted by the reference's sequence: %.3f per ray\n", double(hits) / rays);
     std::printf("candidates per ray: tensor form %.3f (fp32 truncating accumulate) / %.3f (binary64 accumulate); shipped slack 96 u, exact arithmetic: %.3f\n",

@@ -3,7 +3,8 @@
 
 Run in the build container only (needs /root/reference to build oracle/_ref/libspt_ref.so):
 
-    python tests/golden/make_golden.py
+    python tests/golden/make_golden.py                # everything but the two slow renders below
+    python tests/golden/make_golden.py --converged2   # converged_task2.npz: configs 2 and 4 (minutes of CPU)
 
 Every array below is an output of the reference's own code (compiled by oracle/Makefile from
 /root/reference/include with shim headers, no source edits), with its clock-seeded RNG handed a
@@ -25,8 +26,45 @@ def scene_dict(sc):
     return dict(centers=sc.centers, radii=sc.radii, materials=sc.materials, colors=sc.colors, fuzz=sc.fuzz)
 
 
+def config2_scene():
+    """BASELINE config 2: one diffuse sphere over a ground sphere (the scene of test_first_hit_config2_full_resolution)."""
+    from oracle import Scene
+
+    return Scene(np.array([[0, -1000.5, 0, 0], [0, 1, 0, 0]], np.float32), np.array([1000.0, 0.5], np.float32),
+                 np.array([3, 3], np.uint8), np.array([[30, 144, 255, 0], [255, 100, 230, 0]], np.float32), np.zeros(2, np.float32))
+
+
+def converged_configs_2_and_4():
+    """Converged renders of the UNMODIFIED reference for BASELINE config 2 (its "convergence check") and for a config-4
+    style metal/glass scene (501 spheres, through the wide-index build: Collision.hpp:87-92 holds a uint8_t index):
+    RenderSegmentTask over square tiles, all host threads.  Written to converged_task2.npz (minutes of CPU)."""
+    import simplepathtracer_b200 as spt  # host-side generators only (no GPU needed)
+
+    threads = os.cpu_count() or 8
+    cv = {}
+    jobs = (
+        ("c2", False, config2_scene(), (480, 270, 8192, 4, 30)),
+        ("c4", True, spt.generate_metal_glass(4, 500), (160, 90, 8192, 50, 10)),
+    )
+    for name, wide, scene, (w, h, spp, depth, tile) in jobs:
+        R = Reference(wide=wide)
+        R.set_camera()
+        R.set_scene(scene)
+        R.set_config(w, h, spp, depth)
+        mean, rgb, sec = R.render_mt(1, tile, threads, 4321)
+        print(f"converged {name}: {w}x{h}x{spp} depth {depth} in {sec:.1f}s = {w*h*spp/sec/1e6:.2f} Msamples/s on {threads} threads")
+        cv[f"{name}_mean"] = mean[..., :3].astype(np.float32)
+        cv[f"{name}_config"] = np.array([w, h, spp, depth], np.int64)
+        for k, v in scene_dict(scene).items():
+            cv[f"{name}_scene_{k}"] = v
+    np.savez_compressed(os.path.join(OUT, "converged_task2.npz"), **cv)
+
+
 def main():
     build_oracle(ref=True)
+    if "--converged2" in sys.argv:
+        converged_configs_2_and_4()
+        return
     R = Reference()
     cam = R.set_camera()  # Globals.hpp:22-24 defaults through Renderer.hpp:321
     np.savez_compressed(os.path.join(OUT, "camera_default.npz"), view=cam.view, eye=cam.eye, sky=cam.sky)

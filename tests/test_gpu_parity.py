@@ -259,28 +259,43 @@ def _psnr_rmse(mean, ref):
     return 10.0 * np.log10(1.0 / mse), float(np.sqrt(mse))
 
 
-@pytest.mark.parametrize("which", ["init", "random"])
-def test_converged_render_matches_reference_own_render(tracer, cam, scene_init, scene_random, which):
-    """North-star gate: a converged CUDA render against the REFERENCE'S OWN high-spp CPU render
-    (RenderSegmentTask over square tiles, frozen in tests/golden/converged_task.npz by make_golden.py):
-    PSNR >= 45 dB or RMSE <= 1e-3 in linear radiance.  The two use unrelated random numbers, so this
-    is the statistical check that the counter-based RNG and the restated shading are the same estimator."""
+def _converged_case(which, scene_init, scene_random):
+    """(scene, w, h, ref_spp, depth, reference mean at image rows) of one converged REFERENCE render frozen under tests/golden/."""
     from conftest import golden_path
 
-    g = np.load(golden_path("converged_task.npz"))
+    if which in ("init", "random"):
+        g = np.load(golden_path("converged_task.npz"))
+        scene = scene_init if which == "init" else scene_random
+    else:  # BASELINE config 2 (its "convergence check") and a config-4 style metal/glass scene (wide-index reference build)
+        g = np.load(golden_path("converged_task2.npz"))
+        scene = spt.Scene(**{k: g[f"{which}_scene_{k}"] for k in ("centers", "radii", "materials", "colors", "fuzz")})
     w, h, ref_spp, depth = [int(v) for v in g[f"{which}_config"]]
-    ref = g[f"{which}_mean"][::-1]  # fixture rows are at the reference's flipped slots
-    scene = scene_init if which == "init" else scene_random
+    return scene, w, h, ref_spp, depth, g[f"{which}_mean"][::-1]  # fixture rows are at the reference's flipped slots
+
+
+@pytest.mark.parametrize("which", ["init", "random", "c2", "c4"])
+def test_converged_render_matches_reference_own_render(tracer, cam, scene_init, scene_random, which):
+    """North-star gate: a converged CUDA render against the REFERENCE'S OWN high-spp CPU render
+    (RenderSegmentTask over square tiles, frozen in tests/golden/converged_task*.npz by make_golden.py):
+    PSNR >= 45 dB in linear radiance, with the RMSE recorded.  The two use unrelated random numbers, so this
+    is the statistical check that the counter-based RNG and the restated shading are the same estimator.
+    Cases: the 10-sphere scene, the random scene (config 1/3's), BASELINE config 2 at depth 4, and a 501-sphere
+    mirror/glass scene at depth 50 (config 4's, where a path draws the most random numbers)."""
+    scene, w, h, ref_spp, depth, ref = _converged_case(which, scene_init, scene_random)
     tracer.set_scene(scene)
-    spp = 65536
+    spp = 65536 if which != "c4" else 32768
     _, acc = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=2024, want_accum=True)
     mean = acc[..., :3] / acc[..., 3:4]
     psnr, rmse = _psnr_rmse(mean, ref)
-    # the reference render itself carries Monte-Carlo noise of its ref_spp samples; the gate is on the sum
-    assert psnr >= 45.0 or rmse <= 1e-3, (psnr, rmse)
-    # and no systematic offset: mean signed error well below the noise floor
-    bias = float(np.mean((mean - ref) / 255.0))
-    assert abs(bias) < 5e-4, bias
+    print(f"converged {which}: {w}x{h} depth {depth}, CUDA {spp} spp vs reference {ref_spp} spp: PSNR {psnr:.2f} dB, RMSE {rmse:.3e}")
+    # The reference render carries the Monte-Carlo noise of its own ref_spp samples, which alone is an RMSE of a few 1e-3:
+    # the north star's "RMSE <= 1e-3 OR PSNR >= 45 dB" is asserted on its PSNR arm, and the RMSE must stay at the level that
+    # noise explains (sigma / sqrt(ref_spp) with sigma <= 0.5 on the 0..1 scale).
+    assert psnr >= 45.0, (psnr, rmse)
+    assert rmse <= 0.5 / np.sqrt(ref_spp) + 1e-3, (psnr, rmse)
+    # and no systematic offset: mean signed error well below the noise floor, per channel
+    bias = np.mean((mean.astype(np.float64) - ref) / 255.0, axis=(0, 1))
+    assert np.abs(bias).max() < 5e-4, bias
 
 
 # ----------------------------------------------------------------------------- wavefront variant
@@ -373,11 +388,90 @@ def test_config5_first_hit_and_prefilter(tracer, oracle, cam, scene_lattice):
     assert np.array_equal(got, oracle.closest_hit_many(scene_lattice, d, o))
 
 
+def _full_size_case(which, scene_random, scene_metal_glass, scene_lattice):
+    scene, depth, spp = {"c3": (scene_random, 50, 4), "c4": (scene_metal_glass, 50, 4), "c5": (scene_lattice, 16, 2)}[which]
+    w, h = (3840, 2160) if which == "c3" else (1920, 1080)
+    return scene, w, h, depth, spp
+
+
+def _pick_crops(oracle, scene, cam, w, h, cw=64, ch=32):
+    """Crops (yBegin, yEnd, xBegin, xEnd) of the full-size image chosen from a coarse first-hit map of the ORACLE (the ray
+    generator is scale-consistent: pixel (x, y) of a w/8 x h/8 image looks where (8x, 8y) of the full one does): the largest
+    glass sphere, the largest mirror, the horizon line, the busiest far field of small spheres, two image corners, and a
+    crop that is not aligned with any CTA tile."""
+    f = 8
+    idx = oracle.first_hit(scene, cam, w // f, h // f)[0].reshape(h // f, w // f)
+    crops = {}
+
+    def around(name, y, x):
+        y0 = int(np.clip(y * f - ch // 2, 0, h - ch))
+        x0 = int(np.clip(x * f - cw // 2, 0, w - cw))
+        crops[name] = (y0, y0 + ch, x0, x0 + cw)
+
+    hit = idx < scene.n
+    for name, mat in (("glass", spt.REFRACTIVE), ("mirror", spt.REFLECTIVE)):
+        cand = [i for i in np.unique(idx[hit]) if scene.materials[i] == mat]
+        if cand:
+            best = max(cand, key=lambda i: (idx == i).sum())
+            ys, xs = np.nonzero(idx == best)
+            around(name, ys.mean(), xs.mean())
+    # horizon: a pixel whose vertical neighbour is sky while it is not
+    edge = np.argwhere(hit[1:, :] != hit[:-1, :])
+    if len(edge):
+        y, x = edge[len(edge) // 2]
+        around("horizon", y + 0.5, x)
+    # far field: the coarse 8x4 window with the most distinct spheres
+    best, where = -1, (0, 0)
+    for y in range(0, h // f - 4, 2):
+        for x in range(0, w // f - 8, 4):
+            k = len(np.unique(idx[y:y + 4, x:x + 8]))
+            if k > best:
+                best, where = k, (y + 2, x + 4)
+    around("far_field", *where)
+    crops["corner00"] = (0, ch, 0, cw)
+    crops["corner11"] = (h - ch, h, w - cw, w)
+    crops["ragged"] = (h // 2 + 3, h // 2 + 3 + ch - 5, w // 3 + 5, w // 3 + 5 + cw - 7)
+    return crops
+
+
+@pytest.mark.parametrize("which", ["c3", "c4", "c5"])
+def test_full_size_render_equals_oracle_on_crops(tracer, oracle, cam, scene_random, scene_metal_glass, scene_lattice, which):
+    """BASELINE configs 3, 4, 5 at their FULL image size, depth and tracer semantics (pass_cap 10), rendered whole by the
+    DEFAULT path (split kernels; streamed list for c5): seven crops of the accumulator -- glass sphere, mirror, horizon, far
+    field, two corners, a ragged rectangle -- equal the oracle's render of the same crop bit for bit
+    (RenderSegmentTask, TaskBasedPathTracer.hpp:54-206; Collision.hpp:87-109)."""
+    import torch
+
+    scene, w, h, depth, spp = _full_size_case(which, scene_random, scene_metal_glass, scene_lattice)
+    tracer.set_scene(scene)
+    tracer.set_stream(torch.cuda.current_stream().cuda_stream)
+    acc = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+    tracer.accumulate(cam, w, h, 0, spp, depth, acc, pass_cap=10, seed=8)
+    torch.cuda.synchronize()
+    tracer.set_stream(None)
+    crops = _pick_crops(oracle, scene, cam, w, h)
+    assert len(crops) >= 6, crops
+    for name, (y0, y1, x0, x1) in crops.items():
+        oacc, _ = oracle.render_accum(scene, cam, w, h, spp, depth, pass_cap=10, seed=8, seg=(y0, y1, x0, x1))
+        got = acc[y0:y1, x0:x1].cpu().numpy()
+        try:
+            assert_accum_equal(got, oacc[y0:y1, x0:x1])
+        except AssertionError as e:
+            raise AssertionError(f"{which} crop {name} {(y0, y1, x0, x1)}: {e}") from None
+    # and the same crops through the host-buffer entry point (spt_cuda_render with a segment = a RenderSegmentData tile)
+    name, seg = next(iter(crops.items()))
+    rgb, part = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=8, seg=seg, want_accum=True)
+    y0, y1, x0, x1 = seg
+    assert_accum_equal(part[y0:y1, x0:x1], acc[y0:y1, x0:x1].cpu().numpy())
+    full = oracle.resolve(part, seg=seg)
+    assert np.array_equal(rgb[h - y1:h - y0, x0:x1], full[h - y1:h - y0, x0:x1])
+
+
 @pytest.mark.parametrize("which", ["c3", "c4", "c5"])
 def test_full_size_properties(tracer, cam, scene_random, scene_metal_glass, scene_lattice, which):
-    """At BASELINE's full image sizes the oracle is out of reach; what must still hold: the three code paths
-    (pre-filter megakernel, strict-loop megakernel, wavefront) produce identical accumulators, sample ranges
-    compose, and count + dropped == spp."""
+    """Size-independent properties at BASELINE's full image sizes (the oracle comparison at these sizes is
+    test_full_size_render_equals_oracle_on_crops): every code path (split, single kernel, streamed, resident, strict loop,
+    wavefront) produces identical accumulators over the WHOLE image, sample ranges compose, and count + dropped == spp."""
     import torch
 
     scene, depth, spp = {"c3": (scene_random, 50, 4), "c4": (scene_metal_glass, 50, 4), "c5": (scene_lattice, 16, 1)}[which]

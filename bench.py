@@ -133,7 +133,8 @@ def cpu_reference_rate(wl, budget_s, threads=None):
         spp = int(max(2, min(4096, budget_s * rate / (w * h))))
         R.set_config(w, h, spp, wl["depth"])
         _, _, sec = R.render_mt(Reference.TASK, tile, threads, 2)
-        return {"value": w * h * spp / sec / 1e6, "unit": "Msamples/s", "cores": threads, "kind": "reference",
+        return {"value": w * h * spp / sec / 1e6, "unit": "Msamples/s", "cores": threads, "kind": "reference", "width": w, "height": h, "spp": spp,
+                "build": "g++ -O2 -msse4.1 -ffp-contract=off over the unmodified headers (oracle/Makefile)",
                 "sample": f"{wl['scene']} scene, {w}x{h}, {spp} spp, depth {wl['depth']}, RenderSegmentTask over {tile}x{tile} tiles, "
                           f"{threads} threads, {sec:.1f} s"}
     # the compiled reference did not travel: fall back to the single-threaded C port of the same tracer
@@ -143,7 +144,7 @@ def cpu_reference_rate(wl, budget_s, threads=None):
     t0 = time.time()
     O.render_refseq(scene, cam, w, h, spp, wl["depth"], Oracle.TASK, 1)
     sec = time.time() - t0
-    return {"value": w * h * spp / sec / 1e6, "unit": "Msamples/s", "cores": 1, "kind": "port",
+    return {"value": w * h * spp / sec / 1e6, "unit": "Msamples/s", "cores": 1, "kind": "port", "width": w, "height": h, "spp": spp,
             "sample": f"{wl['scene']} scene, {w}x{h}, {spp} spp, depth {wl['depth']}, C port of RenderSegmentTask, 1 thread, {sec:.1f} s"}
 
 
@@ -165,11 +166,14 @@ def run_reference_arm(args, wl):
         "impl": "reference", "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": float(np.mean(t_steps)) * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        # the native arm's workload, word for word; what a step of THIS arm actually renders is in `sample`
-        "config": {"workload": f"{args.workload}: {wl['desc']}", "spheres": load_scene(wl["scene"]).n, "width": wl["width"],
-                   "height": wl["height"], "spp": wl["spp"], "depth": wl["depth"], "pass_cap": PASS_CAP,
+        # the native arm's workload is named; width / height / spp are what a step of THIS arm really renders (a bounded
+        # sample of it: same scene, same depth, same tracer; Msamples/s is resolution- and spp-invariant to first order)
+        "config": {"workload": f"{args.workload}: {wl['desc']}", "spheres": load_scene(wl["scene"]).n, "width": sample["width"],
+                   "height": sample["height"], "spp": sample["spp"], "depth": wl["depth"], "pass_cap": PASS_CAP,
+                   "native_arm_size": f"{wl['width']}x{wl['height']}x{wl['spp']} spp",
                    "sample": f"bounded sample per step: {sample['sample']}"},
-        "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": sample["cores"], "kind": sample["kind"], "sample": sample["sample"]},
+        "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": sample["cores"], "kind": sample["kind"], "sample": sample["sample"],
+                         "build": sample.get("build")},
         "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -177,6 +181,28 @@ def run_reference_arm(args, wl):
 
 
 # --------------------------------------------------------------------------- native arm
+EXECUTED_FLOP = {"primary": 8, "secondary": 15}  # per (ray, slot) in the pre-filter: camera form 4 FMA; general form 7 FMA + 1 ADD
+
+
+def kernel_rooflines(ctr_per_render, n_spheres, primary_ms, secondary_ms, peak):
+    """Per-kernel FP32 roofline of split rendering from the device counters of ONE render and the kernels' own durations.
+    Camera segments = samples (one per sample, traced by primary_hits_*), secondary segments = the rest (trace_secondary*).
+    `frac` is ALGORITHMIC: 17 flop per (segment, sphere) as the reference's test defines it (Collision.hpp:9-17);
+    `executed_frac` counts the FMA-pipe flops the pre-filter really executes per test (8 / 15), exact candidates not included."""
+    seg_cam = ctr_per_render["samples"]
+    seg_sec = ctr_per_render["segments"] - ctr_per_render["samples"]
+    out = {}
+    for name, segs, ms, key in (("primary_hits_kernel", seg_cam, primary_ms, "primary"), ("trace_secondary", seg_sec, secondary_ms, "secondary")):
+        if ms <= 0:
+            continue
+        tests = segs * n_spheres
+        alg = FLOP_PER_TEST * tests / (ms * 1e-3) / 1e12
+        exe = EXECUTED_FLOP[key] * tests / (ms * 1e-3) / 1e12
+        out[name] = {"ms_per_render": ms, "segments": segs, "tests": tests, "achieved": alg, "frac": alg / peak if peak else None,
+                     "executed_flop_per_test": EXECUTED_FLOP[key], "executed_frac": exe / peak if peak else None}
+    return out
+
+
 def run_native_arm(args, wl):
     import torch
     import torch.distributed as dist
@@ -211,7 +237,9 @@ def run_native_arm(args, wl):
         s0, s1 = sharding.sample_range(rank, world, spp)
         bands = None
 
+    staging = (args.staging_mib << 20) if args.staging_mib else spt.DEFAULT_STAGING_BYTES
     pt = spt.PathTracer(local)
+    pt.set_staging_limit(staging)
     # one explicit stream for torch fills, our kernels and the timing events
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
@@ -224,11 +252,11 @@ def run_native_arm(args, wl):
     launches = [0]
     variant = spt.WAVEFRONT if args.variant == "wavefront" else spt.MEGAKERNEL
 
-    def step_device(ev=None):
+    def step_device(ev=None, flags=0):
         accum.zero_()
         if ev:
             ev[0].record()
-        pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, flags=spt.FLAG_COUNTERS | args.flags, variant=variant,
+        pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, flags=spt.FLAG_COUNTERS | args.flags | flags, variant=variant,
                       bands=bands)
         if ev:
             ev[1].record()
@@ -284,76 +312,119 @@ def run_native_arm(args, wl):
     value = total_samples / (ms_step * 1e-3) / 1e6
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kernel_events]))
     ctr = pt.counters()
-    trace_launches = pt.timing()["launches"]  # kernels of ONE accumulate call (split rendering: 2 per chunk of samples)
+    timing = pt.timing()
+    trace_launches = timing["launches"]  # kernels of ONE accumulate call (split rendering: 2 per chunk of samples)
     launches_native = int(sumr(launches[0] + args.steps * (trace_launches - 1)))
+    split = trace_launches > 1 and args.variant != "wavefront"
+    ctr1 = {k: v / args.steps for k, v in ctr.items()}  # this rank's share of one render
 
-    # ---- roofline of the dominant kernel (rank 0's trace kernel) ----------------------------------
+    # ---- roofline (rank 0's kernels) ---------------------------------------------------------------
     peak_scalar, peak_packed = pt.measure_fp32_peak()
     peak = max(peak_scalar, peak_packed)
     tests_per_launch = ctr["tests"] / args.steps
-    achieved = FLOP_PER_TEST * tests_per_launch / (kernel_ms * 1e-3) / 1e12
+    achieved_step = FLOP_PER_TEST * tests_per_launch / (kernel_ms * 1e-3) / 1e12
+    kernels, serial_ms = {}, None
+    if split:
+        # one more render, untimed for the headline, with the chunks serialised on one stream: the kernels' OWN durations
+        # (in the timed region the camera kernel of chunk k+1 runs under the tail of the bounce kernel of chunk k)
+        evs = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        step_device(evs, flags=spt.FLAG_SERIAL_CHUNKS)
+        torch.cuda.synchronize()
+        ts = pt.timing()
+        serial_ms = evs[0].elapsed_time(evs[1])
+        kernels = kernel_rooflines(ctr1, scene.n, ts["primary_ms"], ts["secondary_ms"], peak)
     traffic = traffic_detail = None
     try:  # measured once per round under ncu --set full and committed; never measured inside a timed run
         t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(f"{args.workload}:{args.variant}")
         if t:
             per = t.get("samples_per_launch_in_capture")
-            chunk = (s1 - s0) / max(trace_launches // 2, 1) if trace_launches > 1 else (s1 - s0)
-            scale = (chunk / per) if (per and trace_launches > 1) else 1.0
+            chunk = (s1 - s0) / max(trace_launches // 2, 1) if split else (s1 - s0)
+            scale = (chunk / per) if (per and split) else 1.0
             share = (1.0 / world) if bands else 1.0  # this rank's share of the pixels
             scale *= share
             traffic = (t["dram_bytes_read"] + t["dram_bytes_write"]) * scale  # bytes per launch of the dominant kernel
             traffic_detail = {"kernel": t.get("kernel", "trace_megakernel"), "dram_bytes_per_launch": traffic,
-                              "algorithmic_bytes_per_launch": (W * H * 32 + (W * H * chunk * 16 if trace_launches > 1 else 0)) * share,
+                              # the path's algorithmic HBM bytes are the float4 accumulator, read and written once
+                              "algorithmic_bytes_per_launch": W * H * 32 * share,
+                              # the cost of the split design, named separately: one 16-byte record per camera sample, written by
+                              # the camera kernel and read by the bounce kernel
+                              "staging_bytes_per_launch": (W * H * chunk * 16 * share) if split else 0,
                               "source": t["capture"]}
-            if "primary_dram_bytes_write" in t and trace_launches > 1:
+            if "primary_dram_bytes_write" in t and split:
                 traffic_detail["primary_hits_dram_bytes_per_launch"] = (t["primary_dram_bytes_read"] + t["primary_dram_bytes_write"]) * scale
     except (OSError, ValueError):
         pass
+    dom = kernels.get("trace_secondary")
     roofline = {
-        "bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
+        "bound": "fp32", "unit": "TFLOP/s", "peak": peak,
+        # the DOMINANT kernel alone (the bounce kernel, ~3/4 of a render) when the render is split; the whole step otherwise
+        "achieved": dom["achieved"] if dom else achieved_step, "frac": (dom["frac"] if dom else (achieved_step / peak if peak else None)),
+        "kernel": "trace_secondary" if dom else ("trace_" + args.variant),
+        "kernels": kernels,
+        "step": {"achieved": achieved_step, "frac": achieved_step / peak if peak else None, "kernel_ms": kernel_ms,
+                 "kernel_share_of_step": kernel_ms / ms_step,
+                 "launches": f"{trace_launches // 2} chunk(s) x (primary_hits_kernel + trace_secondary)" if split else f"{trace_launches} launch(es)",
+                 "serialised_chunks_ms": serial_ms},
         "traffic": traffic, "traffic_detail": traffic_detail,
         "exact_evals_per_segment": ctr["exact"] / max(ctr["segments"], 1),
-        "kernel": ("trace_" + args.variant) if (args.variant == "wavefront" or trace_launches == 1)
-                  else f"primary_hits_kernel + trace_secondary ({trace_launches // 2} chunk(s) of samples)",
-        "kernel_ms": kernel_ms, "kernel_share_of_step": kernel_ms / ms_step,
-        "algorithmic": f"{FLOP_PER_TEST} flop x {tests_per_launch:.4g} ray-sphere tests per render (all launches of the step; kernel_ms is their sum) "
-                       f"({ctr['segments'] / args.steps:.4g} ray segments x {scene.n} spheres; {ctr['segments'] / max(ctr['samples'], 1):.3f} segments/sample)",
+        "algorithmic": f"{FLOP_PER_TEST} flop x (ray segments x spheres) (BASELINE.md section 4; Collision.hpp:9-17); this rank, one render: "
+                       f"{ctr1['segments']:.4g} segments ({ctr1['samples']:.4g} camera + {ctr1['segments'] - ctr1['samples']:.4g} secondary) x {scene.n} spheres; "
+                       f"{ctr['segments'] / max(ctr['samples'], 1):.3f} segments/sample",
         "peak_source": f"measured in this run: dependent-FMA chains on all SMs, scalar {peak_scalar:.1f} / packed f32x2 {peak_packed:.1f} TFLOP/s "
                        f"(MEASURED_PEAKS.json has no FP32 CUDA-core figure; nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4)",
     }
 
-    # ---- end-to-end arm: host buffers through the C ABI --------------------------------------------
-    h2d = scene.n * (16 + 4 + 1 + 16 + 4) + 96 + 40
+    # ---- end-to-end arm: host buffers through the C ABI, ONE spt_cuda_render call per step ------------------
+    # N = 1: the context of the timed region.  N > 1: rank 0 alone calls spt_cuda_render on a multi-device context over the N
+    # GPUs of the job (spt_cuda_create_multi: the library splits the samples, combines the accumulators over NVLink with its
+    # fused reduce-and-resolve kernel and copies the image back); the other ranks wait at the barrier with their GPUs idle.
+    h2d = scene.n * (16 + 4 + 1 + 16 + 4) + 96 + 56
     d2h = W * H * 3
+    e2e_steps = max(1, min(args.steps, 3))
+    e2e_pt = pt
+    if world > 1:
+        barrier()
+        if rank == 0:
+            e2e_pt = spt.PathTracer(list(range(world)))
+            e2e_pt.set_staging_limit(staging)
+            if args.partition == "bands":
+                e2e_pt.set_partition(spt.PARTITION_BANDS)
 
     def step_e2e():
-        pt.set_scene(scene)  # H2D: the scene globals (Globals.hpp:31-37)
-        if world == 1:
-            pt.render(cam, W, H, spp, depth, pass_cap=PASS_CAP, seed=SEED, rgb8=rgb_host.numpy(), variant=variant, flags=args.flags)  # D2H inside
-        else:
-            accum.zero_()
-            pt.accumulate(cam, W, H, s0, s1, depth, accum, pass_cap=PASS_CAP, seed=SEED, variant=variant, flags=args.flags, bands=bands)
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
-            if rank == 0:
-                pt.resolve(accum, W, H, rgb_dev)
-                rgb_host.copy_(rgb_dev, non_blocking=True)
-            torch.cuda.synchronize()
+        e2e_pt.set_scene(scene)  # H2D: the scene globals (Globals.hpp:31-37), to every device of the context
+        e2e_pt.render(cam, W, H, spp, depth, pass_cap=PASS_CAP, seed=SEED, rgb8=rgb_host.numpy(), variant=variant, flags=args.flags)  # D2H inside
 
-    e2e_steps = max(1, min(args.steps, 3))
-    step_e2e()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
+    e2e_ms = 0.0
+    if rank == 0:
         step_e2e()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            step_e2e()
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+        e2e_launches = e2e_pt.timing()["launches"]
+        if world > 1:
+            e2e_pt.close()
     barrier()
-    e2e_ms = maxr((time.perf_counter() - t0) * 1e3) / e2e_steps
-    e2e = {"value": total_samples / (e2e_ms * 1e-3) / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d * world),
-           "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms}
+    e2e = None
+    if rank == 0:
+        e2e = {"value": total_samples / (e2e_ms * 1e-3) / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d * world),
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms, "launches_per_step": e2e_launches,
+               "path": "spt_cuda_set_scene + spt_cuda_render (host buffers)" + (f" on one multi-device context over {world} GPUs (spt_cuda_create_multi), rank 0's process" if world > 1 else "")}
+
+    # ---- the stress configurations, short legs after the headline (rank 0, N == 1) ---------------------------
+    workloads = None
+    if rank == 0 and world == 1 and args.workload == "c3" and not args.no_extra and not args.spp:
+        workloads = {}
+        for name in ("c4", "c5"):
+            workloads[name] = short_leg(pt, spt, torch, cam, WORKLOADS[name], peak, staging)
+        pt.set_scene(scene)
 
     # ---- CPU baseline (rank 0, N == 1 only) ---------------------------------------------------------
-    cpu = None
+    cpu = cpu4 = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_reference_rate(wl, budget_s=12.0)
+        cpu4 = cpu_reference_rate(wl, budget_s=5.0, threads=4)  # the reference's own g_maxThreads (Globals.hpp:11)
+        cpu["g_maxThreads_4"] = {"value": cpu4["value"], "cores": 4, "sample": cpu4["sample"]}
 
     if rank == 0:
         line = {
@@ -364,14 +435,51 @@ def run_native_arm(args, wl):
                        "spheres": scene.n, "width": W, "height": H, "spp": spp, "depth": depth, "pass_cap": PASS_CAP,
                        "variant": args.variant, "sharding": (f"interleaved 8-row bands of pixels over {world} rank(s)" if args.partition == "bands" else f"sample ranges over {world} rank(s)")
                                    + " + NCCL sum-reduce of float4 accumulators",
+                       "staging": f"first-hit staging limit {staging / 2**30:.0f} GiB per GPU (spt_cuda_set_staging_limit; library default 8 GiB), "
+                                  f"{trace_launches // 2 if split else 0} chunk(s) of samples per render",
                        "l2": f"float4 accumulator {W * H * 16 / 1e6:.1f} MB per step vs 126 MB L2; kernel is compute-bound, scene staged in shared memory"},
-            "e2e": e2e, "gpu_launches": launches_native, "roofline": roofline, "cpu_baseline": cpu, "clocks": clock_info,
+            "e2e": e2e, "gpu_launches": launches_native, "roofline": roofline, "cpu_baseline": cpu, "workloads": workloads, "clocks": clock_info,
             "device": info["name"], "sm_count": info["sm_count"], "counters": ctr,
         }
         emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def short_leg(pt, spt, torch, cam, wl, peak, staging):
+    """One warm-up and one timed render of a stress configuration (BASELINE.json configs 4 / 5) on the context of the headline:
+    Msamples/s with the scene resident, the roofline fractions, and what the scene costs to set up (host generation + upload)."""
+    t0 = time.perf_counter()
+    scene = load_scene(wl["scene"])
+    t_gen = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    pt.set_scene(scene)
+    t_up = time.perf_counter() - t0
+    W, H, spp, depth = wl["width"], wl["height"], wl["spp"], wl["depth"]
+    accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    out = {}
+    for rep in range(2):
+        accum.zero_()
+        pt.reset_counters()
+        ev[0].record()
+        pt.accumulate(cam, W, H, 0, spp, depth, accum, pass_cap=PASS_CAP, seed=SEED, flags=spt.FLAG_COUNTERS | (spt.FLAG_SERIAL_CHUNKS if rep == 0 else 0))
+        ev[1].record()
+        torch.cuda.synchronize()
+        ms = ev[0].elapsed_time(ev[1])
+        ctr = pt.counters()
+        if rep == 0:  # warm-up doubles as the serialised pass that gives the kernels' own durations
+            t = pt.timing()
+            out["kernels"] = kernel_rooflines(ctr, scene.n, t["primary_ms"], t["secondary_ms"], peak)
+    alg = FLOP_PER_TEST * ctr["tests"] / (ms * 1e-3) / 1e12
+    out.update({"workload": wl["desc"], "spheres": scene.n, "value": W * H * spp / (ms * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_render": ms,
+                "roofline_frac_step": alg / peak if peak else None,
+                "roofline_frac": out["kernels"].get("trace_secondary", {}).get("frac"),
+                "segments_per_sample": ctr["segments"] / max(ctr["samples"], 1),
+                "scene_setup_ms": {"host_generation": t_gen * 1e3, "spt_cuda_set_scene": t_up * 1e3,
+                                   "share_of_one_render": (t_gen + t_up) * 1e3 / ms}})
+    return out
 
 
 _REAL_STDOUT = None
@@ -406,6 +514,8 @@ def main():
     ap.add_argument("--variant", default="megakernel", choices=["megakernel", "wavefront"])
     ap.add_argument("--partition", default="samples", choices=["samples", "bands"], help="how N > 1 ranks share a render (sharding.py)")
     ap.add_argument("--flags", type=int, default=0, help="extra SPT_FLAG_* bits for the trace launches (experiments)")
+    ap.add_argument("--staging-mib", type=int, default=0, help="first-hit staging limit per GPU in MiB (0 = the library default, 8 GiB)")
+    ap.add_argument("--no-extra", action="store_true", help="skip the short c4 / c5 legs after the headline")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":

@@ -32,7 +32,8 @@ struct State
     SptContext *ctx = nullptr;
     std::mutex lock;
     bool sceneUploaded = false;
-    int device = 0;
+    std::vector<int> devices{0}; // CUDA ordinals; several = one render spread over several GPUs (spt_cuda_create_multi)
+    uint64_t stagingLimit = 0;   // 0 = the library's default (SPT_DEFAULT_STAGING_BYTES per device)
     uint64_t seed = 1;   // counter-RNG seed (the reference seeds from the clock, Random.hpp:88-89)
     uint32_t flags = 0;  // SPT_FLAG_*
 };
@@ -57,8 +58,19 @@ inline void InvalidateScene()
     s.sceneUploaded = false;
 }
 
-inline void SetDevice(int device) { GetState().device = device; }
+// Device selection; call before the first render (or after Shutdown()).  SetDevices({0, 1, ..., 7}) is the counterpart of the
+// reference's worker pool (g_maxThreads workers in RenderImageParallelMain, Renderer.hpp:257-302): ONE RenderSegmentCuda call
+// then spreads its samples (or 8-row bands) over all listed GPUs and the library combines their accumulators over NVLink.
+inline void SetDevice(int device) { GetState().devices.assign(1, device); }
+inline void SetDevices(std::vector<int> const &devices)
+{
+    if (devices.empty())
+        throw std::runtime_error("CudaPathTracer: SetDevices needs at least one device");
+    GetState().devices = devices;
+}
 inline void SetSeed(uint64_t seed) { GetState().seed = seed; }
+// first-hit staging budget of split rendering per device, in bytes (spt_cuda_set_staging_limit); 0 = library default
+inline void SetStagingLimit(uint64_t bytes) { GetState().stagingLimit = bytes; }
 
 inline SptContext *Acquire()
 {
@@ -68,7 +80,12 @@ inline SptContext *Acquire()
     {
         if (spt_cuda_abi_version() != SPT_ABI_VERSION) // this TU and the library disagree about the struct layouts
             throw std::runtime_error("CudaPathTracer: libspt_cuda.so was built from another revision of spt_cuda.h");
-        Check(spt_cuda_create(&s.ctx, s.device), "spt_cuda_create");
+        if (s.devices.size() > 1)
+            Check(spt_cuda_create_multi(&s.ctx, s.devices.data(), int(s.devices.size())), "spt_cuda_create_multi");
+        else
+            Check(spt_cuda_create(&s.ctx, s.devices[0]), "spt_cuda_create");
+        if (s.stagingLimit)
+            Check(spt_cuda_set_staging_limit(s.ctx, s.stagingLimit), "spt_cuda_set_staging_limit");
     }
     if (!s.sceneUploaded)
     {
@@ -98,38 +115,13 @@ inline void Shutdown()
     s.sceneUploaded = false;
 }
 
-inline void Render(RenderSegmentData segment, uint32_t passCap, uint32_t variant)
+inline void FillCameraAndParams(SptCamera &cam, SptParams &p, uint32_t passCap, uint32_t variant)
 {
     static_assert(sizeof(math::Vec4) == 16, "Vec4 must be 4 packed floats (Math.hpp:9-14)");
-    SptContext *ctx = Acquire();
-    SptCamera cam{};
     for (int k = 0; k < 16; ++k)
         cam.view[k] = viewMatrix.array[k];
     // the tracers only ever multiply the matrix with a w = 0 vector and read lanes 0..2 of the result, so row 3
     // and column 3 never reach a pixel; the reference's identity initialiser has a 1 there, its camera basis a 0
-    cam.view[3] = cam.view[7] = cam.view[11] = cam.view[12] = cam.view[13] = cam.view[14] = cam.view[15] = 0.f;
-    for (int k = 0; k < 3; ++k)
-    {
-        cam.eye[k] = eyePos.xyzw[k];
-        cam.sky[k] = initColor.xyzw[k];
-    }
-    SptParams p{};
-    p.width = g_width;
-    p.height = g_height;
-    p.depth = g_bounces;
-    p.pass_cap = passCap;
-    p.sample_begin = 0;
-    p.sample_end = g_samples;
-    p.seed = GetState().seed;
-    p.variant = variant;
-    p.flags = GetState().flags;
-    SptSegment const seg{segment.yBegin, segment.yEnd, segment.xBegin, segment.xEnd};
-    Check(spt_cuda_render(ctx, &cam, &p, seg, g_data, nullptr), "spt_cuda_render");
-}
-inline void FillCameraAndParams(SptCamera &cam, SptParams &p, uint32_t passCap, uint32_t variant)
-{
-    for (int k = 0; k < 16; ++k)
-        cam.view[k] = viewMatrix.array[k];
     cam.view[3] = cam.view[7] = cam.view[11] = cam.view[12] = cam.view[13] = cam.view[14] = cam.view[15] = 0.f;
     for (int k = 0; k < 3; ++k)
     {
@@ -147,14 +139,25 @@ inline void FillCameraAndParams(SptCamera &cam, SptParams &p, uint32_t passCap, 
     p.flags = GetState().flags;
 }
 
+inline void Render(RenderSegmentData segment, uint32_t passCap, uint32_t variant)
+{
+    SptContext *ctx = Acquire();
+    SptCamera cam{};
+    SptParams p{};
+    FillCameraAndParams(cam, p, passCap, variant);
+    SptSegment const seg{segment.yBegin, segment.yEnd, segment.xBegin, segment.xEnd};
+    Check(spt_cuda_render(ctx, &cam, &p, seg, g_data, nullptr), "spt_cuda_render");
+}
+
 // Progressive rendering of the whole image on the context-owned accumulator: the reference's live preview
 // (UpdateTexture re-reads g_data every frame while RenderJob threads fill it, Renderer.hpp:157-164,282-290,355) and its
 // progress lines (Renderer.hpp:285), as passes over the SAMPLES instead of tiles.  After pass k, g_data holds the image
 // of the first samplesDone samples and onPass(k, passes, samplesDone) is called.  Passes leave the bits of one
 // g_samples render.  firstSample > 0 resumes (accum4 = the checkpointed sums, width*height*4 floats).
+// accumEveryPass: accumOut4 is refreshed before EVERY onPass call (checkpoint after each pass), not only the last.
 template <typename OnPass>
 inline void RenderImageProgressiveCuda(uint32_t passes, uint32_t passCap, uint32_t variant, OnPass onPass, uint32_t firstSample = 0,
-                                       float const *resumeAccum4 = nullptr, float *accumOut4 = nullptr)
+                                       float const *resumeAccum4 = nullptr, float *accumOut4 = nullptr, bool accumEveryPass = false)
 {
     SptContext *ctx = Acquire();
     SptCamera cam{};
@@ -173,7 +176,7 @@ inline void RenderImageProgressiveCuda(uint32_t passes, uint32_t passCap, uint32
         p.sample_end = firstSample + uint32_t(uint64_t(todo) * (k + 1) / passes);
         Check(spt_cuda_progressive_add(ctx, &cam, &p, all), "spt_cuda_progressive_add");
         bool const last = k + 1 == passes;
-        Check(spt_cuda_progressive_image(ctx, all, g_data, last ? accumOut4 : nullptr), "spt_cuda_progressive_image");
+        Check(spt_cuda_progressive_image(ctx, all, g_data, (last || accumEveryPass) ? accumOut4 : nullptr), "spt_cuda_progressive_image");
         onPass(k + 1, passes, p.sample_end);
     }
 }

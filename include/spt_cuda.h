@@ -18,6 +18,8 @@
  *   spt_cuda_first_hit     cd::FindClosestIntersectionSphere + contact helpers on jitter-free pinhole rays
  *   spt_cuda_closest_hit   cd::FindClosestIntersectionSphere  include/Collision.hpp:87-109
  *   spt_cuda_set_scene     the SoA scene globals  include/Globals.hpp:31-37
+ *   spt_cuda_create_multi  the worker pool of RenderImageParallelMain  include/Renderer.hpp:257-302 (RenderJob :242-255):
+ *                          ONE call spreads one render over all workers -- here over several GPUs of one node
  *
  * Inputs the reference keeps in globals (scene, camera, image size, sample/bounce counts) are passed
  * explicitly; the host mirror include/CudaPathTracer.hpp gathers them from the globals.
@@ -86,12 +88,14 @@ enum {
                                   would fit whole (the default for lists above SPT_RESIDENT_LIMIT_BYTES) */
     SPT_FLAG_SPLIT = 32u,      /* megakernel (the DEFAULT, resident and streamed lists): trace the camera segment of every sample
                                   in a separate, fully convergent kernel with the camera form of the pre-filter (one float4 record
-                                  per sample -- direction + first-hit index -- staged in HBM in chunks of <= 64 GiB, smaller when
-                                  the device is short of memory), then run the bounce loop on secondary rays only.  Same bits as
-                                  the single kernel. */
+                                  per sample -- direction + first-hit index -- staged in HBM in chunks bounded by the staging
+                                  limit), then run the bounce loop on secondary rays only.  Same bits as the single kernel. */
     SPT_FLAG_SINGLE_KERNEL = 64u, /* megakernel: do not split; camera and secondary segments in one kernel */
-    SPT_FLAG_RESIDENT = 16u    /* megakernel: keep the whole list resident in shared memory whenever it fits at all, even at
+    SPT_FLAG_RESIDENT = 16u,   /* megakernel: keep the whole list resident in shared memory whenever it fits at all, even at
                                   the price of fewer CTAs per SM */
+    SPT_FLAG_SERIAL_CHUNKS = 128u /* split rendering, measurement: every kernel of every chunk on the main stream, one after the
+                                  other (no camera kernel under the tail of the previous bounce kernel), so that
+                                  SptTiming.primary_ms / secondary_ms are the kernels' own durations */
 };
 /* geometry + pre-filter bytes (36 B per sphere) up to which the whole list is staged once per CTA; four CTAs per SM
  * stay resident below it.  Longer lists stream (spt_streamed.cuh). */
@@ -112,7 +116,11 @@ typedef struct SptParams {
                                           the call renders only the bands with b % band_count == band_index: the
                                           interleaved pixel partition for several GPUs (disjoint pixels, so summing the
                                           per-GPU accumulators reproduces the single-GPU bits).  The reference's analogue
-                                          is RenderImageParallelMain's static tile grid (Renderer.hpp:264-274). */
+                                          is RenderImageParallelMain's static tile grid (Renderer.hpp:264-274).
+                                          Must be 0 / 1 on a multi-device context (the library partitions itself). */
+    uint32_t split_chunk;              /* split rendering: samples of every pixel traced per pair of kernel launches.
+                                          0 = as many as the staging limit allows (spt_cuda_set_staging_limit). */
+    uint32_t reserved;                 /* must be 0 */
 } SptParams;
 #define SPT_BAND_ROWS 8u
 
@@ -129,6 +137,10 @@ typedef struct SptTiming {
     float resolve_ms;   /* device time of the resolve kernel of the last call */
     uint32_t launches;  /* kernels launched by the last call */
     uint32_t reserved;
+    float primary_ms;   /* split rendering: device time of the camera kernels of the last call, summed over its chunks ... */
+    float secondary_ms; /* ... and of the bounce kernels.  Each kernel is bracketed by events on its own stream; with several
+                           chunks the camera kernel of chunk k+1 overlaps the tail of the bounce kernel of chunk k, so the two
+                           sums can exceed trace_ms (SPT_FLAG_SERIAL_CHUNKS makes them additive).  0 for the other kernels. */
 } SptTiming;
 
 typedef struct SptDeviceInfo {
@@ -144,7 +156,30 @@ typedef struct SptContext SptContext;
 
 /* lifetime.  `device` is a CUDA ordinal.  The context owns a stream, the device copy of the scene and scratch. */
 SPT_API int spt_cuda_create(SptContext **out, int device);
+/* One context over SEVERAL GPUs of this node (one host process; replaces the worker pool of RenderImageParallelMain,
+ * Renderer.hpp:257-302).  devices[0] is the primary device.  The scene is replicated; spt_cuda_render and the
+ * progressive entry points split every call over the devices -- sample ranges [k*S/n, (k+1)*S/n) of every pixel, or
+ * interleaved 8-row bands when a call has fewer samples than devices (spt_cuda_set_partition) -- each device tracing into
+ * its own float4 accumulator on its own stream; the accumulators are then combined over NVLink by a fused
+ * reduce-and-resolve kernel (every device sums and encodes one slice of the rows, reading its peers' accumulators
+ * through peer-mapped pointers in device order) and each device copies its slice of the image to the host buffer.
+ * Band partitions leave the single-GPU bits (disjoint pixels); sample ranges re-associate n partial sums per pixel.
+ * The device-pointer entry points (accumulate / resolve / set_stream) and the probes address devices[0] only.
+ * Peer access between all pairs is required (SPT_ERR_CUDA otherwise).  The same ordinal may be listed twice (two
+ * contexts on one GPU: how the path is tested on a single-GPU box). */
+#define SPT_MAX_DEVICES 16
+SPT_API int spt_cuda_create_multi(SptContext **out, const int *devices, int n_devices);
+SPT_API int spt_cuda_device_count(SptContext *ctx); /* devices behind this context (1 for spt_cuda_create) */
+enum { SPT_PARTITION_AUTO = 0, SPT_PARTITION_SAMPLES = 1, SPT_PARTITION_BANDS = 2 };
+SPT_API int spt_cuda_set_partition(SptContext *ctx, int partition); /* multi-device contexts; AUTO = samples when a call has >= n of them */
 SPT_API void spt_cuda_destroy(SptContext *ctx);
+/* Split rendering stages one 16-byte record per camera sample in device memory, in two buffers that alternate (the
+ * camera kernel of chunk k+1 runs on a second stream under the bounce kernel of chunk k).  `bytes` bounds BOTH buffers
+ * together, per device; 0 restores the default, SPT_DEFAULT_STAGING_BYTES.  Longer chunks waste fewer lane-iterations
+ * (a lane owns its pixel for a whole chunk); an application that owns the GPU may raise the limit.  The library never
+ * sizes this from the free device memory. */
+#define SPT_DEFAULT_STAGING_BYTES (8ull << 30)
+SPT_API int spt_cuda_set_staging_limit(SptContext *ctx, uint64_t bytes);
 /* run on a caller stream (cudaStream_t passed as void*; NULL is the legacy default stream) instead of
  * the context's own non-blocking stream; use_own != 0 restores the context's stream */
 SPT_API int spt_cuda_set_stream(SptContext *ctx, void *cuda_stream, int use_own);
@@ -201,8 +236,9 @@ SPT_API const char *spt_cuda_last_error(void);
 SPT_API const char *spt_cuda_version(void);
 
 /* Layout revision of the structs above.  A caller compiled against another revision of this header must not call in
-   (revision 2 appended band_count / band_index to SptParams): compare with SPT_ABI_VERSION once after loading. */
-#define SPT_ABI_VERSION 2u
+   (revision 2 appended band_count / band_index to SptParams, revision 3 split_chunk / reserved): compare with
+   SPT_ABI_VERSION once after loading. */
+#define SPT_ABI_VERSION 3u
 SPT_API uint32_t spt_cuda_abi_version(void);
 
 #ifdef __cplusplus

@@ -78,36 +78,67 @@ inline bool WritePfm(char const *path, uint32_t width, uint32_t height, float co
     return std::fclose(f) == 0;
 }
 
-// Accumulator checkpoint (resume a render later, or on another GPU): 32-byte header
-//   "SPTACC1\0", u32 width, u32 height, u32 samplesDone, u32 depth, u64 seed
-// then width*height float4 (sum r, sum g, sum b, count), little-endian, row y*width + x.
+// Accumulator checkpoint (resume a render later, or on another GPU): 48-byte header
+//   "SPTACC2\0", u32 width, u32 height, u32 samplesDone, u32 depth, u64 seed, u64 identity, u64 reserved
+// then width*height float4 (sum r, sum g, sum b, count), little-endian, row y*width + x.  `identity` is the caller's
+// fingerprint of everything else the sums depend on (scene arrays, camera, tracer semantics: RenderIdentity() below);
+// a loader that passes its own fingerprint refuses a file written for another render.
 struct AccumHeader
 {
     char magic[8];
     uint32_t width, height, samplesDone, depth;
     uint64_t seed;
+    uint64_t identity;
+    uint64_t reserved;
 };
-static_assert(sizeof(AccumHeader) == 32, "checkpoint header layout");
+static_assert(sizeof(AccumHeader) == 48, "checkpoint header layout");
 
-inline bool SaveAccum(char const *path, uint32_t width, uint32_t height, uint32_t samplesDone, uint32_t depth, uint64_t seed,
-                      float const *accum4)
+// FNV-1a over the bytes that decide a render besides size / depth / seed: the SoA scene globals, the camera, the sky, and
+// the tracer's semantics (pass cap).  Two renders with the same fingerprint accumulate the same per-sample radiance.
+inline uint64_t RenderIdentity(uint32_t passCap)
 {
-    FILE *f = std::fopen(path, "wb");
-    if (!f)
-        return false;
-    AccumHeader h{{'S', 'P', 'T', 'A', 'C', 'C', '1', 0}, width, height, samplesDone, depth, seed};
-    bool ok = std::fwrite(&h, sizeof(h), 1, f) == 1;
-    ok = ok && std::fwrite(accum4, sizeof(float) * 4u, size_t(width) * height, f) == size_t(width) * height;
-    return (std::fclose(f) == 0) && ok;
+    uint64_t h = 1469598103934665603ull;
+    auto mix = [&h](void const *p, size_t n) {
+        unsigned char const *b = static_cast<unsigned char const *>(p);
+        for (size_t i = 0; i < n; ++i)
+            h = (h ^ b[i]) * 1099511628211ull;
+    };
+    uint32_t const n = g_sphereNumber;
+    mix(&n, sizeof(n));
+    mix(g_spheres.data(), sizeof(g_spheres[0]) * n);
+    mix(g_radii.data(), sizeof(float) * n);
+    mix(g_materials.data(), sizeof(g_materials[0]) * n);
+    mix(g_colors.data(), sizeof(g_colors[0]) * n);
+    mix(g_diffuses.data(), sizeof(float) * n);
+    mix(viewMatrix.array, sizeof(viewMatrix.array));
+    mix(eyePos.xyzw, sizeof(eyePos.xyzw));
+    mix(initColor.xyzw, sizeof(initColor.xyzw));
+    mix(&passCap, sizeof(passCap));
+    return h ? h : 1;
 }
 
-// returns false when the file is missing, malformed or of another image size
-inline bool LoadAccum(char const *path, uint32_t width, uint32_t height, AccumHeader &h, std::vector<float> &accum4)
+inline bool SaveAccum(char const *path, uint32_t width, uint32_t height, uint32_t samplesDone, uint32_t depth, uint64_t seed,
+                      float const *accum4, uint64_t identity = 0)
+{
+    std::string const tmp = std::string(path) + ".tmp"; // written whole, then renamed: an interrupted run leaves the old file
+    FILE *f = std::fopen(tmp.c_str(), "wb");
+    if (!f)
+        return false;
+    AccumHeader h{{'S', 'P', 'T', 'A', 'C', 'C', '2', 0}, width, height, samplesDone, depth, seed, identity, 0};
+    bool ok = std::fwrite(&h, sizeof(h), 1, f) == 1;
+    ok = ok && std::fwrite(accum4, sizeof(float) * 4u, size_t(width) * height, f) == size_t(width) * height;
+    ok = (std::fclose(f) == 0) && ok;
+    return ok && std::rename(tmp.c_str(), path) == 0;
+}
+
+// returns false when the file is missing, malformed, of another image size, or -- identity != 0 -- written for another render
+inline bool LoadAccum(char const *path, uint32_t width, uint32_t height, AccumHeader &h, std::vector<float> &accum4, uint64_t identity = 0)
 {
     FILE *f = std::fopen(path, "rb");
     if (!f)
         return false;
-    bool ok = std::fread(&h, sizeof(h), 1, f) == 1 && std::string(h.magic, 7) == "SPTACC1" && h.width == width && h.height == height;
+    bool ok = std::fread(&h, sizeof(h), 1, f) == 1 && std::string(h.magic, 7) == "SPTACC2" && h.width == width && h.height == height;
+    ok = ok && (identity == 0 || h.identity == identity);
     if (ok)
     {
         accum4.resize(size_t(width) * height * 4u);

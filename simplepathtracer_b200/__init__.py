@@ -26,10 +26,15 @@ from .binding import (  # noqa: F401
     FLAG_RESIDENT,
     FLAG_SPLIT,
     FLAG_SINGLE_KERNEL,
+    FLAG_SERIAL_CHUNKS,
     DIFFUSE,
     REFLECTIVE,
     REFRACTIVE,
     SKYBOX,
+    PARTITION_AUTO,
+    PARTITION_SAMPLES,
+    PARTITION_BANDS,
+    DEFAULT_STAGING_BYTES,
     init_spheres,
     generate_spheres,
     generate_metal_glass,
@@ -43,4 +48,4 @@ from .binding import (  # noqa: F401
     load_accum,
 )
 
-__version__ = "0.1.0"
+__version__ = "0.2.0"

@@ -15,9 +15,12 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_NAME = "libspt_cuda.so"
 
-ABI_VERSION = 2  # SPT_ABI_VERSION of include/spt_cuda.h
+ABI_VERSION = 3  # SPT_ABI_VERSION of include/spt_cuda.h
+PARTITION_AUTO, PARTITION_SAMPLES, PARTITION_BANDS = 0, 1, 2
+DEFAULT_STAGING_BYTES = 8 << 30  # SPT_DEFAULT_STAGING_BYTES
 MEGAKERNEL, WAVEFRONT = 0, 1
 FLAG_STRICT_LOOP, FLAG_COUNTERS, FLAG_CROSS_CHECK, FLAG_STREAMED, FLAG_RESIDENT, FLAG_SPLIT, FLAG_SINGLE_KERNEL = 1, 2, 4, 8, 16, 32, 64
+FLAG_SERIAL_CHUNKS = 128
 SKYBOX, REFLECTIVE, REFRACTIVE, DIFFUSE = 0, 1, 2, 3  # include/Definitions.hpp:7-13
 
 f32p = C.POINTER(C.c_float)
@@ -142,6 +145,8 @@ class _CParams(C.Structure):
         ("flags", C.c_uint32),
         ("band_count", C.c_uint32),
         ("band_index", C.c_uint32),
+        ("split_chunk", C.c_uint32),
+        ("reserved", C.c_uint32),
     ]
 
 
@@ -153,7 +158,8 @@ class Counters(C.Structure):
 
 
 class Timing(C.Structure):
-    _fields_ = [("trace_ms", C.c_float), ("resolve_ms", C.c_float), ("launches", C.c_uint32), ("reserved", C.c_uint32)]
+    _fields_ = [("trace_ms", C.c_float), ("resolve_ms", C.c_float), ("launches", C.c_uint32), ("reserved", C.c_uint32),
+                ("primary_ms", C.c_float), ("secondary_ms", C.c_float)]
 
 
 class DeviceInfo(C.Structure):
@@ -169,7 +175,8 @@ class DeviceInfo(C.Structure):
 
 
 EXPORTS = [
-    "spt_cuda_create", "spt_cuda_destroy", "spt_cuda_set_stream", "spt_cuda_device_info", "spt_cuda_set_scene",
+    "spt_cuda_create", "spt_cuda_create_multi", "spt_cuda_device_count", "spt_cuda_set_partition", "spt_cuda_set_staging_limit",
+    "spt_cuda_destroy", "spt_cuda_set_stream", "spt_cuda_device_info", "spt_cuda_set_scene",
     "spt_cuda_render", "spt_cuda_accumulate", "spt_cuda_resolve", "spt_cuda_synchronize", "spt_cuda_first_hit",
     "spt_cuda_progressive_begin", "spt_cuda_progressive_add", "spt_cuda_progressive_image", "spt_cuda_progressive_load",
     "spt_cuda_closest_hit", "spt_cuda_get_counters", "spt_cuda_reset_counters", "spt_cuda_get_timing",
@@ -200,6 +207,10 @@ def load_library():
     L.spt_cuda_last_error.restype = C.c_char_p
     L.spt_cuda_version.restype = C.c_char_p
     L.spt_cuda_create.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+    L.spt_cuda_create_multi.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int]
+    L.spt_cuda_device_count.argtypes = [C.c_void_p]
+    L.spt_cuda_set_partition.argtypes = [C.c_void_p, C.c_int]
+    L.spt_cuda_set_staging_limit.argtypes = [C.c_void_p, C.c_uint64]
     L.spt_cuda_destroy.argtypes = [C.c_void_p]
     L.spt_cuda_destroy.restype = None
     L.spt_cuda_set_stream.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
@@ -262,15 +273,34 @@ def _devptr(x) -> int:
 
 
 class PathTracer:
-    """One context on one GPU: RenderSegment / RenderSegmentTask as CUDA (include/spt_cuda.h)."""
+    """One context: RenderSegment / RenderSegmentTask as CUDA (include/spt_cuda.h).  `device` is one CUDA ordinal, or a
+    sequence of them for a multi-device context (spt_cuda_create_multi: one host process, one render spread over the
+    GPUs, accumulators combined over NVLink by the library's fused reduce-and-resolve kernel)."""
 
-    def __init__(self, device: int = 0):
+    def __init__(self, device=0):
         self.L = load_library()
         h = C.c_void_p()
-        self._check(self.L.spt_cuda_create(C.byref(h), device))
+        if isinstance(device, (list, tuple)):
+            devs = (C.c_int * len(device))(*[int(d) for d in device])
+            self._check(self.L.spt_cuda_create_multi(C.byref(h), devs, len(device)))
+            self.devices = [int(d) for d in device]
+        else:
+            self._check(self.L.spt_cuda_create(C.byref(h), device))
+            self.devices = [int(device)]
         self.h = h
-        self.device = device
+        self.device = self.devices[0]
         self.scene: Optional[Scene] = None
+        self.split_chunk = 0  # SptParams.split_chunk of every call made through this object (0 = as the staging limit allows)
+
+    def device_count(self) -> int:
+        return int(self.L.spt_cuda_device_count(self.h))
+
+    def set_partition(self, partition: int) -> None:
+        self._check(self.L.spt_cuda_set_partition(self.h, int(partition)))
+
+    def set_staging_limit(self, nbytes: int) -> None:
+        """Bound of the first-hit staging buffers of split rendering, per device (0 = SPT_DEFAULT_STAGING_BYTES)."""
+        self._check(self.L.spt_cuda_set_staging_limit(self.h, int(nbytes)))
 
     def _check(self, rc: int):
         if rc != 0:
@@ -316,7 +346,7 @@ class PathTracer:
 
     def _params(self, width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags, bands=None) -> _CParams:
         count, index = bands if bands else (0, 0)  # (band_count, band_index): interleaved 8-row bands, include/spt_cuda.h
-        return _CParams(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags, count, index)
+        return _CParams(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags, count, index, int(self.split_chunk), 0)
 
     def render(self, cam, width, height, spp, depth, pass_cap=0, seed=1, seg=None, sample_begin=0, variant=MEGAKERNEL,
                flags=0, rgb8: Optional[np.ndarray] = None, want_accum: bool = False):
@@ -402,7 +432,8 @@ class PathTracer:
     def timing(self) -> dict:
         t = Timing()
         self._check(self.L.spt_cuda_get_timing(self.h, C.byref(t)))
-        return {"trace_ms": float(t.trace_ms), "resolve_ms": float(t.resolve_ms), "launches": int(t.launches)}
+        return {"trace_ms": float(t.trace_ms), "resolve_ms": float(t.resolve_ms), "launches": int(t.launches),
+                "primary_ms": float(t.primary_ms), "secondary_ms": float(t.secondary_ms)}
 
     def measure_fp32_peak(self):
         a, b = C.c_float(), C.c_float()

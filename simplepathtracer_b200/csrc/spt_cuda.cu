@@ -5,7 +5,6 @@
 #include "spt_wavefront.cuh"
 #include "spt_streamed.cuh"
 #include "spt_split.cuh"
-#include "spt_tensor_filter.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -46,7 +45,12 @@ struct SptContext
     cudaDeviceProp prop{};
     cudaStream_t ownStream = nullptr;
     cudaStream_t stream = nullptr;
+    cudaStream_t auxStream = nullptr; // split rendering: the camera kernel of chunk k+1 runs here, under the bounce kernel of chunk k
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t evFork = nullptr, evPrimary[2] = {nullptr, nullptr}, evSecondary[2] = {nullptr, nullptr};
+    cudaEvent_t evDone = nullptr; // multi-device: this device's accumulator is complete
+    std::vector<cudaEvent_t> evKernel; // split rendering: 4 timing events per chunk (camera begin/end, bounce begin/end)
+    uint32_t timedChunks = 0;
     std::mutex lock; // the reference calls its tracers from several host threads (Renderer.hpp:282-290)
 
     uint32_t n = 0;
@@ -64,7 +68,7 @@ struct SptContext
     float4 *dAccum = nullptr;
     uint8_t *dRgb = nullptr;
     size_t accumPixels = 0;
-    // split rendering: camera-form filter blob (rebuilt when the eye changes) and the first-hit staging buffer
+    // split rendering: camera-form filter blob (rebuilt when the eye changes) and the first-hit staging buffers
     spt::FilterPair *dPairsCam = nullptr;
     std::vector<unsigned char> hostBlob; // the general blob, kept to derive the camera form
     std::vector<double> hostGeom;        // cx, cy, cz, r per SLOT in binary64
@@ -72,6 +76,7 @@ struct SptContext
     float camEpsT = 0.f;
     float4 *dFirstHits = nullptr;
     size_t firstHitsBytes = 0;
+    uint64_t stagingLimit = SPT_DEFAULT_STAGING_BYTES;
     // context-owned accumulator of the progressive entry points
     float4 *dProgAccum = nullptr;
     uint8_t *dProgRgb = nullptr;
@@ -79,11 +84,10 @@ struct SptContext
     void *dProbe = nullptr;
     size_t probeBytes = 0;
     size_t maxSmemOptin = 0;
-#if SPT_TENSOR_FILTER
-    float *dTensorB = nullptr; // sphere matrix of the tensor-core filter (spt_tensor_host.hpp)
-    float *dTensorBCam = nullptr; // its camera form, rebuilt with the camera blob when the eye changes
-    uint32_t tensorRows = 0;
-#endif
+
+    // multi-device contexts (spt_cuda_create_multi): `all` = this context followed by one internal context per further device
+    std::vector<SptContext *> all;
+    int partition = SPT_PARTITION_AUTO;
 };
 
 namespace
@@ -205,19 +209,9 @@ int ensure_camera_blob(SptContext *c, const float eye[3])
     if (!c->dPairsCam)
         SPT_CUDA_CHECK(cudaMalloc(&c->dPairsCam, blob.size() + 16));
     SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream)); // an earlier launch may still read the previous camera's records
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->auxStream));
     if (!blob.empty())
         SPT_CUDA_CHECK(cudaMemcpy(c->dPairsCam, blob.data(), blob.size(), cudaMemcpyHostToDevice));
-#if SPT_TENSOR_FILTER
-    if (nSlots > 0)
-    {
-        std::vector<float> B;
-        double const e[3] = {ex, ey, ez};
-        spt::build_tensor_matrix_cam(c->hostGeom, nSlots, e, B);
-        if (!c->dTensorBCam)
-            SPT_CUDA_CHECK(cudaMalloc(&c->dTensorBCam, B.size() * sizeof(float)));
-        SPT_CUDA_CHECK(cudaMemcpy(c->dTensorBCam, B.data(), B.size() * sizeof(float), cudaMemcpyHostToDevice));
-    }
-#endif
     c->camEye[0] = eye[0];
     c->camEye[1] = eye[1];
     c->camEye[2] = eye[2];
@@ -262,8 +256,12 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
         return fail(SPT_ERR_NO_SCENE, "spt_cuda_set_scene has not been called");
     if (prm->variant != SPT_VARIANT_MEGAKERNEL && prm->variant != SPT_VARIANT_WAVEFRONT)
         return fail(SPT_ERR_INVALID, "unknown variant");
+    if (prm->reserved != 0u)
+        return fail(SPT_ERR_INVALID, "SptParams.reserved must be 0 (struct built against another revision of spt_cuda.h?)");
     c->timing.trace_ms = 0.f;
     c->timing.launches = 0;
+    c->timing.primary_ms = c->timing.secondary_ms = 0.f;
+    c->timedChunks = 0;
     uint32_t const segW = seg.xEnd - seg.xBegin, segH = seg.yEnd - seg.yBegin;
     if (segW == 0 || segH == 0 || prm->sample_end <= prm->sample_begin)
         return SPT_OK;
@@ -369,49 +367,39 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             p.filterCam.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairsCam + c->filter.nSlots / 2);
             p.filterCam.epsTCam = c->camEpsT;
             size_t const pixels = size_t(segW) * std::min<size_t>(segH, size_t(myBands) * SPT_BAND_ROWS); // rows the launch covers
-            // Staging budget.  A lane owns its pixel for a whole chunk and the warp waits for its slowest lane, so longer
-            // chunks waste fewer lane-iterations (config 3 on B200: 8 / 16 / 32 / 64 GiB = 5 815 / 5 893 / 5 963 / 6 006
-            // Msamples/s, profiles/r1_ab_chunk_and_cta_shape.txt): up to 64 GiB (512 spp of a 3840x2160 render), but never
-            // more than 45 % of what the device has free.
-            size_t cap = size_t(64) << 30;
-            {
-                size_t freeB = 0, totalB = 0;
-                if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess)
-                    cap = std::min(cap, (freeB + c->firstHitsBytes) / 100 * 45);
-                else
-                    (void)cudaGetLastError();
-            }
-            if (const char *knob = std::getenv("SPT_SPLIT_CAP_MIB")) // experiments: staging budget in MiB
-                cap = std::max<size_t>(size_t(1) << 20, size_t(std::atoll(knob)) << 20);
+            // Staging.  A lane owns its pixel for a whole chunk of samples and the warp waits for its slowest lane, so longer
+            // chunks waste fewer lane-iterations -- but the budget is the caller's (spt_cuda_set_staging_limit, 8 GiB unless
+            // raised), never a share of whatever the device has free.  When the sample range needs several chunks the budget
+            // is cut into TWO buffers that alternate: the camera kernel of chunk k+1 runs on the auxiliary stream while the
+            // bounce kernel of chunk k drains (its last CTAs leave SMs idle that the camera kernel's CTAs take).
+            size_t const recBytes = pixels * sizeof(float4); // one sample of every pixel of the launch
+            size_t const pad = 256;                          // the consumer prefetches four records past the one it reads
             uint32_t const total = prm->sample_end - prm->sample_begin;
-            uint32_t chunk = uint32_t(std::max<size_t>(1, std::min<size_t>(total, cap / (pixels * sizeof(float4)))));
-            if (const char *knob = std::getenv("SPT_SPLIT_CHUNK")) // test knob: force several chunks on small renders
-                chunk = std::max<uint32_t>(1u, std::min<uint32_t>(chunk, uint32_t(std::atoi(knob))));
-            size_t const pad = 256; // the consumer prefetches four records past the one it reads
-            if (pixels * chunk * sizeof(float4) + pad > c->firstHitsBytes)
+            size_t const limit = std::max<size_t>(size_t(c->stagingLimit), 2 * (recBytes + pad));
+            uint32_t chunk = total;
+            if (prm->split_chunk)
+                chunk = std::min(chunk, prm->split_chunk);
+            if (size_t(chunk) * recBytes + pad > limit)
+                chunk = uint32_t(std::max<size_t>(1, (limit / 2 - pad) / recBytes));
+            uint32_t const nChunks = (total + chunk - 1) / chunk;
+            uint32_t const nBuffers = nChunks > 1 ? 2u : 1u;
+            size_t const bufBytes = (size_t(chunk) * recBytes + pad + 255) & ~size_t(255);
+            if (bufBytes * nBuffers > c->firstHitsBytes)
             {
                 SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+                SPT_CUDA_CHECK(cudaStreamSynchronize(c->auxStream));
                 cudaFree(c->dFirstHits);
                 c->dFirstHits = nullptr;
                 c->firstHitsBytes = 0;
-                // a device short of memory gets smaller chunks (more launches), not an error
-                for (;;)
+                cudaError_t const ce = cudaMalloc(&c->dFirstHits, bufBytes * nBuffers);
+                if (ce != cudaSuccess)
                 {
-                    size_t const need = pixels * chunk * sizeof(float4) + pad;
-                    cudaError_t const ce = cudaMalloc(&c->dFirstHits, need);
-                    if (ce == cudaSuccess)
-                    {
-                        c->firstHitsBytes = need;
-                        break;
-                    }
-                    (void)cudaGetLastError();
                     c->dFirstHits = nullptr;
-                    if (chunk == 1)
-                        return fail(SPT_ERR_CUDA, "cudaMalloc of the first-hit staging buffer failed", ce);
-                    chunk = (chunk + 1) / 2;
+                    (void)cudaGetLastError();
+                    return fail(SPT_ERR_CUDA, "cudaMalloc of the first-hit staging buffers failed (lower spt_cuda_set_staging_limit)", ce);
                 }
+                c->firstHitsBytes = bufBytes * nBuffers;
             }
-            p.firstHits = c->dFirstHits;
             void (*primary)(const spt::TraceParams) = streamed ? spt::primary_hits_streamed : spt::primary_hits_kernel<2, spt::SplitShape>;
             void (*secondary)(const spt::TraceParams) = streamed ? spt::trace_secondary_streamed : spt::trace_secondary<2, spt::SplitShape>;
             // the resident kernels run smaller CTAs than the rest (spt_split.cuh, SplitShape)
@@ -419,44 +407,46 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             dim3 const sBlock(streamed ? spt::kBlockThreads : spt::SplitShape::kThreads);
             SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
             SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-            size_t smem2 = smem, smem1 = smem;
-            dim3 sGrid2 = sGrid, sBlock2 = sBlock, sGrid1 = sGrid, sBlock1 = sBlock;
-#if SPT_TENSOR_FILTER
-            // experimental build: the resident bounce kernel takes its discriminants from the tensor core unless SPT_TENSOR=0
+            // camera kernels on the auxiliary stream (after everything queued on the main stream so far), bounce kernels on
+            // the main stream: P(k) needs buffer k % 2 free (S(k-2) done), S(k) needs P(k); S(k) after S(k-1) by stream order
+            // (the per-pixel running sums continue across chunks).  Every camera kernel is waited for by a bounce kernel on
+            // the main stream, so the main stream alone orders the caller's later work.
+            bool const overlap = nBuffers > 1 && !(prm->flags & SPT_FLAG_SERIAL_CHUNKS);
+            cudaStream_t const sp = overlap ? c->auxStream : c->stream;
+            while (c->evKernel.size() < size_t(nChunks) * 4)
             {
-                const char *knob = std::getenv("SPT_TENSOR");
-                if (!streamed && c->dTensorB && !(knob && knob[0] == '0'))
-                {
-                    p.tensorB = c->dTensorB;
-                    p.tensorRows = c->tensorRows;
-                    secondary = spt::trace_secondary_tc;
-                    sGrid2 = dim3((segW + spt::TensorShape::kTileW - 1) / spt::TensorShape::kTileW, myBands);
-                    sBlock2 = dim3(spt::TensorShape::kThreads);
-                    smem2 = ((geomBytes + pairBytes + 127) & ~size_t(127)) + spt::tensor_b_bytes(c->tensorRows) +
-                            size_t(spt::kTensorAcc) * spt::kTensorABytes;
-                    SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem2)));
-                }
-                // ... and the camera kernel unless SPT_TENSOR_PRIMARY=0
-                knob = std::getenv("SPT_TENSOR_PRIMARY");
-                if (!streamed && c->dTensorBCam && !(knob && knob[0] == '0'))
-                {
-                    p.tensorBCam = c->dTensorBCam;
-                    p.tensorRows = c->tensorRows;
-                    primary = spt::primary_hits_tc;
-                    sGrid1 = dim3((segW + spt::TensorShape::kTileW - 1) / spt::TensorShape::kTileW, myBands);
-                    sBlock1 = dim3(spt::TensorShape::kThreads);
-                    smem1 = ((geomBytes + pairBytes + 127) & ~size_t(127)) + spt::tensor_b_bytes_cam(c->tensorRows) +
-                            size_t(spt::kTensorAcc) * spt::kTensorABytesCam;
-                    SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem1)));
-                }
+                cudaEvent_t e = nullptr;
+                SPT_CUDA_CHECK(cudaEventCreate(&e));
+                c->evKernel.push_back(e);
             }
-#endif
-            for (uint32_t s0 = prm->sample_begin; s0 < prm->sample_end; s0 += chunk)
+            c->timedChunks = nChunks;
+            if (overlap)
             {
+                SPT_CUDA_CHECK(cudaEventRecord(c->evFork, c->stream));
+                SPT_CUDA_CHECK(cudaStreamWaitEvent(sp, c->evFork, 0));
+            }
+            uint32_t k = 0;
+            for (uint32_t s0 = prm->sample_begin; s0 < prm->sample_end; s0 += chunk, ++k)
+            {
+                uint32_t const b = k % nBuffers;
                 p.sampleBegin = s0;
                 p.sampleEnd = std::min(prm->sample_end, s0 + chunk);
-                primary<<<sGrid1, sBlock1, smem1, c->stream>>>(p);
-                secondary<<<sGrid2, sBlock2, smem2, c->stream>>>(p);
+                p.firstHits = reinterpret_cast<float4 *>(reinterpret_cast<unsigned char *>(c->dFirstHits) + size_t(b) * bufBytes);
+                if (overlap && k >= 2)
+                    SPT_CUDA_CHECK(cudaStreamWaitEvent(sp, c->evSecondary[b], 0));
+                SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * k + 0], sp));
+                primary<<<sGrid, sBlock, smem, sp>>>(p);
+                SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * k + 1], sp));
+                if (overlap)
+                {
+                    SPT_CUDA_CHECK(cudaEventRecord(c->evPrimary[b], sp));
+                    SPT_CUDA_CHECK(cudaStreamWaitEvent(c->stream, c->evPrimary[b], 0));
+                }
+                SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * k + 2], c->stream));
+                secondary<<<sGrid, sBlock, smem, c->stream>>>(p);
+                SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * k + 3], c->stream));
+                if (overlap)
+                    SPT_CUDA_CHECK(cudaEventRecord(c->evSecondary[b], c->stream));
                 c->timing.launches += 2;
             }
             c->timing.launches -= 1; // the common tail below counts one
@@ -496,20 +486,9 @@ int launch_resolve(SptContext *c, const float4 *dAccum, uint32_t width, uint32_t
     c->timing.launches += 1;
     return SPT_OK;
 }
-} // namespace
 
-extern "C"
+int create_one(SptContext **out, int device)
 {
-
-const char *spt_cuda_last_error(void) { return g_lastError.c_str(); }
-const char *spt_cuda_version(void) { return "simplepathtracer_b200 0.1 (sm_100a)"; }
-uint32_t spt_cuda_abi_version(void) { return SPT_ABI_VERSION; }
-
-int spt_cuda_create(SptContext **out, int device)
-{
-    if (!out)
-        return fail(SPT_ERR_INVALID, "out is null");
-    *out = nullptr;
     int count = 0;
     cudaError_t ce = cudaGetDeviceCount(&count);
     if (ce != cudaSuccess || count <= 0)
@@ -522,8 +501,14 @@ int spt_cuda_create(SptContext **out, int device)
     ce = cudaGetDeviceProperties(&c->prop, device);
     if (ce == cudaSuccess)
         ce = cudaStreamCreateWithFlags(&c->ownStream, cudaStreamNonBlocking);
+    if (ce == cudaSuccess)
+        ce = cudaStreamCreateWithFlags(&c->auxStream, cudaStreamNonBlocking);
     for (int i = 0; i < 4 && ce == cudaSuccess; ++i)
         ce = cudaEventCreate(&c->ev[i]);
+    cudaEvent_t *const sync[] = {&c->evFork, &c->evPrimary[0], &c->evPrimary[1], &c->evSecondary[0], &c->evSecondary[1], &c->evDone};
+    for (cudaEvent_t *e : sync)
+        if (ce == cudaSuccess)
+            ce = cudaEventCreateWithFlags(e, cudaEventDisableTiming);
     if (ce == cudaSuccess)
         ce = cudaMalloc(&c->dCounters, 8 * sizeof(unsigned long long));
     if (ce == cudaSuccess)
@@ -539,12 +524,14 @@ int spt_cuda_create(SptContext **out, int device)
     return SPT_OK;
 }
 
-void spt_cuda_destroy(SptContext *c)
+void destroy_one(SptContext *c)
 {
     if (!c)
         return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    if (c->auxStream)
+        cudaStreamSynchronize(c->auxStream);
     cudaFree(c->dGeom);
     cudaFree(c->dShade);
     cudaFree(c->dMat);
@@ -558,16 +545,311 @@ void spt_cuda_destroy(SptContext *c)
     cudaFree(c->dProgRgb);
     cudaFree(c->dPairsCam);
     cudaFree(c->dFirstHits);
-#if SPT_TENSOR_FILTER
-    cudaFree(c->dTensorB);
-    cudaFree(c->dTensorBCam);
-#endif
     for (auto &e : c->ev)
+        if (e)
+            cudaEventDestroy(e);
+    for (cudaEvent_t e : c->evKernel)
+        cudaEventDestroy(e);
+    for (cudaEvent_t e : {c->evFork, c->evPrimary[0], c->evPrimary[1], c->evSecondary[0], c->evSecondary[1], c->evDone})
         if (e)
             cudaEventDestroy(e);
     if (c->ownStream)
         cudaStreamDestroy(c->ownStream);
+    if (c->auxStream)
+        cudaStreamDestroy(c->auxStream);
     delete c;
+}
+
+// the scene as every device receives it, prepared once on the host
+struct HostScene
+{
+    uint32_t n = 0;
+    std::vector<float4> geom, shade;
+    const uint8_t *materials = nullptr;
+    std::vector<unsigned char> blob;
+    std::vector<uint32_t> big;
+    std::vector<double> slotGeom;
+    uint32_t nSlots = 0;
+    float amax = 0.f;
+};
+
+// Build the new device scene completely, THEN retire the old one: a failed allocation leaves the context as it was.
+int upload_scene(SptContext *c, const HostScene &hs)
+{
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    float4 *dGeom = nullptr, *dShade = nullptr;
+    uint8_t *dMat = nullptr;
+    spt::FilterPair *dPairs = nullptr;
+    uint32_t *dBigIdx = nullptr;
+    cudaError_t ce = cudaMalloc(&dPairs, hs.blob.size() + 16);
+    if (ce == cudaSuccess)
+        ce = cudaMalloc(&dBigIdx, (hs.big.size() + 1) * sizeof(uint32_t));
+    if (ce == cudaSuccess)
+        ce = cudaMalloc(&dGeom, hs.n * sizeof(float4));
+    if (ce == cudaSuccess)
+        ce = cudaMalloc(&dShade, hs.n * sizeof(float4));
+    if (ce == cudaSuccess)
+        ce = cudaMalloc(&dMat, hs.n);
+    if (ce == cudaSuccess && !hs.blob.empty())
+        ce = cudaMemcpy(dPairs, hs.blob.data(), hs.blob.size(), cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess && !hs.big.empty())
+        ce = cudaMemcpy(dBigIdx, hs.big.data(), hs.big.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess)
+        ce = cudaMemcpy(dGeom, hs.geom.data(), hs.n * sizeof(float4), cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess)
+        ce = cudaMemcpy(dShade, hs.shade.data(), hs.n * sizeof(float4), cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess)
+        ce = cudaMemcpy(dMat, hs.materials, hs.n, cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess)
+        ce = cudaStreamSynchronize(c->stream); // launches that still read the old scene
+    if (ce == cudaSuccess)
+        ce = cudaStreamSynchronize(c->auxStream);
+    if (ce != cudaSuccess)
+    {
+        cudaFree(dPairs);
+        cudaFree(dBigIdx);
+        cudaFree(dGeom);
+        cudaFree(dShade);
+        cudaFree(dMat);
+        return fail(SPT_ERR_CUDA, "spt_cuda_set_scene: upload failed, the previous scene is kept", ce);
+    }
+    cudaFree(c->dGeom);
+    cudaFree(c->dShade);
+    cudaFree(c->dMat);
+    cudaFree(c->dPairs);
+    cudaFree(c->dBigIdx);
+    cudaFree(c->dPairsCam); // sized by the scene; ensure_camera_blob rebuilds it
+    c->dGeom = dGeom;
+    c->dShade = dShade;
+    c->dMat = dMat;
+    c->dPairs = dPairs;
+    c->dBigIdx = dBigIdx;
+    c->dPairsCam = nullptr;
+    c->camEye[0] = c->camEye[1] = c->camEye[2] = NAN;
+    c->hostBlob = hs.blob;
+    c->hostGeom = hs.slotGeom;
+    c->filter.pairs = dPairs;
+    c->filter.nSlots = hs.nSlots;
+    c->filter.slotIdx = reinterpret_cast<const uint32_t *>(dPairs + hs.nSlots / 2);
+    c->filter.bigIdx = dBigIdx;
+    c->filter.nBig = uint32_t(hs.big.size());
+    c->filter.amax = hs.amax;
+    c->n = hs.n;
+    return SPT_OK;
+}
+
+// segment of the device image / accumulator -> the caller's host buffers (pixel (x,y) lives in byte row H-1-y)
+int copy_segment_to_host(SptContext *c, uint32_t W, uint32_t H, SptSegment seg, const uint8_t *dRgb, uint8_t *rgb8, const float4 *dAccum,
+                         float *accum4)
+{
+    uint32_t const segW = seg.xEnd - seg.xBegin, segH = seg.yEnd - seg.yBegin;
+    if (segW == 0 || segH == 0)
+        return SPT_OK;
+    uint32_t const rowTop = H - seg.yEnd; // flipped
+    if (rgb8)
+        SPT_CUDA_CHECK(cudaMemcpy2DAsync(rgb8 + (size_t(rowTop) * W + seg.xBegin) * 3, size_t(W) * 3,
+                                         dRgb + (size_t(rowTop) * W + seg.xBegin) * 3, size_t(W) * 3, size_t(segW) * 3, segH,
+                                         cudaMemcpyDeviceToHost, c->stream));
+    if (accum4)
+        SPT_CUDA_CHECK(cudaMemcpy2DAsync(accum4 + (size_t(seg.yBegin) * W + seg.xBegin) * 4, size_t(W) * sizeof(float4),
+                                         dAccum + size_t(seg.yBegin) * W + seg.xBegin, size_t(W) * sizeof(float4),
+                                         size_t(segW) * sizeof(float4), segH, cudaMemcpyDeviceToHost, c->stream));
+    return SPT_OK;
+}
+
+// One call spread over the devices of a multi-device context (Renderer.hpp:257-302's worker pool): device k traces samples
+// [b + k S / n, b + (k + 1) S / n) of every pixel of the segment, or -- fewer samples than devices, or by request -- all
+// samples of the interleaved 8-row bands b with b % n == k, into accOf(device).  Asynchronous on each device's stream.
+template <typename AccOf>
+int trace_multi(SptContext *c, const SptCamera *cam, const SptParams *prm, SptSegment seg, AccOf accOf)
+{
+    if (prm->band_count > 1u)
+        return fail(SPT_ERR_INVALID, "band_count / band_index belong to single-device contexts: a multi-device context partitions itself");
+    uint32_t const n = uint32_t(c->all.size());
+    uint32_t const total = prm->sample_end > prm->sample_begin ? prm->sample_end - prm->sample_begin : 0u;
+    bool const bySamples = c->partition == SPT_PARTITION_SAMPLES || (c->partition == SPT_PARTITION_AUTO && total >= n);
+    for (uint32_t k = 0; k < n; ++k)
+    {
+        SptContext *d = c->all[k];
+        SPT_CUDA_CHECK(cudaSetDevice(d->device));
+        if (!accOf(d))
+            return fail(SPT_ERR_INVALID, "accumulator missing on a device of the context");
+        SptParams pk = *prm;
+        if (bySamples)
+        {
+            pk.sample_begin = prm->sample_begin + uint32_t(uint64_t(total) * k / n);
+            pk.sample_end = prm->sample_begin + uint32_t(uint64_t(total) * (k + 1) / n);
+        }
+        else
+        {
+            pk.band_count = n;
+            pk.band_index = k;
+        }
+        int const rc = launch_trace(d, cam, &pk, seg, accOf(d));
+        if (rc)
+            return rc;
+    }
+    return SPT_OK;
+}
+
+// The exchange step: every device sums one slice of the segment's rows over all devices' accumulators (peer loads over
+// NVLink, device order), encodes it, and copies its slice to the host buffers.  Blocking.
+template <typename SrcOf, typename SumOf, typename RgbOf>
+int reduce_multi(SptContext *c, uint32_t W, uint32_t H, SptSegment seg, SrcOf srcOf, SumOf sumOf, RgbOf rgbOf, uint8_t *rgb8, float *accum4)
+{
+    uint32_t const n = uint32_t(c->all.size());
+    uint32_t const segW = seg.xEnd - seg.xBegin, segH = seg.yEnd - seg.yBegin;
+    spt::ReduceParams r{};
+    r.n = n;
+    for (uint32_t k = 0; k < n; ++k)
+    {
+        SptContext *d = c->all[k];
+        r.acc[k] = srcOf(d);
+        SPT_CUDA_CHECK(cudaSetDevice(d->device));
+        SPT_CUDA_CHECK(cudaEventRecord(d->evDone, d->stream));
+    }
+    for (uint32_t k = 0; k < n; ++k)
+    {
+        SptContext *d = c->all[k];
+        SPT_CUDA_CHECK(cudaSetDevice(d->device));
+        d->timing.resolve_ms = 0.f;
+        uint32_t const y0 = seg.yBegin + uint32_t(uint64_t(segH) * k / n), y1 = seg.yBegin + uint32_t(uint64_t(segH) * (k + 1) / n);
+        if (y1 == y0)
+            continue;
+        for (uint32_t j = 0; j < n; ++j)
+            if (j != k)
+                SPT_CUDA_CHECK(cudaStreamWaitEvent(d->stream, c->all[j]->evDone, 0));
+        dim3 const block(128);
+        dim3 const grid((segW + block.x - 1) / block.x, y1 - y0);
+        SPT_CUDA_CHECK(cudaEventRecord(d->ev[2], d->stream));
+        spt::reduce_resolve_kernel<<<grid, block, 0, d->stream>>>(r, W, H, y0, y1, seg.xBegin, seg.xEnd, accum4 ? sumOf(d) : nullptr,
+                                                                   rgb8 ? rgbOf(d) : nullptr);
+        SPT_CUDA_CHECK(cudaGetLastError());
+        SPT_CUDA_CHECK(cudaEventRecord(d->ev[3], d->stream));
+        d->timing.launches += 1;
+        int const rc = copy_segment_to_host(d, W, H, SptSegment{y0, y1, seg.xBegin, seg.xEnd}, rgbOf(d), rgb8, sumOf(d), accum4);
+        if (rc)
+            return rc;
+    }
+    for (SptContext *d : c->all)
+    {
+        SPT_CUDA_CHECK(cudaSetDevice(d->device));
+        SPT_CUDA_CHECK(cudaStreamSynchronize(d->stream));
+    }
+    return SPT_OK;
+}
+} // namespace
+
+extern "C"
+{
+
+const char *spt_cuda_last_error(void) { return g_lastError.c_str(); }
+const char *spt_cuda_version(void) { return "simplepathtracer_b200 0.1 (sm_100a)"; }
+uint32_t spt_cuda_abi_version(void) { return SPT_ABI_VERSION; }
+
+int spt_cuda_create(SptContext **out, int device)
+{
+    if (!out)
+        return fail(SPT_ERR_INVALID, "out is null");
+    *out = nullptr;
+    SptContext *c = nullptr;
+    int const rc = create_one(&c, device);
+    if (rc)
+        return rc;
+    c->all.assign(1, c);
+    *out = c;
+    return SPT_OK;
+}
+
+int spt_cuda_create_multi(SptContext **out, const int *devices, int n_devices)
+{
+    if (!out || !devices)
+        return fail(SPT_ERR_INVALID, "null argument");
+    *out = nullptr;
+    if (n_devices < 1 || n_devices > SPT_MAX_DEVICES)
+        return fail(SPT_ERR_INVALID, "n_devices must be in 1..SPT_MAX_DEVICES");
+    static_assert(SPT_MAX_DEVICES <= spt::kMaxDevices, "ReduceParams holds one pointer per device");
+    std::vector<SptContext *> all;
+    auto cleanup = [&]() {
+        for (SptContext *d : all)
+            destroy_one(d);
+    };
+    for (int k = 0; k < n_devices; ++k)
+    {
+        SptContext *d = nullptr;
+        int const rc = create_one(&d, devices[k]);
+        if (rc)
+        {
+            cleanup();
+            return rc;
+        }
+        all.push_back(d);
+    }
+    // every device reads every other device's accumulator in the fused reduce-and-resolve kernel
+    for (SptContext *a : all)
+        for (SptContext *b : all)
+        {
+            if (a->device == b->device)
+                continue;
+            int can = 0;
+            cudaError_t ce = cudaDeviceCanAccessPeer(&can, a->device, b->device);
+            if (ce == cudaSuccess && !can)
+            {
+                cleanup();
+                return fail(SPT_ERR_CUDA, "spt_cuda_create_multi: the devices have no peer access to each other");
+            }
+            if (ce == cudaSuccess)
+                ce = cudaSetDevice(a->device);
+            if (ce == cudaSuccess)
+            {
+                ce = cudaDeviceEnablePeerAccess(b->device, 0);
+                if (ce == cudaErrorPeerAccessAlreadyEnabled)
+                {
+                    (void)cudaGetLastError();
+                    ce = cudaSuccess;
+                }
+            }
+            if (ce != cudaSuccess)
+            {
+                cleanup();
+                return fail(SPT_ERR_CUDA, "cudaDeviceEnablePeerAccess", ce);
+            }
+        }
+    all[0]->all = all;
+    *out = all[0];
+    return SPT_OK;
+}
+
+int spt_cuda_device_count(SptContext *c) { return c ? int(c->all.size()) : 0; }
+
+int spt_cuda_set_partition(SptContext *c, int partition)
+{
+    if (!c)
+        return fail(SPT_ERR_INVALID, "context is null");
+    if (partition != SPT_PARTITION_AUTO && partition != SPT_PARTITION_SAMPLES && partition != SPT_PARTITION_BANDS)
+        return fail(SPT_ERR_INVALID, "unknown partition");
+    std::lock_guard<std::mutex> g(c->lock);
+    c->partition = partition;
+    return SPT_OK;
+}
+
+int spt_cuda_set_staging_limit(SptContext *c, uint64_t bytes)
+{
+    if (!c)
+        return fail(SPT_ERR_INVALID, "context is null");
+    std::lock_guard<std::mutex> g(c->lock);
+    for (SptContext *d : c->all)
+        d->stagingLimit = bytes ? bytes : SPT_DEFAULT_STAGING_BYTES;
+    return SPT_OK;
+}
+
+void spt_cuda_destroy(SptContext *c)
+{
+    if (!c)
+        return;
+    std::vector<SptContext *> const all = c->all;
+    for (SptContext *d : all)
+        destroy_one(d);
 }
 
 int spt_cuda_set_stream(SptContext *c, void *cuda_stream, int use_own)
@@ -575,6 +857,10 @@ int spt_cuda_set_stream(SptContext *c, void *cuda_stream, int use_own)
     if (!c)
         return fail(SPT_ERR_INVALID, "context is null");
     std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    // work queued on the stream being left may still use context-owned buffers (staging, camera records, scratch)
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->auxStream));
     // a null handle is a real stream (the legacy default stream), so "own" is a separate switch
     c->stream = use_own ? c->ownStream : static_cast<cudaStream_t>(cuda_stream);
     return SPT_OK;
@@ -604,82 +890,40 @@ int spt_cuda_set_scene(SptContext *c, const SptScene *s)
     if (s->n == 0 || !s->centers4 || !s->radii || !s->materials || !s->colors4 || !s->fuzz)
         return fail(SPT_ERR_INVALID, "scene arrays must be non-null and n > 0");
     std::lock_guard<std::mutex> g(c->lock);
-    SPT_CUDA_CHECK(cudaSetDevice(c->device));
-    std::vector<float4> geom(s->n), shade(s->n);
+    HostScene hs;
+    hs.n = s->n;
+    hs.materials = s->materials;
+    hs.geom.resize(s->n);
+    hs.shade.resize(s->n);
     for (uint32_t i = 0; i < s->n; ++i)
     {
         if (s->centers4[4 * i + 3] != 0.f)
             return fail(SPT_ERR_INVALID, "sphere centre w must be 0 (Vec4{x,y,z} initialisers, SceneGenerators.hpp)");
-        geom[i] = make_float4(s->centers4[4 * i], s->centers4[4 * i + 1], s->centers4[4 * i + 2], s->radii[i]);
-        shade[i] = make_float4(s->colors4[4 * i], s->colors4[4 * i + 1], s->colors4[4 * i + 2], s->fuzz[i]);
+        hs.geom[i] = make_float4(s->centers4[4 * i], s->centers4[4 * i + 1], s->centers4[4 * i + 2], s->radii[i]);
+        hs.shade[i] = make_float4(s->colors4[4 * i], s->colors4[4 * i + 1], s->colors4[4 * i + 2], s->fuzz[i]);
     }
-    std::vector<unsigned char> blob;
-    std::vector<uint32_t> big;
-    uint32_t nSlots = 0;
-    float amax = 0.f;
-    build_filter(s, blob, nSlots, big, amax);
-    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    cudaFree(c->dGeom);
-    cudaFree(c->dShade);
-    cudaFree(c->dMat);
-    cudaFree(c->dPairs);
-    cudaFree(c->dBigIdx);
-    c->dGeom = c->dShade = nullptr;
-    c->dMat = nullptr;
-    c->dPairs = nullptr;
-    c->dBigIdx = nullptr;
-    c->n = 0;
-    SPT_CUDA_CHECK(cudaMalloc(&c->dPairs, blob.size() + 16));
-    SPT_CUDA_CHECK(cudaMalloc(&c->dBigIdx, (big.size() + 1) * sizeof(uint32_t)));
-    if (!blob.empty())
-        SPT_CUDA_CHECK(cudaMemcpy(c->dPairs, blob.data(), blob.size(), cudaMemcpyHostToDevice));
-    if (!big.empty())
-        SPT_CUDA_CHECK(cudaMemcpy(c->dBigIdx, big.data(), big.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    build_filter(s, hs.blob, hs.nSlots, hs.big, hs.amax);
     // host copies from which the camera form of the records is derived per eye (ensure_camera_blob)
-    c->hostBlob = blob;
-    c->hostGeom.assign(size_t(nSlots) * 4, -1.0);
+    hs.slotGeom.assign(size_t(hs.nSlots) * 4, -1.0);
     {
-        const uint32_t *slotIdx = reinterpret_cast<const uint32_t *>(blob.data() + size_t(nSlots) / 2 * sizeof(spt::FilterPair));
-        for (uint32_t k = 0; k < nSlots; ++k)
+        const uint32_t *slotIdx = reinterpret_cast<const uint32_t *>(hs.blob.data() + size_t(hs.nSlots) / 2 * sizeof(spt::FilterPair));
+        for (uint32_t k = 0; k < hs.nSlots; ++k)
         {
             uint32_t const i = slotIdx[k];
             if (i >= s->n)
                 continue; // padding: radius stays -1
-            c->hostGeom[4 * k + 0] = s->centers4[4 * i];
-            c->hostGeom[4 * k + 1] = s->centers4[4 * i + 1];
-            c->hostGeom[4 * k + 2] = s->centers4[4 * i + 2];
-            c->hostGeom[4 * k + 3] = std::fabs(double(s->radii[i]));
+            hs.slotGeom[4 * k + 0] = s->centers4[4 * i];
+            hs.slotGeom[4 * k + 1] = s->centers4[4 * i + 1];
+            hs.slotGeom[4 * k + 2] = s->centers4[4 * i + 2];
+            hs.slotGeom[4 * k + 3] = std::fabs(double(s->radii[i]));
         }
     }
-#if SPT_TENSOR_FILTER
-    cudaFree(c->dTensorB);
-    cudaFree(c->dTensorBCam); // sized by the scene; ensure_camera_blob rebuilds it (camEye is reset below)
-    c->dTensorB = c->dTensorBCam = nullptr;
-    c->tensorRows = spt::tensor_rows(nSlots);
-    if (nSlots > 0)
+    for (SptContext *d : c->all)
     {
-        std::vector<float> B;
-        spt::build_tensor_matrix(c->hostGeom, nSlots, B);
-        SPT_CUDA_CHECK(cudaMalloc(&c->dTensorB, B.size() * sizeof(float)));
-        SPT_CUDA_CHECK(cudaMemcpy(c->dTensorB, B.data(), B.size() * sizeof(float), cudaMemcpyHostToDevice));
+        int const rc = upload_scene(d, hs);
+        if (rc)
+            return rc;
     }
-#endif
-    cudaFree(c->dPairsCam);
-    c->dPairsCam = nullptr;
-    c->camEye[0] = c->camEye[1] = c->camEye[2] = NAN;
-    c->filter.pairs = c->dPairs;
-    c->filter.nSlots = nSlots;
-    c->filter.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairs + nSlots / 2);
-    c->filter.bigIdx = c->dBigIdx;
-    c->filter.nBig = uint32_t(big.size());
-    c->filter.amax = amax;
-    SPT_CUDA_CHECK(cudaMalloc(&c->dGeom, s->n * sizeof(float4)));
-    SPT_CUDA_CHECK(cudaMalloc(&c->dShade, s->n * sizeof(float4)));
-    SPT_CUDA_CHECK(cudaMalloc(&c->dMat, s->n));
-    SPT_CUDA_CHECK(cudaMemcpy(c->dGeom, geom.data(), s->n * sizeof(float4), cudaMemcpyHostToDevice));
-    SPT_CUDA_CHECK(cudaMemcpy(c->dShade, shade.data(), s->n * sizeof(float4), cudaMemcpyHostToDevice));
-    SPT_CUDA_CHECK(cudaMemcpy(c->dMat, s->materials, s->n, cudaMemcpyHostToDevice));
-    c->n = s->n;
     return SPT_OK;
 }
 
@@ -714,8 +958,12 @@ int spt_cuda_synchronize(SptContext *c)
 {
     if (!c)
         return fail(SPT_ERR_INVALID, "context is null");
-    SPT_CUDA_CHECK(cudaSetDevice(c->device));
-    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    std::lock_guard<std::mutex> g(c->lock);
+    for (SptContext *d : c->all)
+    {
+        SPT_CUDA_CHECK(cudaSetDevice(d->device));
+        SPT_CUDA_CHECK(cudaStreamSynchronize(d->stream));
+    }
     return SPT_OK;
 }
 
@@ -730,11 +978,30 @@ int spt_cuda_render(SptContext *c, const SptCamera *cam, const SptParams *prm, S
     if (rc)
         return rc;
     std::lock_guard<std::mutex> g(c->lock);
-    SPT_CUDA_CHECK(cudaSetDevice(c->device));
     uint32_t const W = prm->width, H = prm->height;
     uint32_t const segW = seg.xEnd - seg.xBegin, segH = seg.yEnd - seg.yBegin;
     if (segW == 0 || segH == 0)
         return SPT_OK;
+    if (c->all.size() > 1)
+    {
+        // every device: zero its accumulator rows, trace its share
+        for (SptContext *d : c->all)
+        {
+            SPT_CUDA_CHECK(cudaSetDevice(d->device));
+            rc = ensure_scratch(d, size_t(W) * H);
+            if (rc)
+                return rc;
+            SPT_CUDA_CHECK(cudaMemset2DAsync(d->dAccum + size_t(seg.yBegin) * W + seg.xBegin, size_t(W) * sizeof(float4), 0,
+                                             size_t(segW) * sizeof(float4), segH, d->stream));
+        }
+        rc = trace_multi(c, cam, prm, seg, [](SptContext *d) { return d->dAccum; });
+        if (rc)
+            return rc;
+        // the totals may replace each device's own slice of its accumulator
+        return reduce_multi(c, W, H, seg, [](SptContext *d) { return d->dAccum; }, [](SptContext *d) { return d->dAccum; },
+                            [](SptContext *d) { return d->dRgb; }, rgb8, accum4);
+    }
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
     rc = ensure_scratch(c, size_t(W) * H);
     if (rc)
         return rc;
@@ -744,20 +1011,12 @@ int spt_cuda_render(SptContext *c, const SptCamera *cam, const SptParams *prm, S
     rc = launch_trace(c, cam, prm, seg, c->dAccum);
     if (rc)
         return rc;
-    uint32_t const traceLaunches = c->timing.launches;
     rc = launch_resolve(c, c->dAccum, W, H, seg, c->dRgb);
     if (rc)
         return rc;
-    c->timing.launches += traceLaunches;
-    // pixel (x,y) lives in byte row H-1-y: copy the segment's rows back into the caller's g_data
-    uint32_t const rowTop = H - seg.yEnd; // flipped
-    SPT_CUDA_CHECK(cudaMemcpy2DAsync(rgb8 + (size_t(rowTop) * W + seg.xBegin) * 3, size_t(W) * 3,
-                                     c->dRgb + (size_t(rowTop) * W + seg.xBegin) * 3, size_t(W) * 3, size_t(segW) * 3, segH,
-                                     cudaMemcpyDeviceToHost, c->stream));
-    if (accum4)
-        SPT_CUDA_CHECK(cudaMemcpy2DAsync(accum4 + (size_t(seg.yBegin) * W + seg.xBegin) * 4, size_t(W) * sizeof(float4),
-                                         c->dAccum + size_t(seg.yBegin) * W + seg.xBegin, size_t(W) * sizeof(float4),
-                                         size_t(segW) * sizeof(float4), segH, cudaMemcpyDeviceToHost, c->stream));
+    rc = copy_segment_to_host(c, W, H, seg, c->dRgb, rgb8, c->dAccum, accum4);
+    if (rc)
+        return rc;
     SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     return SPT_OK;
 }
@@ -770,21 +1029,24 @@ int spt_cuda_progressive_begin(SptContext *c, uint32_t width, uint32_t height)
     if (rc)
         return rc;
     std::lock_guard<std::mutex> g(c->lock);
-    SPT_CUDA_CHECK(cudaSetDevice(c->device));
-    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    if (width != c->progW || height != c->progH || !c->dProgAccum)
+    for (SptContext *d : c->all)
     {
-        cudaFree(c->dProgAccum);
-        cudaFree(c->dProgRgb);
-        c->dProgAccum = nullptr;
-        c->dProgRgb = nullptr;
-        c->progW = c->progH = 0;
-        SPT_CUDA_CHECK(cudaMalloc(&c->dProgAccum, size_t(width) * height * sizeof(float4)));
-        SPT_CUDA_CHECK(cudaMalloc(&c->dProgRgb, size_t(width) * height * 3));
-        c->progW = width;
-        c->progH = height;
+        SPT_CUDA_CHECK(cudaSetDevice(d->device));
+        SPT_CUDA_CHECK(cudaStreamSynchronize(d->stream));
+        if (width != d->progW || height != d->progH || !d->dProgAccum)
+        {
+            cudaFree(d->dProgAccum);
+            cudaFree(d->dProgRgb);
+            d->dProgAccum = nullptr;
+            d->dProgRgb = nullptr;
+            d->progW = d->progH = 0;
+            SPT_CUDA_CHECK(cudaMalloc(&d->dProgAccum, size_t(width) * height * sizeof(float4)));
+            SPT_CUDA_CHECK(cudaMalloc(&d->dProgRgb, size_t(width) * height * 3));
+            d->progW = width;
+            d->progH = height;
+        }
+        SPT_CUDA_CHECK(cudaMemsetAsync(d->dProgAccum, 0, size_t(width) * height * sizeof(float4), d->stream));
     }
-    SPT_CUDA_CHECK(cudaMemsetAsync(c->dProgAccum, 0, size_t(width) * height * sizeof(float4), c->stream));
     return SPT_OK;
 }
 
@@ -799,9 +1061,11 @@ int spt_cuda_progressive_add(SptContext *c, const SptCamera *cam, const SptParam
     if (rc)
         return rc;
     std::lock_guard<std::mutex> g(c->lock);
-    SPT_CUDA_CHECK(cudaSetDevice(c->device));
     if (!c->dProgAccum || prm->width != c->progW || prm->height != c->progH)
         return fail(SPT_ERR_INVALID, "spt_cuda_progressive_begin has not been called with this image size");
+    if (c->all.size() > 1)
+        return trace_multi(c, cam, prm, seg, [](SptContext *d) { return d->dProgAccum; });
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
     return launch_trace(c, cam, prm, seg, c->dProgAccum);
 }
 
@@ -810,7 +1074,6 @@ int spt_cuda_progressive_image(SptContext *c, SptSegment seg, uint8_t *rgb8, flo
     if (!c)
         return fail(SPT_ERR_INVALID, "context is null");
     std::lock_guard<std::mutex> g(c->lock);
-    SPT_CUDA_CHECK(cudaSetDevice(c->device));
     if (!c->dProgAccum)
         return fail(SPT_ERR_INVALID, "spt_cuda_progressive_begin has not been called");
     uint32_t const W = c->progW, H = c->progH;
@@ -820,20 +1083,29 @@ int spt_cuda_progressive_image(SptContext *c, SptSegment seg, uint8_t *rgb8, flo
     uint32_t const segW = seg.xEnd - seg.xBegin, segH = seg.yEnd - seg.yBegin;
     if (segW == 0 || segH == 0)
         return SPT_OK;
+    if (c->all.size() > 1)
+    {
+        // the per-device sums go on accumulating afterwards: the totals are written to each device's scratch
+        for (SptContext *d : c->all)
+        {
+            SPT_CUDA_CHECK(cudaSetDevice(d->device));
+            rc = ensure_scratch(d, size_t(W) * H);
+            if (rc)
+                return rc;
+        }
+        return reduce_multi(c, W, H, seg, [](SptContext *d) { return d->dProgAccum; }, [](SptContext *d) { return d->dAccum; },
+                            [](SptContext *d) { return d->dProgRgb; }, rgb8, accum4);
+    }
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
     if (rgb8)
     {
         rc = launch_resolve(c, c->dProgAccum, W, H, seg, c->dProgRgb);
         if (rc)
             return rc;
-        uint32_t const rowTop = H - seg.yEnd; // pixel (x,y) lives in byte row H-1-y
-        SPT_CUDA_CHECK(cudaMemcpy2DAsync(rgb8 + (size_t(rowTop) * W + seg.xBegin) * 3, size_t(W) * 3,
-                                         c->dProgRgb + (size_t(rowTop) * W + seg.xBegin) * 3, size_t(W) * 3, size_t(segW) * 3, segH,
-                                         cudaMemcpyDeviceToHost, c->stream));
     }
-    if (accum4)
-        SPT_CUDA_CHECK(cudaMemcpy2DAsync(accum4 + (size_t(seg.yBegin) * W + seg.xBegin) * 4, size_t(W) * sizeof(float4),
-                                         c->dProgAccum + size_t(seg.yBegin) * W + seg.xBegin, size_t(W) * sizeof(float4),
-                                         size_t(segW) * sizeof(float4), segH, cudaMemcpyDeviceToHost, c->stream));
+    rc = copy_segment_to_host(c, W, H, seg, c->dProgRgb, rgb8, c->dProgAccum, accum4);
+    if (rc)
+        return rc;
     SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     return SPT_OK;
 }
@@ -843,11 +1115,34 @@ int spt_cuda_progressive_load(SptContext *c, const float *accum4)
     if (!c || !accum4)
         return fail(SPT_ERR_INVALID, "null argument");
     std::lock_guard<std::mutex> g(c->lock);
-    SPT_CUDA_CHECK(cudaSetDevice(c->device));
     if (!c->dProgAccum)
         return fail(SPT_ERR_INVALID, "spt_cuda_progressive_begin has not been called");
-    SPT_CUDA_CHECK(cudaMemcpyAsync(c->dProgAccum, accum4, size_t(c->progW) * c->progH * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
-    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    // The checkpoint holds totals.  Every device continues from the rows of ITS bands of the full image (band b of 8 rows
+    // belongs to device b % n, the ownership a full-image call with the band partition uses) and from zero elsewhere: a
+    // resumed band-partitioned render continues every pixel's running sum on the device that owns it -- the bits of an
+    // uninterrupted render -- and any other partition still sums to the same totals.
+    uint32_t const n = uint32_t(c->all.size());
+    for (uint32_t k = 0; k < n; ++k)
+    {
+        SptContext *d = c->all[k];
+        SPT_CUDA_CHECK(cudaSetDevice(d->device));
+        size_t const rowBytes = size_t(d->progW) * sizeof(float4);
+        if (n == 1)
+        {
+            SPT_CUDA_CHECK(cudaMemcpyAsync(d->dProgAccum, accum4, rowBytes * d->progH, cudaMemcpyHostToDevice, d->stream));
+        }
+        else
+        {
+            SPT_CUDA_CHECK(cudaMemsetAsync(d->dProgAccum, 0, rowBytes * d->progH, d->stream));
+            for (uint32_t y = k * SPT_BAND_ROWS; y < d->progH; y += n * SPT_BAND_ROWS)
+            {
+                uint32_t const rows = std::min<uint32_t>(SPT_BAND_ROWS, d->progH - y);
+                SPT_CUDA_CHECK(cudaMemcpyAsync(d->dProgAccum + size_t(y) * d->progW, accum4 + size_t(y) * d->progW * 4, rowBytes * rows,
+                                               cudaMemcpyHostToDevice, d->stream));
+            }
+        }
+        SPT_CUDA_CHECK(cudaStreamSynchronize(d->stream));
+    }
     return SPT_OK;
 }
 
@@ -932,15 +1227,19 @@ int spt_cuda_get_counters(SptContext *c, SptCounters *out)
     if (!c || !out)
         return fail(SPT_ERR_INVALID, "null argument");
     std::lock_guard<std::mutex> g(c->lock);
-    SPT_CUDA_CHECK(cudaSetDevice(c->device));
-    unsigned long long h[8];
-    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    SPT_CUDA_CHECK(cudaMemcpy(h, c->dCounters, sizeof(h), cudaMemcpyDeviceToHost));
-    out->segments = h[0];
-    out->tests = h[0] * c->n;
-    out->samples = h[1];
-    out->dropped = h[2];
-    out->exact = h[3];
+    memset(out, 0, sizeof(*out));
+    for (SptContext *d : c->all) // a multi-device context reports the sum over its devices
+    {
+        SPT_CUDA_CHECK(cudaSetDevice(d->device));
+        unsigned long long h[8];
+        SPT_CUDA_CHECK(cudaStreamSynchronize(d->stream));
+        SPT_CUDA_CHECK(cudaMemcpy(h, d->dCounters, sizeof(h), cudaMemcpyDeviceToHost));
+        out->segments += h[0];
+        out->tests += h[0] * d->n;
+        out->samples += h[1];
+        out->dropped += h[2];
+        out->exact += h[3];
+    }
     return SPT_OK;
 }
 
@@ -949,8 +1248,11 @@ int spt_cuda_reset_counters(SptContext *c)
     if (!c)
         return fail(SPT_ERR_INVALID, "context is null");
     std::lock_guard<std::mutex> g(c->lock);
-    SPT_CUDA_CHECK(cudaSetDevice(c->device));
-    SPT_CUDA_CHECK(cudaMemsetAsync(c->dCounters, 0, 8 * sizeof(unsigned long long), c->stream));
+    for (SptContext *d : c->all)
+    {
+        SPT_CUDA_CHECK(cudaSetDevice(d->device));
+        SPT_CUDA_CHECK(cudaMemsetAsync(d->dCounters, 0, 8 * sizeof(unsigned long long), d->stream));
+    }
     return SPT_OK;
 }
 
@@ -959,15 +1261,38 @@ int spt_cuda_get_timing(SptContext *c, SptTiming *out)
     if (!c || !out)
         return fail(SPT_ERR_INVALID, "null argument");
     std::lock_guard<std::mutex> g(c->lock);
-    SPT_CUDA_CHECK(cudaSetDevice(c->device));
-    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]) == cudaSuccess)
-        c->timing.trace_ms = ms;
-    if (cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]) == cudaSuccess)
-        c->timing.resolve_ms = ms;
-    cudaGetLastError(); // events never recorded: not an error of the caller
-    *out = c->timing;
+    SptTiming t{};
+    for (SptContext *d : c->all) // several devices work side by side: the slowest one's times, everybody's launches
+    {
+        SPT_CUDA_CHECK(cudaSetDevice(d->device));
+        SPT_CUDA_CHECK(cudaStreamSynchronize(d->stream));
+        float ms = 0.f;
+        if (d->timing.launches && cudaEventElapsedTime(&ms, d->ev[0], d->ev[1]) == cudaSuccess)
+            d->timing.trace_ms = ms;
+        if (d->timedChunks)
+        {
+            SPT_CUDA_CHECK(cudaStreamSynchronize(d->auxStream));
+            float pm = 0.f, sm = 0.f;
+            for (uint32_t k = 0; k < d->timedChunks; ++k)
+            {
+                if (cudaEventElapsedTime(&ms, d->evKernel[4 * k + 0], d->evKernel[4 * k + 1]) == cudaSuccess)
+                    pm += ms;
+                if (cudaEventElapsedTime(&ms, d->evKernel[4 * k + 2], d->evKernel[4 * k + 3]) == cudaSuccess)
+                    sm += ms;
+            }
+            d->timing.primary_ms = pm;
+            d->timing.secondary_ms = sm;
+        }
+        if (cudaEventElapsedTime(&ms, d->ev[2], d->ev[3]) == cudaSuccess)
+            d->timing.resolve_ms = ms;
+        cudaGetLastError(); // events never recorded: not an error of the caller
+        t.trace_ms = std::max(t.trace_ms, d->timing.trace_ms);
+        t.resolve_ms = std::max(t.resolve_ms, d->timing.resolve_ms);
+        t.launches += d->timing.launches;
+        t.primary_ms = std::max(t.primary_ms, d->timing.primary_ms);
+        t.secondary_ms = std::max(t.secondary_ms, d->timing.secondary_ms);
+    }
+    *out = t;
     return SPT_OK;
 }
 

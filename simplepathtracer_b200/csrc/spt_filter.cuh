@@ -36,9 +36,6 @@ namespace spt
 #ifndef SPT_FILTER_TC
 #define SPT_FILTER_TC 0 // 1: the pre-filter also tests the sign of tC (one more FMNMX per sphere, fewer candidates)
 #endif
-#ifndef SPT_TENSOR_FILTER
-#define SPT_TENSOR_FILTER 0 // 1: EXPERIMENTAL builds only -- the bounce kernel with the discriminant on tcgen05 (spt_tensor_filter.cuh)
-#endif
 #ifndef SPT_WORD_UNROLL2
 #define SPT_WORD_UNROLL2 1 // the single-ray word loop takes two full words per trip while it can (+0.6 .. 1.0 % on config 3; 0: one)
 #endif

@@ -63,11 +63,6 @@ struct TraceParams
     // [(y - yBegin) * segW + (x - xBegin)][sample - sampleBegin]
     float4 *firstHits;
     FilterScene filterCam; // pre-filter records specialised for the eye (camera form)
-#if SPT_TENSOR_FILTER
-    const float *tensorB;  // spt_tensor_filter.cuh: the sphere matrix in UMMA canonical layout
-    uint32_t tensorRows;   // its rows: the slots it covers padded to a multiple of 16
-    const float *tensorBCam; // the camera form of the matrix for this launch's eye (primary_hits_tc)
-#endif
 };
 
 constexpr uint32_t kMissIndex = 0xFFFFFFFFu;
@@ -662,6 +657,48 @@ __global__ void resolve_kernel(const float4 *accum, uint32_t width, uint32_t hei
     rgb8[index + 0] = encode_channel(fmul(a.x, inv));
     rgb8[index + 1] = encode_channel(fmul(a.y, inv));
     rgb8[index + 2] = encode_channel(fmul(a.z, inv));
+}
+
+// ---- multi-device epilogue: reduce + resolve, fused ---------------------------------------------------
+// Several GPUs each hold a float4 accumulator of the same image (sample ranges of every pixel, or disjoint row bands with
+// zeros elsewhere).  This kernel runs on EVERY device over its own slice of the rows: it sums the n accumulators in device
+// order through peer-mapped pointers (loads over NVLink), optionally keeps the total (sumOut, which may alias this device's
+// own accumulator: a thread reads and writes only its own pixel), and encodes the pixel exactly as resolve_kernel does.
+// With disjoint bands the sum adds zeros to one value: the single-GPU bits.
+constexpr int kMaxDevices = 16;
+struct ReduceParams
+{
+    const float4 *acc[kMaxDevices];
+    uint32_t n;
+};
+__global__ void reduce_resolve_kernel(const __grid_constant__ ReduceParams r, uint32_t width, uint32_t height, uint32_t yBegin, uint32_t yEnd,
+                                      uint32_t xBegin, uint32_t xEnd, float4 *sumOut, uint8_t *rgb8)
+{
+    uint32_t const x = xBegin + blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t const y = yBegin + blockIdx.y;
+    if (x >= xEnd || y >= yEnd)
+        return;
+    size_t const i = size_t(y) * width + x;
+    float4 a = r.acc[0][i];
+    for (uint32_t k = 1; k < r.n; ++k)
+    {
+        float4 const b = r.acc[k][i];
+        a.x = fadd(a.x, b.x);
+        a.y = fadd(a.y, b.y);
+        a.z = fadd(a.z, b.z);
+        a.w = fadd(a.w, b.w);
+    }
+    if (sumOut)
+        sumOut[i] = a;
+    if (rgb8)
+    {
+        float const inv = fdiv(1.f, a.w);
+        uint32_t const size = width * height * 3u;
+        uint32_t const index = size - ((width - x) * 3u + y * width * 3u);
+        rgb8[index + 0] = encode_channel(fmul(a.x, inv));
+        rgb8[index + 1] = encode_channel(fmul(a.y, inv));
+        rgb8[index + 2] = encode_channel(fmul(a.z, inv));
+    }
 }
 
 // ---- FP32 peak microbenchmark ---------------------------------------------------------------------

@@ -8,7 +8,10 @@
 //                [--progressive P]   P passes over the samples on a persistent accumulator; prints k/P and rewrites
 //                                    the image after each (the reference's live preview, Renderer.hpp:157-164)
 //                [--pfm file.pfm]    also write the linear float image (needs --progressive >= 1)
-//                [--checkpoint file] resume from the accumulators in `file` when it matches, write them back at the end
+//                [--checkpoint file] resume from the accumulators in `file` when it was written for THIS render (size, depth,
+//                                    seed, scene, camera, tracer), rewrite it after every pass
+//                [--gpus N]          one render spread over CUDA devices 0..N-1 by the library (spt_cuda_create_multi)
+//                [--staging-mib M]   first-hit staging budget of split rendering per device (default 8192)
 #include "../../include/spt_host/Scene.hpp"
 #include "../../include/spt_host/SceneFile.hpp"
 #include "../../include/spt_host/SceneGenerators.hpp"
@@ -26,7 +29,7 @@ int main(int argc, char **argv)
 {
     std::string scene = "reference", tracer = "recursive", out;
     std::string pfm, checkpoint, dumpScene;
-    uint32_t seed = 1, width = 1440, height = 1440, spp = 100, depth = 10, tiles = 1, progressive = 0;
+    uint32_t seed = 1, width = 1440, height = 1440, spp = 100, depth = 10, tiles = 1, progressive = 0, gpus = 1, stagingMib = 0;
     for (int i = 1; i + 1 < argc; i += 2)
     {
         std::string const k = argv[i], v = argv[i + 1];
@@ -43,6 +46,8 @@ int main(int argc, char **argv)
         else if (k == "--pfm") pfm = v;
         else if (k == "--dump-scene") dumpScene = v;
         else if (k == "--checkpoint") checkpoint = v;
+        else if (k == "--gpus") gpus = uint32_t(std::stoul(v));
+        else if (k == "--staging-mib") stagingMib = uint32_t(std::stoul(v));
         else { std::cerr << "unknown flag " << k << "\n"; return 2; }
     }
     SetRenderConfig(width, height, spp, depth);
@@ -55,6 +60,15 @@ int main(int argc, char **argv)
     if (!dumpScene.empty() && !io::SaveScene(dumpScene.c_str())) { std::cerr << "cannot write " << dumpScene << "\n"; return 1; }
     spt_cuda::SetSeed(seed);
     spt_cuda::InvalidateScene();
+    if (gpus > 1)
+    {
+        std::vector<int> devices(gpus);
+        for (uint32_t k = 0; k < gpus; ++k)
+            devices[k] = int(k);
+        spt_cuda::SetDevices(devices);
+    }
+    if (stagingMib)
+        spt_cuda::SetStagingLimit(uint64_t(stagingMib) << 20);
 
     if ((!pfm.empty() || !checkpoint.empty()) && progressive == 0)
         progressive = 1;
@@ -68,8 +82,9 @@ int main(int argc, char **argv)
             std::vector<float> accum(size_t(width) * height * 4u), resume;
             io::AccumHeader h{};
             uint32_t first = 0;
-            if (!checkpoint.empty() && io::LoadAccum(checkpoint.c_str(), width, height, h, resume) && h.depth == depth && h.seed == seed &&
-                h.samplesDone <= spp)
+            uint64_t const identity = io::RenderIdentity(passCap); // scene, camera, tracer semantics
+            if (!checkpoint.empty() && io::LoadAccum(checkpoint.c_str(), width, height, h, resume, identity) && h.depth == depth &&
+                h.seed == seed && h.samplesDone <= spp)
             {
                 first = h.samplesDone;
                 std::cout << "Resuming at sample " << first << " of " << spp << std::endl;
@@ -82,12 +97,13 @@ int main(int argc, char **argv)
                     std::cout << k << "/" << n << "  (" << samplesDone << " spp)" << std::endl; // Renderer.hpp:285
                     if (n > 1 && !io::SaveImage(out.empty() ? nullptr : out.c_str()))               // the live preview, as a file
                         std::cerr << "cannot write image\n";
+                    // after EVERY pass: an interrupted render resumes from the last completed one
+                    if (!checkpoint.empty() && !io::SaveAccum(checkpoint.c_str(), width, height, samplesDone, depth, seed, accum.data(), identity))
+                        std::cerr << "cannot write " << checkpoint << "\n";
                 },
-                first, resume.empty() ? nullptr : resume.data(), accum.data());
+                first, resume.empty() ? nullptr : resume.data(), accum.data(), !checkpoint.empty());
             if (!pfm.empty() && !io::WritePfm(pfm.c_str(), width, height, accum.data()))
                 std::cerr << "cannot write " << pfm << "\n";
-            if (!checkpoint.empty() && !io::SaveAccum(checkpoint.c_str(), width, height, spp, depth, seed, accum.data()))
-                std::cerr << "cannot write " << checkpoint << "\n";
         }
         else
         {
@@ -98,7 +114,9 @@ int main(int argc, char **argv)
         for (uint32_t j = 0; j < tiles; ++j)
             for (uint32_t i = 0; i < tiles; ++i)
             {
-                RenderSegmentData const seg{sh * j, std::min(sh * (j + 1), g_height), sw * i, std::min(sw * (i + 1), g_width)};
+                // ceil-sized tiles: the last ones may be short or empty (e.g. width 10, 8 tiles): clamp BOTH ends
+                RenderSegmentData const seg{std::min(sh * j, g_height), std::min(sh * (j + 1), g_height), std::min(sw * i, g_width),
+                                            std::min(sw * (i + 1), g_width)};
                 if (tiles > 1)
                     std::cout << ++done << "/" << tiles * tiles << std::endl; // Renderer.hpp:285
                 if (tracer == "recursive") RenderSegmentCuda(seg);

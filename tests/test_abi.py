@@ -36,10 +36,10 @@ def test_struct_sizes_match_header():
     # natural C layout of the structs in include/spt_cuda.h on LP64
     assert ctypes.sizeof(binding.Segment) == 16
     assert ctypes.sizeof(binding._CCamera) == 96
-    assert ctypes.sizeof(binding._CParams) == 48  # band_count, band_index appended
+    assert ctypes.sizeof(binding._CParams) == 56  # revision 2: band_count, band_index; revision 3: split_chunk, reserved
     assert ctypes.sizeof(binding._CScene) == 48
     assert ctypes.sizeof(binding.Counters) == 40
-    assert ctypes.sizeof(binding.Timing) == 16
+    assert ctypes.sizeof(binding.Timing) == 24
 
 
 def test_struct_layouts_match_the_c_compiler(tmp_path):

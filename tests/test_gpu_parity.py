@@ -510,7 +510,7 @@ def test_streamed_megakernel_bit_exact(tracer, oracle, cam, scene_init, scene_ra
     one almost full chunk (501) and several chunks with a ragged tail (1600 spheres = 3 full chunks + 63 slots)."""
     scene = {"init": scene_init, "random": scene_random, "metal_glass": scene_metal_glass}.get(which) or spt.generate_lattice(7, 40)
     w, h, spp, depth = 100, 45, 5, 12  # ragged tiles: CTAs with dead warps and dead lanes must keep the ring moving
-    monkeypatch.setenv("SPT_SPLIT_CHUNK", "2")  # split rendering (the default): 3 chunks of samples
+    monkeypatch.setattr(tracer, "split_chunk", 2)  # SptParams.split_chunk: 3 chunks of samples through the two staging buffers
     tracer.set_scene(scene)
     tracer.reset_counters()
     rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=pass_cap, seed=33, want_accum=True,
@@ -569,7 +569,7 @@ def test_split_render_bit_exact(tracer, oracle, cam, scene_init, scene_random, s
     """SPT_FLAG_SPLIT: camera segments traced by primary_hits_kernel with the camera form of the pre-filter, bounce loop
     on secondary rays only.  Same bits as the oracle, same counters; several chunks of samples on purpose."""
     scene = {"init": scene_init, "random": scene_random, "metal_glass": scene_metal_glass}[which]
-    monkeypatch.setenv("SPT_SPLIT_CHUNK", "3")
+    monkeypatch.setattr(tracer, "split_chunk", 3)
     w, h, spp, depth = 100, 45, 7, 12
     tracer.set_scene(scene)
     tracer.reset_counters()
@@ -601,7 +601,7 @@ def test_row_bands_compose_to_the_full_render(tracer, oracle, cam, scene_random,
     one full render (what the multi-GPU partition relies on), on a ragged segment, for every kernel family."""
     import torch
 
-    monkeypatch.setenv("SPT_SPLIT_CHUNK", "3")  # several chunks of samples per call
+    monkeypatch.setattr(tracer, "split_chunk", 3)  # several chunks of samples per call
     tracer.set_scene(scene_random)
     tracer.set_stream(torch.cuda.current_stream().cuda_stream)  # torch's fills and our kernels in one stream order
     w, h, spp, depth = 150, 93, 5, 8
@@ -626,3 +626,120 @@ def test_row_bands_compose_to_the_full_render(tracer, oracle, cam, scene_random,
     with pytest.raises(spt.SptError):
         tracer.accumulate(cam, w, h, 0, spp, depth, full, bands=(2, 2))
     tracer.set_stream(None)
+
+
+# ----------------------------------------------------------------------------- staging limit (two alternating buffers, second stream)
+def test_staging_limit_forces_chunks_and_keeps_the_bits(tracer, oracle, cam, scene_random):
+    """spt_cuda_set_staging_limit: a tiny budget cuts the sample range into many chunks that alternate between the two
+    staging buffers (camera kernel of chunk k+1 on the auxiliary stream under the bounce kernel of chunk k); the per-pixel
+    running sums continue across chunks, so the accumulators are those of one launch -- and the oracle's."""
+    w, h, spp, depth = 100, 45, 11, 12
+    tracer.set_scene(scene_random)
+    oacc, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, pass_cap=10, seed=5)
+    try:
+        for limit, launches in ((2 * (w * h * 16 + 512), 2 * 11 + 1), (5 * w * h * 16, 2 * 6 + 1), (0, 2 + 1)):
+            tracer.set_staging_limit(limit)
+            _, acc = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=5, want_accum=True)
+            assert_accum_equal(acc, oacc)
+            assert tracer.timing()["launches"] == launches, (limit, tracer.timing())
+    finally:
+        tracer.set_staging_limit(0)
+
+
+# ----------------------------------------------------------------------------- several GPUs behind ONE context (spt_cuda_create_multi)
+def _device_list(n):
+    """n CUDA ordinals for a multi-device context: distinct GPUs when the box has them, otherwise the same GPU listed
+    several times (several internal contexts on one device: every code path but the NVLink hop)."""
+    import torch
+
+    have = torch.cuda.device_count()
+    return [k % have for k in range(n)]
+
+
+@pytest.mark.parametrize("ndev", [2, 3])
+@pytest.mark.parametrize("variant", [spt.MEGAKERNEL, spt.WAVEFRONT])
+def test_multi_device_context_bands_leave_the_single_gpu_bits(tracer, oracle, cam, scene_random, ndev, variant):
+    """One spt_cuda_render call on a multi-device context, band partition: the devices trace disjoint 8-row bands, the fused
+    reduce-and-resolve kernel adds zeros, and both the accumulators and the RGB8 bytes equal the oracle's (ragged segment,
+    bytes outside it untouched).  Renderer.hpp:257-302: one call spreads one render over all workers."""
+    w, h, spp, depth = 150, 93, 5, 8
+    seg = (3, 90, 7, 141)
+    oacc, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, pass_cap=10, seed=12, seg=seg)
+    with spt.PathTracer(_device_list(ndev)) as multi:
+        assert multi.device_count() == ndev
+        multi.set_scene(scene_random)
+        multi.set_partition(spt.PARTITION_BANDS)
+        multi.split_chunk = 2
+        rgb0 = np.full((h, w, 3), 9, np.uint8)
+        multi.reset_counters()
+        rgb, acc = multi.render(cam, w, h, spp, depth, pass_cap=10, seed=12, seg=seg, want_accum=True, rgb8=rgb0.copy(), variant=variant,
+                                flags=spt.FLAG_COUNTERS)
+        assert_accum_equal(acc, oacc)
+        want = rgb0.copy()
+        y0, y1, x0, x1 = seg
+        want[h - y1:h - y0, x0:x1] = oracle.resolve(oacc, seg=seg)[h - y1:h - y0, x0:x1]
+        assert np.array_equal(rgb, want)
+        c = multi.counters()
+        assert c["samples"] == (y1 - y0) * (x1 - x0) * spp
+        with pytest.raises(spt.SptError):  # the library partitions a multi-device context itself
+            multi.progressive_begin(w, h) or multi.progressive_add(cam, 0, 1, depth, bands=(2, 0))
+
+
+@pytest.mark.parametrize("ndev", [2, 4])
+def test_multi_device_context_sample_ranges(tracer, oracle, cam, scene_random, ndev):
+    """Sample-range partition (the default when a call has at least as many samples as devices): device k traces samples
+    [k S / n, (k+1) S / n) of every pixel; the per-device sums are the oracle's for those ranges and the fused epilogue adds
+    them in device order -- so the total is reproduced EXACTLY by adding the oracle's partial sums in the same order."""
+    w, h, spp, depth = 96, 64, 10, 8
+    parts = []
+    for k in range(ndev):
+        s0, s1 = spp * k // ndev, spp * (k + 1) // ndev
+        o, _ = oracle.render_accum(scene_random, cam, w, h, s1 - s0, depth, pass_cap=10, seed=6, sample_begin=s0)
+        parts.append(o)
+    want = parts[0].copy()
+    for o in parts[1:]:
+        want = want + o  # float32 adds in device order, as reduce_resolve_kernel does
+    with spt.PathTracer(_device_list(ndev)) as multi:
+        multi.set_scene(scene_random)
+        rgb, acc = multi.render(cam, w, h, spp, depth, pass_cap=10, seed=6, want_accum=True)
+        assert_accum_equal(acc, want)
+        assert np.array_equal(rgb, oracle.resolve(want))
+        assert multi.timing()["launches"] == ndev * 3  # camera + bounce + epilogue slice on every device
+        # against the single-device render: same samples, sums re-associated
+        _, one = tracer_render_single(tracer, scene_random, cam, w, h, spp, depth)
+        assert np.array_equal(acc[..., 3], one[..., 3])
+        np.testing.assert_allclose(acc[..., :3], one[..., :3], rtol=2e-6, atol=0)
+        # fewer samples than devices: AUTO falls back to bands, which are bit-identical to one GPU
+        _, few = multi.render(cam, w, h, 1, depth, pass_cap=10, seed=6, want_accum=True)
+        _, few1 = tracer.render(cam, w, h, 1, depth, pass_cap=10, seed=6, want_accum=True)
+        assert_accum_equal(few, few1)
+
+
+def tracer_render_single(tracer, scene, cam, w, h, spp, depth):
+    tracer.set_scene(scene)
+    return tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=6, want_accum=True)
+
+
+def test_multi_device_progressive(tracer, oracle, cam, scene_random):
+    """The progressive entry points on a multi-device context: passes and tiles accumulate per device, every image is the
+    fused reduction of the per-device sums, and with the band partition it is bit-identical to one render."""
+    w, h, spp, depth = 96, 64, 6, 8
+    oacc, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, pass_cap=10, seed=6)
+    with spt.PathTracer(_device_list(2)) as multi:
+        multi.set_scene(scene_random)
+        multi.set_partition(spt.PARTITION_BANDS)
+        multi.progressive_begin(w, h)
+        for s0, s1 in [(0, 1), (1, 4), (4, 6)]:
+            for seg in [(0, 32, 0, 48), (0, 32, 48, 96), (32, 64, 0, 48), (32, 64, 48, 96)]:
+                multi.progressive_add(cam, s0, s1, depth, pass_cap=10, seed=6, seg=seg)
+            rgb, acc = multi.progressive_image(want_accum=True)
+            assert acc[..., 3].max() == s1
+        assert_accum_equal(acc, oacc)
+        assert np.array_equal(rgb, oracle.resolve(oacc))
+        # resume from a checkpoint of the totals
+        part, _ = oracle.render_accum(scene_random, cam, w, h, 4, depth, pass_cap=10, seed=6)
+        multi.progressive_begin(w, h)
+        multi.progressive_load(part)
+        multi.progressive_add(cam, 4, 6, depth, pass_cap=10, seed=6)
+        _, acc2 = multi.progressive_image(want_accum=True)
+        assert_accum_equal(acc2, oacc)

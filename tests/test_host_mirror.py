@@ -78,7 +78,7 @@ def test_pfm_and_accumulator_checkpoint_files(tmp_path):
     assert np.array_equal(body, want)
     ck = str(tmp_path / "a.sptacc")
     spt.save_accum(ck, acc, samples_done=9, depth=4, seed=77)
-    assert os.path.getsize(ck) == 32 + acc.nbytes
+    assert os.path.getsize(ck) == 48 + acc.nbytes  # "SPTACC2" header: ... seed, identity, reserved
     got = spt.load_accum(ck, 7, 5)
     assert got is not None and np.array_equal(got[0], acc) and got[1:] == (9, 4, 77)
     assert spt.load_accum(ck, 8, 5) is None  # another image size

@@ -200,6 +200,9 @@ def kernel_rooflines(ctr_per_render, n_spheres, primary_ms, secondary_ms, peak):
         exe = EXECUTED_FLOP[key] * tests / (ms * 1e-3) / 1e12
         out[name] = {"ms_per_render": ms, "segments": segs, "tests": tests, "achieved": alg, "frac": alg / peak if peak else None,
                      "executed_flop_per_test": EXECUTED_FLOP[key], "executed_frac": exe / peak if peak else None}
+        if key == "secondary" and ctr_per_render.get("warp_iterations"):
+            # share of the lanes that held a ray in the bounce kernel's closest-hit trips (the rest waited for warp-mates)
+            out[name]["lanes_with_a_ray"] = segs / (32.0 * ctr_per_render["warp_iterations"])
     return out
 
 
@@ -240,6 +243,7 @@ def run_native_arm(args, wl):
     staging = (args.staging_mib << 20) if args.staging_mib else spt.DEFAULT_STAGING_BYTES
     pt = spt.PathTracer(local)
     pt.set_staging_limit(staging)
+    pt.lane_tiles = args.lane_tiles
     # one explicit stream for torch fills, our kernels and the timing events
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
@@ -515,6 +519,7 @@ def main():
     ap.add_argument("--partition", default="samples", choices=["samples", "bands"], help="how N > 1 ranks share a render (sharding.py)")
     ap.add_argument("--flags", type=int, default=0, help="extra SPT_FLAG_* bits for the trace launches (experiments)")
     ap.add_argument("--staging-mib", type=int, default=0, help="first-hit staging limit per GPU in MiB (0 = the library default, 8 GiB)")
+    ap.add_argument("--lane-tiles", type=int, default=0, help="SptParams.lane_tiles (0 = chosen by the library)")
     ap.add_argument("--no-extra", action="store_true", help="skip the short c4 / c5 legs after the headline")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]

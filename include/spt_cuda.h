@@ -120,7 +120,9 @@ typedef struct SptParams {
                                           Must be 0 / 1 on a multi-device context (the library partitions itself). */
     uint32_t split_chunk;              /* split rendering: samples of every pixel traced per pair of kernel launches.
                                           0 = as many as the staging limit allows (spt_cuda_set_staging_limit). */
-    uint32_t reserved;                 /* must be 0 */
+    uint32_t lane_tiles;               /* split rendering: pixels a lane of the bounce kernel renders one after the other (tile rows
+                                          spread over the segment), which evens out the work of a warp's lanes when chunks are
+                                          short.  0 = chosen by the library from the chunk length and the grid size; 1..64. */
 } SptParams;
 #define SPT_BAND_ROWS 8u
 
@@ -130,6 +132,8 @@ typedef struct SptCounters {
     uint64_t samples;  /* camera samples traced */
     uint64_t dropped;  /* samples dropped by pass_cap */
     uint64_t exact;    /* sphere evaluations that went through the exact (reference-order) sequence */
+    uint64_t warp_iterations; /* split rendering: closest-hit trips of the bounce kernel, counted per WARP; the share of lanes
+                                 that held a ray in them is (segments - samples) / (32 * warp_iterations) */
 } SptCounters;
 
 typedef struct SptTiming {
@@ -232,11 +236,16 @@ SPT_API int spt_cuda_get_timing(SptContext *ctx, SptTiming *out);
  * denominator BASELINE.md section 4 asks for).  scalar: fma.rn.f32; packed: fma.rn.f32x2. */
 SPT_API int spt_cuda_measure_fp32_peak(SptContext *ctx, float *tflops_scalar, float *tflops_packed);
 
+/* Device self-check of the shared-reciprocal division the kernels use in Normalize and in the camera ray (csrc/spt_device.cuh):
+ * `sets` pseudo-random operand sets (rounded up to whole warps), each compared bit for bit with __fdiv_rn.  Blocking. */
+SPT_API int spt_cuda_self_check_division(SptContext *ctx, uint64_t seed, uint64_t sets, uint64_t *tested, uint64_t *mismatches);
+
 SPT_API const char *spt_cuda_last_error(void);
 SPT_API const char *spt_cuda_version(void);
 
 /* Layout revision of the structs above.  A caller compiled against another revision of this header must not call in
-   (revision 2 appended band_count / band_index to SptParams, revision 3 split_chunk / reserved): compare with
+   (revision 2 appended band_count / band_index to SptParams, revision 3 split_chunk / lane_tiles, SptTiming.primary_ms / secondary_ms,
+   SptCounters.warp_iterations): compare with
    SPT_ABI_VERSION once after loading. */
 #define SPT_ABI_VERSION 3u
 SPT_API uint32_t spt_cuda_abi_version(void);

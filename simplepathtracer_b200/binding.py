@@ -146,12 +146,13 @@ class _CParams(C.Structure):
         ("band_count", C.c_uint32),
         ("band_index", C.c_uint32),
         ("split_chunk", C.c_uint32),
-        ("reserved", C.c_uint32),
+        ("lane_tiles", C.c_uint32),
     ]
 
 
 class Counters(C.Structure):
-    _fields_ = [("segments", C.c_uint64), ("tests", C.c_uint64), ("samples", C.c_uint64), ("dropped", C.c_uint64), ("exact", C.c_uint64)]
+    _fields_ = [("segments", C.c_uint64), ("tests", C.c_uint64), ("samples", C.c_uint64), ("dropped", C.c_uint64), ("exact", C.c_uint64),
+                ("warp_iterations", C.c_uint64)]
 
     def asdict(self):
         return {k: int(getattr(self, k)) for k, _ in self._fields_}
@@ -180,7 +181,7 @@ EXPORTS = [
     "spt_cuda_render", "spt_cuda_accumulate", "spt_cuda_resolve", "spt_cuda_synchronize", "spt_cuda_first_hit",
     "spt_cuda_progressive_begin", "spt_cuda_progressive_add", "spt_cuda_progressive_image", "spt_cuda_progressive_load",
     "spt_cuda_closest_hit", "spt_cuda_get_counters", "spt_cuda_reset_counters", "spt_cuda_get_timing",
-    "spt_cuda_measure_fp32_peak", "spt_cuda_last_error", "spt_cuda_version", "spt_cuda_abi_version",
+    "spt_cuda_measure_fp32_peak", "spt_cuda_self_check_division", "spt_cuda_last_error", "spt_cuda_version", "spt_cuda_abi_version",
 ]
 HOST_EXPORTS = [
     "spt_host_init_spheres", "spt_host_generate_spheres", "spt_host_generate_metal_glass", "spt_host_generate_lattice",
@@ -231,6 +232,8 @@ def load_library():
     L.spt_cuda_reset_counters.argtypes = [C.c_void_p]
     L.spt_cuda_get_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
     L.spt_cuda_measure_fp32_peak.argtypes = [C.c_void_p, f32p, f32p]
+    if hasattr(L, "spt_cuda_self_check_division"):  # absent from libraries built before it existed (A/B runs via SPT_CUDA_LIB)
+        L.spt_cuda_self_check_division.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     gen = [C.c_uint32, C.c_uint32, f32p, f32p, u8p, f32p, f32p]
     L.spt_host_init_spheres.argtypes = gen
     L.spt_host_generate_spheres.argtypes = gen
@@ -291,6 +294,7 @@ class PathTracer:
         self.device = self.devices[0]
         self.scene: Optional[Scene] = None
         self.split_chunk = 0  # SptParams.split_chunk of every call made through this object (0 = as the staging limit allows)
+        self.lane_tiles = 0  # SptParams.lane_tiles (0 = chosen by the library)
 
     def device_count(self) -> int:
         return int(self.L.spt_cuda_device_count(self.h))
@@ -346,7 +350,7 @@ class PathTracer:
 
     def _params(self, width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags, bands=None) -> _CParams:
         count, index = bands if bands else (0, 0)  # (band_count, band_index): interleaved 8-row bands, include/spt_cuda.h
-        return _CParams(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags, count, index, int(self.split_chunk), 0)
+        return _CParams(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags, count, index, int(self.split_chunk), int(self.lane_tiles))
 
     def render(self, cam, width, height, spp, depth, pass_cap=0, seed=1, seg=None, sample_begin=0, variant=MEGAKERNEL,
                flags=0, rgb8: Optional[np.ndarray] = None, want_accum: bool = False):
@@ -434,6 +438,12 @@ class PathTracer:
         self._check(self.L.spt_cuda_get_timing(self.h, C.byref(t)))
         return {"trace_ms": float(t.trace_ms), "resolve_ms": float(t.resolve_ms), "launches": int(t.launches),
                 "primary_ms": float(t.primary_ms), "secondary_ms": float(t.secondary_ms)}
+
+    def self_check_division(self, sets: int, seed: int = 1):
+        """(operand sets tested, mismatches against __fdiv_rn) of the shared-reciprocal division (spt_cuda_self_check_division)."""
+        t, m = C.c_uint64(), C.c_uint64()
+        self._check(self.L.spt_cuda_self_check_division(self.h, seed, sets, C.byref(t), C.byref(m)))
+        return int(t.value), int(m.value)
 
     def measure_fp32_peak(self):
         a, b = C.c_float(), C.c_float()

@@ -256,8 +256,8 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
         return fail(SPT_ERR_NO_SCENE, "spt_cuda_set_scene has not been called");
     if (prm->variant != SPT_VARIANT_MEGAKERNEL && prm->variant != SPT_VARIANT_WAVEFRONT)
         return fail(SPT_ERR_INVALID, "unknown variant");
-    if (prm->reserved != 0u)
-        return fail(SPT_ERR_INVALID, "SptParams.reserved must be 0 (struct built against another revision of spt_cuda.h?)");
+    if (prm->lane_tiles > 64u)
+        return fail(SPT_ERR_INVALID, "SptParams.lane_tiles must be 0 (automatic) or 1..64");
     c->timing.trace_ms = 0.f;
     c->timing.launches = 0;
     c->timing.primary_ms = c->timing.secondary_ms = 0.f;
@@ -407,6 +407,20 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             dim3 const sBlock(streamed ? spt::kBlockThreads : spt::SplitShape::kThreads);
             SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
             SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+            // Pixels per lane of the bounce kernel (spt_split.cuh, secondary_bounce_loop).  A warp leaves when its slowest lane
+            // does; with short chunks the lanes' totals differ a lot (few samples to average over), so each lane renders
+            // several pixels from tile rows far apart: about 256 samples per lane, as long as the grid keeps >= 8 waves.
+            uint32_t laneTiles = prm->lane_tiles;
+            if (laneTiles == 0)
+            {
+                laneTiles = std::max(1u, std::min(64u, 256u / std::max(1u, chunk)));
+                uint64_t const slots = uint64_t(c->prop.multiProcessorCount) * (streamed ? 4u : 8u);
+                while (laneTiles > 1 && uint64_t(sGrid.x) * ((myBands + laneTiles - 1) / laneTiles) < 8 * slots)
+                    laneTiles /= 2;
+            }
+            laneTiles = std::min(laneTiles, std::max(1u, myBands));
+            p.tileRows = myBands;
+            dim3 const sGrid2(sGrid.x, (myBands + laneTiles - 1) / laneTiles);
             // camera kernels on the auxiliary stream (after everything queued on the main stream so far), bounce kernels on
             // the main stream: P(k) needs buffer k % 2 free (S(k-2) done), S(k) needs P(k); S(k) after S(k-1) by stream order
             // (the per-pixel running sums continue across chunks).  Every camera kernel is waited for by a bounce kernel on
@@ -443,7 +457,7 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
                     SPT_CUDA_CHECK(cudaStreamWaitEvent(c->stream, c->evPrimary[b], 0));
                 }
                 SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * k + 2], c->stream));
-                secondary<<<sGrid, sBlock, smem, c->stream>>>(p);
+                secondary<<<sGrid2, sBlock, smem, c->stream>>>(p);
                 SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * k + 3], c->stream));
                 if (overlap)
                     SPT_CUDA_CHECK(cudaEventRecord(c->evSecondary[b], c->stream));
@@ -634,6 +648,18 @@ int upload_scene(SptContext *c, const HostScene &hs)
     c->filter.bigIdx = dBigIdx;
     c->filter.nBig = uint32_t(hs.big.size());
     c->filter.amax = hs.amax;
+    {
+        // origins with |O|^2 <= nearOO satisfy amax + |O| <= 1024 (make_filter_ray's tC test needs no widening there)
+        double const t = 1024.0 - double(hs.amax);
+        float near = -1.f;
+        if (t > 0.0)
+        {
+            near = float(t * t);
+            if (double(near) > t * t)
+                near = std::nextafterf(near, -INFINITY);
+        }
+        c->filter.nearOO = near;
+    }
     c->n = hs.n;
     return SPT_OK;
 }
@@ -1239,6 +1265,7 @@ int spt_cuda_get_counters(SptContext *c, SptCounters *out)
         out->samples += h[1];
         out->dropped += h[2];
         out->exact += h[3];
+        out->warp_iterations += h[4];
     }
     return SPT_OK;
 }
@@ -1293,6 +1320,31 @@ int spt_cuda_get_timing(SptContext *c, SptTiming *out)
         t.secondary_ms = std::max(t.secondary_ms, d->timing.secondary_ms);
     }
     *out = t;
+    return SPT_OK;
+}
+
+int spt_cuda_self_check_division(SptContext *c, uint64_t seed, uint64_t sets, uint64_t *tested, uint64_t *mismatches)
+{
+    if (!c || !tested || !mismatches)
+        return fail(SPT_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    int rc = ensure_probe(c, 256);
+    if (rc)
+        return rc;
+    unsigned long long *dOut = static_cast<unsigned long long *>(c->dProbe);
+    SPT_CUDA_CHECK(cudaMemsetAsync(dOut, 0, 16, c->stream));
+    uint32_t const threads = 256, blocks = uint32_t(c->prop.multiProcessorCount) * 8u;
+    uint64_t const perThread = std::max<uint64_t>(1, (sets + uint64_t(threads) * blocks - 1) / (uint64_t(threads) * blocks));
+    if (perThread > 0xFFFFFFFFull)
+        return fail(SPT_ERR_INVALID, "too many operand sets");
+    spt::division_selfcheck_kernel<<<blocks, threads, 0, c->stream>>>(seed, uint32_t(perThread), dOut);
+    SPT_CUDA_CHECK(cudaGetLastError());
+    unsigned long long h[2] = {0, 0};
+    SPT_CUDA_CHECK(cudaMemcpyAsync(h, dOut, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    *tested = h[0];
+    *mismatches = h[1];
     return SPT_OK;
 }
 

@@ -65,6 +65,7 @@ struct FilterScene
     const uint32_t *bigIdx;   // spheres always evaluated exactly
     uint32_t nBig;
     float amax;               // max |C_i| over filtered spheres
+    float nearOO;             // origins with |O|^2 <= nearOO have amax + |O| <= 1024: the tC test needs no widening (host, rounded down)
     float epsTCam;            // camera form only: the epsT the launch's records were built with (0 unless the eye is far away)
 };
 
@@ -112,15 +113,14 @@ struct FilterRay
     unsigned long long noo;           // -|O|^2 + S_ray
 };
 
-__device__ __forceinline__ FilterRay make_filter_ray(V3 dir, V3 org, float od, float amax)
+__device__ __forceinline__ FilterRay make_filter_ray(V3 dir, V3 org, float od, float amax, float nearOO)
 {
     float const oo = __fmaf_ru(org.z, org.z, __fmaf_ru(org.y, org.y, __fmul_ru(org.x, org.x))); // >= |O|^2
     float sRay = __fmul_ru(oo, float(kSlackU) * 1.0001f);
     float epsT = 0.f;
-    float const b = __fsqrt_ru(oo);
-    float const m = __fadd_ru(amax, b);
-    if (m > 1024.f)
+    if (!(oo <= nearOO)) // amax + |O| may exceed 1024 (decided without a square root: nearOO = (1024 - amax)^2, rounded down)
     { // far-away origin: widen the tC test, and pay for shifting tC in the square
+        float const m = __fadd_ru(amax, __fsqrt_ru(oo));
         epsT = __fmul_ru(m, 9.5367431640625e-7f);                   // 2^-20 (Amax + B)
         sRay = __fadd_ru(sRay, __fmul_ru(__fmul_ru(m, m), 3.8146973e-6f)); // + 2^-18 (Amax + B)^2
     }
@@ -203,12 +203,12 @@ __device__ __forceinline__ FilterRay make_filter_ray_cam(V3 dir, float od, float
 // loop (resolve_candidates) runs once per super-word, so lanes with candidates in different words of the same
 // super-word are served in the same trips.
 //
-// resolve_candidates: the exact sequence on the candidates parked in c0..c3: c_k holds the mask of word (wEnd - 1 - k) of the span.  Leaves all
-// four masks zero.  Lanes without candidates idle here (the only divergent part of the closest hit).
+// resolve_candidates: the exact sequence on the candidates parked in c0..c4: c_k holds the mask of word (wEnd - 1 - k) of the span.  Leaves all
+// five masks zero.  Lanes without candidates idle here (the only divergent part of the closest hit).
 template <typename GeomPtr>
-__device__ __forceinline__ void resolve_candidates(uint32_t &c0, uint32_t &c1, uint32_t &c2, uint32_t &c3, uint32_t wEnd, const uint32_t *slotIdx,
-                                                   GeomPtr geom, uint32_t n, V3 dir, V3 org, float od, uint32_t &minIndex,
-                                                   float &minDistanceSq, uint32_t &exactEvals)
+__device__ __forceinline__ void resolve_candidates(uint32_t &c0, uint32_t &c1, uint32_t &c2, uint32_t &c3, uint32_t &c4, uint32_t wEnd,
+                                                   const uint32_t *slotIdx, GeomPtr geom, uint32_t n, V3 dir, V3 org, float od,
+                                                   uint32_t &minIndex, float &minDistanceSq, uint32_t &exactEvals)
 {
     for (;;)
     {
@@ -217,13 +217,15 @@ __device__ __forceinline__ void resolve_candidates(uint32_t &c0, uint32_t &c1, u
         else if (c1) { k = 1; bits = c1; }
         else if (c2) { k = 2; bits = c2; }
         else if (c3) { k = 3; bits = c3; }
+        else if (c4) { k = 4; bits = c4; }
         else break;
         uint32_t const j = __clz(bits);
         uint32_t const cleared = bits & ~(0x80000000u >> j);
         if (k == 0) c0 = cleared;
         else if (k == 1) c1 = cleared;
         else if (k == 2) c2 = cleared;
-        else c3 = cleared;
+        else if (k == 3) c3 = cleared;
+        else c4 = cleared;
         uint32_t const i = slotIdx[(wEnd - 1u - k) * kWordSpheres + j];
         if (i < n) // padding records can only show up for NaN rays
         {
@@ -231,6 +233,21 @@ __device__ __forceinline__ void resolve_candidates(uint32_t &c0, uint32_t &c1, u
             ++exactEvals;
         }
     }
+}
+
+// When the parked masks are resolved: after kSuperWords words -- unless exactly ONE word is left in the span, which then
+// joins the round (a 149-sphere list is 4 full words + 24 slots: one divergent round per closest hit instead of two; the
+// trips of a round are the maximum over the lanes, so one round over five words makes fewer than two rounds over 4 + 1).
+#ifndef SPT_RESOLVE_MERGE_TAIL
+#define SPT_RESOLVE_MERGE_TAIL 1
+#endif
+__device__ __forceinline__ bool resolve_now(uint32_t pend, uint32_t w, uint32_t nWords)
+{
+#if SPT_RESOLVE_MERGE_TAIL
+    return w == nWords || (pend >= kSuperWords && w + 1u != nWords);
+#else
+    return w == nWords || pend >= kSuperWords;
+#endif
 }
 
 template <bool CAM = false, typename GeomPtr>
@@ -241,8 +258,8 @@ __device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_
     uint32_t const nWords = (spanSlots + kWordSpheres - 1u) / kWordSpheres;
     uint32_t const tailQuads = (spanSlots - (nWords - 1u) * kWordSpheres) / kQuadSpheres; // 1..4 quads in the last word
     uint32_t const nFull = tailQuads == kWordSpheres / kQuadSpheres ? nWords : nWords - 1u; // words with all 16 records
-    // candidate masks of the last kSuperWords words filtered, newest in c0 (a shift register: no per-word selects)
-    uint32_t c0 = 0u, c1 = 0u, c2 = 0u, c3 = 0u;
+    // candidate masks of the last (up to kSuperWords + 1) words filtered, newest in c0 (a shift register: no per-word selects)
+    uint32_t c0 = 0u, c1 = 0u, c2 = 0u, c3 = 0u, c4 = 0u, pend = 0u;
 #pragma unroll 1
     for (uint32_t w = 0; w < nWords;) // everything about w is warp-uniform
     {
@@ -268,10 +285,12 @@ __device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_
                     filter_pair(rec + pp, fr, mask);
             }
             rec += kWordSpheres;
+            c4 = c2;
             c3 = c1;
             c2 = c0;
             c1 = live ? ~mask0 : 0u;
             ++w;
+            ++pend;
         }
         else
 #endif
@@ -306,14 +325,19 @@ __device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_
                 uint32_t const sh = kWordSpheres - kQuadSpheres * tailQuads; // 8, 16 or 24 missing slots: fail bits
                 mask = (mask << sh) | ((1u << sh) - 1u);
             }
+            c4 = c3;
             c3 = c2;
             c2 = c1;
             c1 = c0;
         }
         c0 = live ? ~mask : 0u; // bit (31 - j) set <=> slot j of the word is a candidate
         ++w;
-        if ((w & (kSuperWords - 1u)) == 0u || w == nWords)
-            resolve_candidates(c0, c1, c2, c3, w, slotIdx, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals);
+        ++pend;
+        if (resolve_now(pend, w, nWords))
+        {
+            resolve_candidates(c0, c1, c2, c3, c4, w, slotIdx, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals);
+            pend = 0u;
+        }
     }
 }
 
@@ -344,7 +368,7 @@ __device__ __forceinline__ uint32_t closest_hit_filtered(const FilterScene &fs, 
     float minDistanceSq = FLT_MAX;
     float const od = vdot(org, dir);
     exact_big_spheres(fs, geom, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
-    FilterRay const fr = make_filter_ray(dir, org, od, fs.amax);
+    FilterRay const fr = make_filter_ray(dir, org, od, fs.amax, fs.nearOO);
     filter_span(fs.pairs, fs.slotIdx, fs.nSlots, fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
     return minIndex;
 }
@@ -383,7 +407,7 @@ __device__ __forceinline__ void filter_span_cam2(const FilterPair *rec, const ui
     uint32_t const nWords = (spanSlots + kWordSpheres - 1u) / kWordSpheres;
     uint32_t const tailQuads = (spanSlots - (nWords - 1u) * kWordSpheres) / kQuadSpheres;
     uint32_t const nFull = tailQuads == kWordSpheres / kQuadSpheres ? nWords : nWords - 1u;
-    uint32_t a0 = 0u, a1 = 0u, a2 = 0u, a3 = 0u, b0 = 0u, b1 = 0u, b2 = 0u, b3 = 0u;
+    uint32_t a0 = 0u, a1 = 0u, a2 = 0u, a3 = 0u, a4 = 0u, b0 = 0u, b1 = 0u, b2 = 0u, b3 = 0u, b4 = 0u, pend = 0u;
 #pragma unroll 1
     for (uint32_t w = 0; w < nWords;)
     {
@@ -409,13 +433,15 @@ __device__ __forceinline__ void filter_span_cam2(const FilterPair *rec, const ui
             maskA = (maskA << sh) | ((1u << sh) - 1u);
             maskB = (maskB << sh) | ((1u << sh) - 1u);
         }
-        a3 = a2; a2 = a1; a1 = a0; a0 = liveA ? ~maskA : 0u;
-        b3 = b2; b2 = b1; b1 = b0; b0 = liveB ? ~maskB : 0u;
+        a4 = a3; a3 = a2; a2 = a1; a1 = a0; a0 = liveA ? ~maskA : 0u;
+        b4 = b3; b3 = b2; b2 = b1; b1 = b0; b0 = liveB ? ~maskB : 0u;
         ++w;
-        if ((w & (kSuperWords - 1u)) == 0u || w == nWords)
+        ++pend;
+        if (resolve_now(pend, w, nWords))
         {
-            resolve_candidates(a0, a1, a2, a3, w, slotIdx, geom, n, dirA, org, odA, minA, distA, exactEvals);
-            resolve_candidates(b0, b1, b2, b3, w, slotIdx, geom, n, dirB, org, odB, minB, distB, exactEvals);
+            resolve_candidates(a0, a1, a2, a3, a4, w, slotIdx, geom, n, dirA, org, odA, minA, distA, exactEvals);
+            resolve_candidates(b0, b1, b2, b3, b4, w, slotIdx, geom, n, dirB, org, odB, minB, distB, exactEvals);
+            pend = 0u;
         }
     }
 }

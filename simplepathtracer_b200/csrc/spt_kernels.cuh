@@ -63,6 +63,9 @@ struct TraceParams
     // [(y - yBegin) * segW + (x - xBegin)][sample - sampleBegin]
     float4 *firstHits;
     FilterScene filterCam; // pre-filter records specialised for the eye (camera form)
+    // bounce kernels of split rendering: every lane walks the tile rows blockIdx.y, blockIdx.y + gridDim.y, ... < tileRows one
+    // pixel after the other (tileRows = tile rows the launch covers; gridDim.y = ceil(tileRows / tiles per lane))
+    uint32_t tileRows;
 };
 
 constexpr uint32_t kMissIndex = 0xFFFFFFFFu;
@@ -244,11 +247,37 @@ struct ShellSlots
     uint32_t base[32];
 };
 
+#ifndef SPT_SHELL_LOCAL
+#define SPT_SHELL_LOCAL 2 // attempts every lane makes on its OWN stream before the cooperative rounds start (0: none)
+#endif
 __device__ __forceinline__ V3 coop_shell(bool need, unsigned long long state0, ShellSlots &slot)
 {
     uint32_t const lane = threadIdx.x & 31u;
     V3 sh = v3(0.f, 0.f, 0.f);
     uint32_t base = 0;
+#if SPT_SHELL_LOCAL > 0
+    // Round 0 needs no coordination: with most of the warp pending there is at most one helper per lane anyway, so every lane
+    // evaluates the first SPT_SHELL_LOCAL attempts of its own stream (independent chains: instruction-level parallelism
+    // instead of ballots, shared-memory slots and shuffles) and keeps the FIRST accepted one.  72 % of the lanes are done
+    // after two attempts; the cooperative rounds below then serve the few that are left with 4 or more helpers each.
+    {
+        V3 cand[SPT_SHELL_LOCAL];
+        bool ok[SPT_SHELL_LOCAL];
+#pragma unroll
+        for (int t = 0; t < SPT_SHELL_LOCAL; ++t)
+            ok[t] = shell_attempt(state0, uint32_t(t), cand[t]);
+        bool got = false;
+#pragma unroll
+        for (int t = 0; t < SPT_SHELL_LOCAL; ++t)
+            if (!got && ok[t])
+            {
+                sh = cand[t];
+                got = true;
+            }
+        base = SPT_SHELL_LOCAL;
+        need = need && !got;
+    }
+#endif
     uint32_t pending = __ballot_sync(0xffffffffu, need);
     while (pending) // warp-uniform
     {
@@ -439,23 +468,33 @@ __device__ __forceinline__ void warp_counter_add(unsigned long long *ctr, unsign
         atomicAdd(ctr, v);
 }
 
-// pixel of this lane inside the segment: warps tile 8x4, blocks 32x8
+// pixel of this lane inside the segment, in tile row `tileRow` of the launch: warps tile 8x4, blocks 32x8
 template <typename S = DefaultShape>
-__device__ __forceinline__ void lane_pixel(const TraceParams &p, uint32_t &x, uint32_t &y, bool &inside)
+__device__ __forceinline__ void lane_pixel_at(const TraceParams &p, uint32_t tileRow, uint32_t &x, uint32_t &y, bool &inside)
 {
     uint32_t const lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t const lx = (lane & (kWarpW - 1)) + (warp % S::kWarpsX) * kWarpW;
     uint32_t const ly = (lane / kWarpW) + (warp / S::kWarpsX) * kWarpH;
     x = p.xBegin + blockIdx.x * S::kTileW + lx;
-    y = p.yBegin + (blockIdx.y * p.bandCount + p.bandIndex) * S::kTileH + ly;
+    y = p.yBegin + (tileRow * p.bandCount + p.bandIndex) * S::kTileH + ly;
     inside = x < p.xEnd && y < p.yEnd;
+}
+template <typename S = DefaultShape>
+__device__ __forceinline__ void lane_pixel(const TraceParams &p, uint32_t &x, uint32_t &y, bool &inside)
+{
+    lane_pixel_at<S>(p, blockIdx.y, x, y, inside);
 }
 // row of this lane among the rows the LAUNCH covers (== y - yBegin unless the call renders interleaved bands)
 template <typename S = DefaultShape>
-__device__ __forceinline__ uint32_t lane_row_local()
+__device__ __forceinline__ uint32_t lane_row_local_at(uint32_t tileRow)
 {
     uint32_t const lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    return blockIdx.y * S::kTileH + (lane / kWarpW) + (warp / S::kWarpsX) * kWarpH;
+    return tileRow * S::kTileH + (lane / kWarpW) + (warp / S::kWarpsX) * kWarpH;
+}
+template <typename S = DefaultShape>
+__device__ __forceinline__ uint32_t lane_row_local()
+{
+    return lane_row_local_at<S>(blockIdx.y);
 }
 static_assert(kTileH == 8 && BlockShape<2, 2>::kTileH == 8, "SPT_BAND_ROWS is one tile row of every tracing kernel");
 
@@ -638,6 +677,60 @@ __global__ void closest_hit_kernel(const float4 *geom, uint32_t n, FilterScene f
     idx[k] = r;
     if (evals)
         evals[k] = exactEvals;
+}
+
+// ---- self-check of the shared-reciprocal division (spt_device.cuh) ------------------------------------------------
+// Every thread draws operand pairs from a counter RNG -- random mantissas; exponents mostly inside the fast path's domain,
+// a share of them at and beyond its edges, plus zeros / denormals / infinities -- and compares, bit for bit,
+//   fdiv_shared(a, b, rcp_refined(b))  with  __fdiv_rn(a, b)            (the camera ray's divisions by the image size)
+//   vnormalize(v)                      with  the three __fdiv_rn by sqrt_rn(|v|^2)  (Math.hpp:140-154)
+// out[0] += operand sets tested, out[1] += mismatches (must stay 0).
+__device__ __forceinline__ float selfcheck_operand(uint64_t z, uint32_t kind)
+{
+    uint32_t const mant = uint32_t(z) & 0x7FFFFFu, sign = uint32_t(z >> 63) << 31;
+    uint32_t e;
+    uint32_t const r = uint32_t(z >> 32) & 0xFFFFu;
+    if (kind < 12u)
+        e = 127u - 60u + r % 121u; // 2^-60 .. 2^60: the fast path's domain
+    else if (kind < 14u)
+        e = 127u - 64u + r % 9u + (r & 0x100u ? 120u : 0u); // around either edge of the domain
+    else if (kind == 14u)
+        e = r % 255u; // anything finite, denormals and zero included
+    else
+        return (r & 1u) ? 0.f : __uint_as_float(sign | 0x7F800000u | ((r & 2u) ? mant : 0u)); // zero, infinity, NaN
+    return __uint_as_float(sign | (e << 23) | ((kind == 14u && e == 0u && (r & 0x200u)) ? 0u : mant));
+}
+__device__ __forceinline__ bool same_bits(float x, float y)
+{
+    return __float_as_uint(x) == __float_as_uint(y) || (x != x && y != y);
+}
+__global__ void __launch_bounds__(256) division_selfcheck_kernel(uint64_t seed, uint32_t perThread, unsigned long long *out)
+{
+    uint64_t const tid = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    uint64_t state = mix64(seed + SPT_GOLDEN * (tid + 1ull));
+    unsigned long long bad = 0;
+    for (uint32_t i = 0; i < perThread; ++i)
+    {
+        uint64_t const z0 = mix64(state += SPT_GOLDEN), z1 = mix64(state += SPT_GOLDEN), z2 = mix64(state += SPT_GOLDEN);
+        uint32_t const kind = uint32_t(z0 >> 48) & 15u;
+        float const a = selfcheck_operand(z0, kind), b = selfcheck_operand(z1, (kind + 5u) & 15u);
+        // a divisor the callers would hand over: a positive, safe one (image sizes; a vector's length is checked by vnormalize itself)
+        float const bs = fabsf(b);
+        if (div_operand_safe(bs))
+            bad += same_bits(fdiv_shared(a, bs, rcp_refined(bs)), __fdiv_rn(a, bs)) ? 0u : 1u;
+        V3 const v = v3(a, b, selfcheck_operand(z2, (kind + 11u) & 15u));
+        float const l = fsqrt(vlensq(v));
+        V3 const n = vnormalize(v);
+        bad += (same_bits(n.x, __fdiv_rn(v.x, l)) && same_bits(n.y, __fdiv_rn(v.y, l)) && same_bits(n.z, __fdiv_rn(v.z, l))) ? 0u : 1u;
+    }
+    for (int o = 16; o > 0; o >>= 1)
+        bad += __shfl_down_sync(0xffffffffu, bad, o);
+    if ((threadIdx.x & 31) == 0)
+    {
+        atomicAdd(out + 0, 32ull * perThread);
+        if (bad)
+            atomicAdd(out + 1, bad);
+    }
 }
 
 // ---- resolve ------------------------------------------------------------------------------------

@@ -115,7 +115,7 @@ __device__ __forceinline__ uint32_t streamed_closest_hit(const FilterScene &fs, 
     float minDistanceSq = FLT_MAX;
     float const od = vdot(org, dir);
     exact_big_spheres(fs, geom, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
-    FilterRay const fr = CAM ? make_filter_ray_cam(dir, od, fs.epsTCam) : make_filter_ray(dir, org, od, fs.amax);
+    FilterRay const fr = CAM ? make_filter_ray_cam(dir, od, fs.epsTCam) : make_filter_ray(dir, org, od, fs.amax, fs.nearOO);
     for (uint32_t c = 0; c < nChunks; ++c)
     {
         if (threadIdx.x == 0 && c + kAhead < nChunks)

@@ -11,6 +11,8 @@
 //                [--checkpoint file] resume from the accumulators in `file` when it was written for THIS render (size, depth,
 //                                    seed, scene, camera, tracer), rewrite it after every pass
 //                [--gpus N]          one render spread over CUDA devices 0..N-1 by the library (spt_cuda_create_multi)
+//                [--devices a,b,..]  the same with an explicit list of CUDA ordinals (an ordinal may repeat: several internal
+//                                    contexts on one GPU)
 //                [--staging-mib M]   first-hit staging budget of split rendering per device (default 8192)
 #include "../../include/spt_host/Scene.hpp"
 #include "../../include/spt_host/SceneFile.hpp"
@@ -18,6 +20,7 @@
 #include "../../include/spt_host/Image.hpp"
 #include "../../include/CudaPathTracer.hpp"
 
+#include <algorithm>
 #include <chrono>
 #include <cstring>
 #include <iostream>
@@ -28,7 +31,7 @@
 int main(int argc, char **argv)
 {
     std::string scene = "reference", tracer = "recursive", out;
-    std::string pfm, checkpoint, dumpScene;
+    std::string pfm, checkpoint, dumpScene, deviceList;
     uint32_t seed = 1, width = 1440, height = 1440, spp = 100, depth = 10, tiles = 1, progressive = 0, gpus = 1, stagingMib = 0;
     for (int i = 1; i + 1 < argc; i += 2)
     {
@@ -47,6 +50,7 @@ int main(int argc, char **argv)
         else if (k == "--dump-scene") dumpScene = v;
         else if (k == "--checkpoint") checkpoint = v;
         else if (k == "--gpus") gpus = uint32_t(std::stoul(v));
+        else if (k == "--devices") deviceList = v;
         else if (k == "--staging-mib") stagingMib = uint32_t(std::stoul(v));
         else { std::cerr << "unknown flag " << k << "\n"; return 2; }
     }
@@ -60,7 +64,18 @@ int main(int argc, char **argv)
     if (!dumpScene.empty() && !io::SaveScene(dumpScene.c_str())) { std::cerr << "cannot write " << dumpScene << "\n"; return 1; }
     spt_cuda::SetSeed(seed);
     spt_cuda::InvalidateScene();
-    if (gpus > 1)
+    if (!deviceList.empty())
+    {
+        std::vector<int> devices;
+        for (size_t pos = 0; pos <= deviceList.size();)
+        {
+            size_t const comma = std::min(deviceList.find(',', pos), deviceList.size());
+            devices.push_back(std::stoi(deviceList.substr(pos, comma - pos)));
+            pos = comma + 1;
+        }
+        spt_cuda::SetDevices(devices);
+    }
+    else if (gpus > 1)
     {
         std::vector<int> devices(gpus);
         for (uint32_t k = 0; k < gpus; ++k)

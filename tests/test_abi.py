@@ -38,7 +38,7 @@ def test_struct_sizes_match_header():
     assert ctypes.sizeof(binding._CCamera) == 96
     assert ctypes.sizeof(binding._CParams) == 56  # revision 2: band_count, band_index; revision 3: split_chunk, reserved
     assert ctypes.sizeof(binding._CScene) == 48
-    assert ctypes.sizeof(binding.Counters) == 40
+    assert ctypes.sizeof(binding.Counters) == 48
     assert ctypes.sizeof(binding.Timing) == 24
 
 

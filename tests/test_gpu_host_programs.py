@@ -108,3 +108,39 @@ def test_headless_scene_file(tmp_path):
 
     sc, _ = spt.load_scene_file(scn)
     assert sc.n == 501
+
+
+def test_headless_multi_device_and_checkpoint_identity(tmp_path, oracle):
+    """spt_headless --devices a,b: ONE render spread over two device contexts by the library (RenderImageParallelMain's role,
+    Renderer.hpp:257-302).  8 samples over 2 devices = sample ranges: the image is the in-order sum of two partial renders,
+    which the oracle reproduces exactly; --tiles with ragged, partly empty tiles works (both tile ends are clamped); and a
+    checkpoint written for another scene is refused."""
+    import torch
+
+    exe = os.path.join(ROOT, "simplepathtracer_b200", "host", "spt_headless")
+    subprocess.run(["make", "-s", "-C", os.path.dirname(exe)], check=True)
+    devs = "0,1" if torch.cuda.device_count() >= 2 else "0,0"
+    w, h, spp, depth, seed = 90, 52, 8, 6, 3
+    out = str(tmp_path / "multi.bmp")
+    base = ["--seed", str(seed), "--width", str(w), "--height", str(h), "--depth", str(depth), "--tracer", "task"]
+    r = subprocess.run([exe, "--scene", "random", "--spp", str(spp), "--devices", devs, "--out", out] + base, capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    scene = oracle.generate_spheres(seed)
+    cam = oracle.camera()
+    a, _ = oracle.render_accum(scene, cam, w, h, spp // 2, depth, pass_cap=10, seed=seed)
+    b, _ = oracle.render_accum(scene, cam, w, h, spp - spp // 2, depth, pass_cap=10, seed=seed, sample_begin=spp // 2)
+    assert np.array_equal(read_bmp(out), oracle.resolve(a + b))
+    # width 10 in 8 tiles: ceil-sized tiles run past the image, the last ones are empty
+    small = str(tmp_path / "small.bmp")
+    r = subprocess.run([exe, "--scene", "reference", "--seed", "2", "--width", "10", "--height", "9", "--spp", "2", "--depth", "4",
+                        "--tracer", "task", "--tiles", "8", "--out", small], capture_output=True, text=True)
+    assert r.returncode == 0 and "64/64" in r.stdout, r.stdout + r.stderr
+    acc, _ = oracle.render_accum(oracle.init_spheres(2), cam, 10, 9, 2, 4, pass_cap=10, seed=2)
+    assert np.array_equal(read_bmp(small), oracle.resolve(acc))
+    # checkpoint identity: same size / depth / seed, another scene -> not resumed
+    ck = str(tmp_path / "ck.sptacc")
+    assert subprocess.run([exe, "--scene", "reference", "--spp", "4", "--checkpoint", ck, "--out", out] + base).returncode == 0
+    r = subprocess.run([exe, "--scene", "random", "--spp", "8", "--checkpoint", ck, "--out", out] + base, capture_output=True, text=True)
+    assert r.returncode == 0 and "Resuming" not in r.stdout, r.stdout
+    r = subprocess.run([exe, "--scene", "random", "--spp", "8", "--checkpoint", ck, "--out", out] + base, capture_output=True, text=True)
+    assert r.returncode == 0 and "Resuming at sample 8" in r.stdout, r.stdout  # the file now belongs to the random scene, complete

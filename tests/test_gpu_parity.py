@@ -743,3 +743,17 @@ def test_multi_device_progressive(tracer, oracle, cam, scene_random):
         multi.progressive_add(cam, 4, 6, depth, pass_cap=10, seed=6)
         _, acc2 = multi.progressive_image(want_accum=True)
         assert_accum_equal(acc2, oacc)
+
+
+# ----------------------------------------------------------------------------- shared-reciprocal division
+def test_shared_reciprocal_division_equals_fdiv_rn(tracer):
+    """Normalize and the camera ray divide by a shared, once-refined reciprocal (csrc/spt_device.cuh: the inline fast path of
+    __fdiv_rn with its first three instructions hoisted).  On the device, 4e9 operand sets -- random mantissas, exponents
+    inside, at the edges of and beyond the fast path's domain, zeros, denormals, infinities, NaNs -- give the bits of
+    __fdiv_rn itself, for single quotients and for whole Normalize calls (Math.hpp:140-154)."""
+    total = 0
+    for seed in (1, 2, 3, 4):
+        tested, bad = tracer.self_check_division(1 << 30, seed=seed)
+        assert bad == 0, (seed, tested, bad)
+        total += tested
+    assert total >= 4 << 30

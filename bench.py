@@ -181,7 +181,10 @@ def run_reference_arm(args, wl):
 
 
 # --------------------------------------------------------------------------- native arm
-EXECUTED_FLOP = {"primary": 8, "secondary": 15}  # per (ray, slot) in the pre-filter: camera form 4 FMA; general form 7 FMA + 1 ADD
+# FMA-pipe flops the pre-filter really executes per (ray, sphere) test.  Bounce kernel: general form, 7 FMA + 1 ADD.  Camera
+# kernel: NONE per sample -- one camera-form test (4 FMA) per sphere, PIXEL and launch decides which few spheres a pixel's
+# samples can hit (pixel cone, csrc/spt_filter.cuh); the samples run the exact sequence on that list only.
+EXECUTED_FLOP = {"primary": None, "secondary": 15}
 
 
 def kernel_rooflines(ctr_per_render, n_spheres, primary_ms, secondary_ms, peak):
@@ -197,9 +200,13 @@ def kernel_rooflines(ctr_per_render, n_spheres, primary_ms, secondary_ms, peak):
             continue
         tests = segs * n_spheres
         alg = FLOP_PER_TEST * tests / (ms * 1e-3) / 1e12
-        exe = EXECUTED_FLOP[key] * tests / (ms * 1e-3) / 1e12
-        out[name] = {"ms_per_render": ms, "segments": segs, "tests": tests, "achieved": alg, "frac": alg / peak if peak else None,
-                     "executed_flop_per_test": EXECUTED_FLOP[key], "executed_frac": exe / peak if peak else None}
+        out[name] = {"ms_per_render": ms, "segments": segs, "tests": tests, "achieved": alg, "frac": alg / peak if peak else None}
+        if EXECUTED_FLOP[key]:
+            exe = EXECUTED_FLOP[key] * tests / (ms * 1e-3) / 1e12
+            out[name].update({"executed_flop_per_test": EXECUTED_FLOP[key], "executed_frac": exe / peak if peak else None})
+        else:
+            out[name]["note"] = ("algorithmic rate only: the tests of a camera sample are implied by ONE conservative test per sphere, pixel and "
+                                 "launch (pixel-cone candidate lists); per sample the kernel runs the exact sequence on the listed spheres")
         if key == "secondary" and ctr_per_render.get("warp_iterations"):
             # share of the lanes that held a ray in the bounce kernel's closest-hit trips (the rest waited for warp-mates)
             out[name]["lanes_with_a_ray"] = segs / (32.0 * ctr_per_render["warp_iterations"])
@@ -243,7 +250,7 @@ def run_native_arm(args, wl):
     staging = (args.staging_mib << 20) if args.staging_mib else spt.DEFAULT_STAGING_BYTES
     pt = spt.PathTracer(local)
     pt.set_staging_limit(staging)
-    pt.lane_tiles = args.lane_tiles
+    pt.strip_rows, pt.split_chunk = args.strip_rows, args.split_chunk
     # one explicit stream for torch fills, our kernels and the timing events
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
@@ -367,7 +374,7 @@ def run_native_arm(args, wl):
         "kernels": kernels,
         "step": {"achieved": achieved_step, "frac": achieved_step / peak if peak else None, "kernel_ms": kernel_ms,
                  "kernel_share_of_step": kernel_ms / ms_step,
-                 "launches": f"{trace_launches // 2} chunk(s) x (primary_hits_kernel + trace_secondary)" if split else f"{trace_launches} launch(es)",
+                 "launches": f"{trace_launches // 2} work item(s) x (primary_hits_kernel + trace_secondary)" if split else f"{trace_launches} launch(es)",
                  "serialised_chunks_ms": serial_ms},
         "traffic": traffic, "traffic_detail": traffic_detail,
         "exact_evals_per_segment": ctr["exact"] / max(ctr["segments"], 1),
@@ -440,7 +447,7 @@ def run_native_arm(args, wl):
                        "variant": args.variant, "sharding": (f"interleaved 8-row bands of pixels over {world} rank(s)" if args.partition == "bands" else f"sample ranges over {world} rank(s)")
                                    + " + NCCL sum-reduce of float4 accumulators",
                        "staging": f"first-hit staging limit {staging / 2**30:.0f} GiB per GPU (spt_cuda_set_staging_limit; library default 8 GiB), "
-                                  f"{trace_launches // 2 if split else 0} chunk(s) of samples per render",
+                                  f"{trace_launches // 2 if split else 0} work item(s) (strips of tile rows x chunks of samples) per render",
                        "l2": f"float4 accumulator {W * H * 16 / 1e6:.1f} MB per step vs 126 MB L2; kernel is compute-bound, scene staged in shared memory"},
             "e2e": e2e, "gpu_launches": launches_native, "roofline": roofline, "cpu_baseline": cpu, "workloads": workloads, "clocks": clock_info,
             "device": info["name"], "sm_count": info["sm_count"], "counters": ctr,
@@ -519,7 +526,8 @@ def main():
     ap.add_argument("--partition", default="samples", choices=["samples", "bands"], help="how N > 1 ranks share a render (sharding.py)")
     ap.add_argument("--flags", type=int, default=0, help="extra SPT_FLAG_* bits for the trace launches (experiments)")
     ap.add_argument("--staging-mib", type=int, default=0, help="first-hit staging limit per GPU in MiB (0 = the library default, 8 GiB)")
-    ap.add_argument("--lane-tiles", type=int, default=0, help="SptParams.lane_tiles (0 = chosen by the library)")
+    ap.add_argument("--strip-rows", type=int, default=0, help="SptParams.strip_rows (0 = chosen by the library; experiments)")
+    ap.add_argument("--split-chunk", type=int, default=0, help="SptParams.split_chunk (0 = chosen by the library; experiments)")
     ap.add_argument("--no-extra", action="store_true", help="skip the short c4 / c5 legs after the headline")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]

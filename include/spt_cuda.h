@@ -119,10 +119,9 @@ typedef struct SptParams {
                                           is RenderImageParallelMain's static tile grid (Renderer.hpp:264-274).
                                           Must be 0 / 1 on a multi-device context (the library partitions itself). */
     uint32_t split_chunk;              /* split rendering: samples of every pixel traced per pair of kernel launches.
-                                          0 = as many as the staging limit allows (spt_cuda_set_staging_limit). */
-    uint32_t lane_tiles;               /* split rendering: pixels a lane of the bounce kernel renders one after the other (tile rows
-                                          spread over the segment), which evens out the work of a warp's lanes when chunks are
-                                          short.  0 = chosen by the library from the chunk length and the grid size; 1..64. */
+                                          0 = chosen by the library from the staging limit (spt_cuda_set_staging_limit). */
+    uint32_t strip_rows;               /* split rendering: 8-row tile rows of the segment covered per pair of kernel launches.
+                                          0 = chosen by the library (all of them when the staging limit allows). */
 } SptParams;
 #define SPT_BAND_ROWS 8u
 
@@ -177,11 +176,11 @@ SPT_API int spt_cuda_device_count(SptContext *ctx); /* devices behind this conte
 enum { SPT_PARTITION_AUTO = 0, SPT_PARTITION_SAMPLES = 1, SPT_PARTITION_BANDS = 2 };
 SPT_API int spt_cuda_set_partition(SptContext *ctx, int partition); /* multi-device contexts; AUTO = samples when a call has >= n of them */
 SPT_API void spt_cuda_destroy(SptContext *ctx);
-/* Split rendering stages one 16-byte record per camera sample in device memory, in two buffers that alternate (the
- * camera kernel of chunk k+1 runs on a second stream under the bounce kernel of chunk k).  `bytes` bounds BOTH buffers
- * together, per device; 0 restores the default, SPT_DEFAULT_STAGING_BYTES.  Longer chunks waste fewer lane-iterations
- * (a lane owns its pixel for a whole chunk); an application that owns the GPU may raise the limit.  The library never
- * sizes this from the free device memory. */
+/* Split rendering stages one 16-byte record per camera sample in device memory.  `bytes` bounds the staging per device (two
+ * buffers that alternate); 0 restores the default, SPT_DEFAULT_STAGING_BYTES.  A call that does not fit is cut into strips of
+ * tile rows first (all samples of a strip in one pair of launches: the lanes of a warp finish closer together the more of a
+ * pixel's samples one launch covers) and into sample chunks only below two waves of CTAs per strip; camera kernels and the
+ * bounce kernels of neighbouring strips overlap on auxiliary streams.  The library never sizes this from the free device memory. */
 #define SPT_DEFAULT_STAGING_BYTES (8ull << 30)
 SPT_API int spt_cuda_set_staging_limit(SptContext *ctx, uint64_t bytes);
 /* run on a caller stream (cudaStream_t passed as void*; NULL is the legacy default stream) instead of
@@ -244,7 +243,7 @@ SPT_API const char *spt_cuda_last_error(void);
 SPT_API const char *spt_cuda_version(void);
 
 /* Layout revision of the structs above.  A caller compiled against another revision of this header must not call in
-   (revision 2 appended band_count / band_index to SptParams, revision 3 split_chunk / lane_tiles, SptTiming.primary_ms / secondary_ms,
+   (revision 2 appended band_count / band_index to SptParams, revision 3 split_chunk / strip_rows, SptTiming.primary_ms / secondary_ms,
    SptCounters.warp_iterations): compare with
    SPT_ABI_VERSION once after loading. */
 #define SPT_ABI_VERSION 3u

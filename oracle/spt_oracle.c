@@ -136,12 +136,15 @@ static uint64_t mix64(uint64_t z)
 
 /* Counter-based keying that replaces the per-thread, clock-seeded generator (Random.hpp:88-89):
  * one splitmix stream per (pixel, sample, event).  Event 0 = camera jitter; every scatter
- * (diffuse bounce, reflective, refractive) opens the next event. */
+ * (diffuse bounce, reflective, refractive) opens the next event.  The pixel part is mixed (one splitmix
+ * finaliser per pixel and launch on the GPU); sample and event enter as Weyl increments of the engine's
+ * state -- the engine step itself (state += G; output = finaliser(state), Random.hpp:35-41) is what turns
+ * distinct (pixel, sample, event, step) counters into independent-looking draws, so a second finaliser per
+ * sample would only repeat its work. */
 uint64_t spo_stream_key(uint64_t seed, uint32_t pixel, uint32_t sample)
 {
-    uint64_t k = mix64(seed + SPO_GOLDEN * ((uint64_t)pixel + 1ULL));
-    k = mix64(k ^ (0xD1B54A32D192ED03ULL * ((uint64_t)sample + 1ULL)));
-    return k;
+    uint64_t const k = mix64(seed + SPO_GOLDEN * ((uint64_t)pixel + 1ULL));
+    return k ^ (0xD1B54A32D192ED03ULL * ((uint64_t)sample + 1ULL));
 }
 
 uint64_t spo_event_state(uint64_t key, uint32_t event) { return key + 0xA0761D6478BD642FULL * (uint64_t)event; }

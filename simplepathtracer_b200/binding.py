@@ -146,7 +146,7 @@ class _CParams(C.Structure):
         ("band_count", C.c_uint32),
         ("band_index", C.c_uint32),
         ("split_chunk", C.c_uint32),
-        ("lane_tiles", C.c_uint32),
+        ("strip_rows", C.c_uint32),
     ]
 
 
@@ -294,7 +294,7 @@ class PathTracer:
         self.device = self.devices[0]
         self.scene: Optional[Scene] = None
         self.split_chunk = 0  # SptParams.split_chunk of every call made through this object (0 = as the staging limit allows)
-        self.lane_tiles = 0  # SptParams.lane_tiles (0 = chosen by the library)
+        self.strip_rows = 0  # SptParams.strip_rows (0 = chosen by the library)
 
     def device_count(self) -> int:
         return int(self.L.spt_cuda_device_count(self.h))
@@ -350,7 +350,7 @@ class PathTracer:
 
     def _params(self, width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags, bands=None) -> _CParams:
         count, index = bands if bands else (0, 0)  # (band_count, band_index): interleaved 8-row bands, include/spt_cuda.h
-        return _CParams(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags, count, index, int(self.split_chunk), int(self.lane_tiles))
+        return _CParams(width, height, depth, pass_cap, sample_begin, sample_end, seed, variant, flags, count, index, int(self.split_chunk), int(self.strip_rows))
 
     def render(self, cam, width, height, spp, depth, pass_cap=0, seed=1, seg=None, sample_begin=0, variant=MEGAKERNEL,
                flags=0, rgb8: Optional[np.ndarray] = None, want_accum: bool = False):

@@ -45,15 +45,21 @@ struct SptContext
     cudaDeviceProp prop{};
     cudaStream_t ownStream = nullptr;
     cudaStream_t stream = nullptr;
-    cudaStream_t auxStream = nullptr; // split rendering: the camera kernel of chunk k+1 runs here, under the bounce kernel of chunk k
+    cudaStream_t auxStream = nullptr;  // split rendering: the camera kernels run here, under the bounce kernel of the previous work item
+    cudaStream_t auxStream2 = nullptr; // ... and the bounce kernels of every other strip here, next to the main stream's
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-    cudaEvent_t evFork = nullptr, evPrimary[2] = {nullptr, nullptr}, evSecondary[2] = {nullptr, nullptr};
+    cudaEvent_t evFork = nullptr, evJoin = nullptr, evPrimary[2] = {nullptr, nullptr}, evSecondary[2] = {nullptr, nullptr};
     cudaEvent_t evDone = nullptr; // multi-device: this device's accumulator is complete
     std::vector<cudaEvent_t> evKernel; // split rendering: 4 timing events per chunk (camera begin/end, bounce begin/end)
     uint32_t timedChunks = 0;
     std::mutex lock; // the reference calls its tracers from several host threads (Renderer.hpp:282-290)
 
     uint32_t n = 0;
+    // the device scene: pointers into dSceneArena[sceneArena] (upload_scene)
+    unsigned char *dSceneArena[2] = {nullptr, nullptr};
+    size_t sceneArenaBytes[2] = {0, 0};
+    int sceneArena = 0;
+    std::vector<unsigned char> hostScenePacked;
     float4 *dGeom = nullptr;
     float4 *dShade = nullptr;
     uint8_t *dMat = nullptr;
@@ -69,10 +75,14 @@ struct SptContext
     uint8_t *dRgb = nullptr;
     size_t accumPixels = 0;
     // split rendering: camera-form filter blob (rebuilt when the eye changes) and the first-hit staging buffers
-    spt::FilterPair *dPairsCam = nullptr;
+    spt::FilterPair *dPairsCam = nullptr; // = dCamArena[camArena]: two arenas that take turns, as the scene's
+    unsigned char *dCamArena[2] = {nullptr, nullptr};
+    size_t camArenaBytes[2] = {0, 0};
+    int camArena = 0;
     std::vector<unsigned char> hostBlob; // the general blob, kept to derive the camera form
     std::vector<double> hostGeom;        // cx, cy, cz, r per SLOT in binary64
-    float camEye[3] = {NAN, NAN, NAN};
+    float camKey[16] = {NAN}; // view rows 0..2 + eye the camera records were built for, and the image size
+    uint32_t camW = 0, camH = 0;
     float camEpsT = 0.f;
     float4 *dFirstHits = nullptr;
     size_t firstHitsBytes = 0;
@@ -178,11 +188,65 @@ void build_filter(const SptScene *s, std::vector<unsigned char> &blob, uint32_t 
     amax = round_up_to_float(amaxD);
 }
 
-// Camera form of the blob (spt_filter.cuh, filter_pair_cam): per slot nkc = -(|C - E|^2 - r^2) + S_i + S_ray(E) - 1e-3 in
-// binary64, rounded up; S_ray and epsT exactly as make_filter_ray derives them for an origin at E.
-int ensure_camera_blob(SptContext *c, const float eye[3])
+// Bound on |D(xi) - D(0)| over the camera rays of ONE pixel -- jitter xi in [-1, 1)^2, quirk Q2 -- for any pixel of a
+// width x height image (spt_device.cuh, primary_direction): r(px, py) = px c0 + py c1 + c2 with px = -1 + 2 (x + xi_v) / H,
+// py = -1 + 2 (y + xi_u) / W (swapped divisors, quirk Q1), D = r / |r|.  |r(xi) - r(0)| <= 2 |c0| / H + 2 |c1| / W =: dr, and
+// |a/|a| - b/|b|| <= 2 |a - b| / max(|a|, |b|), so delta = 2 dr / min|r| over the image (the exact minimum of a convex
+// quadratic over the box of (px, py)), plus the float rounding of the two directions.  4 = "every sphere is a candidate".
+double pixel_cone_delta(const SptCamera *cam, uint32_t width, uint32_t height)
 {
-    if (c->dPairsCam && eye[0] == c->camEye[0] && eye[1] == c->camEye[1] && eye[2] == c->camEye[2])
+    double const c0[3] = {cam->view[0], cam->view[4], cam->view[8]}, c1[3] = {cam->view[1], cam->view[5], cam->view[9]},
+                 c2[3] = {cam->view[2], cam->view[6], cam->view[10]};
+    auto dot = [](const double *a, const double *b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; };
+    double const W = width, H = height;
+    double const lo[2] = {-1.0 - 2.0 / H - 1e-6, -1.0 - 2.0 / W - 1e-6}, hi[2] = {-1.0 + 2.0 * W / H + 1e-6, -1.0 + 2.0 * H / W + 1e-6};
+    // f(px, py) = |px c0 + py c1 + c2|^2 = a px^2 + 2 b px py + c py^2 + 2 d px + 2 e py + g
+    double const a = dot(c0, c0), b = dot(c0, c1), c = dot(c1, c1), d = dot(c0, c2), e = dot(c1, c2), g = dot(c2, c2);
+    auto f = [&](double px, double py) { return a * px * px + 2 * b * px * py + c * py * py + 2 * d * px + 2 * e * py + g; };
+    auto clamp = [](double v, double l, double h) { return v < l ? l : (v > h ? h : v); };
+    double best = std::min(std::min(f(lo[0], lo[1]), f(lo[0], hi[1])), std::min(f(hi[0], lo[1]), f(hi[0], hi[1])));
+    double const det = a * c - b * b;
+    if (det > 1e-12 * (a * c + 1e-300))
+    {
+        double const px = (-d * c + e * b) / det, py = (-e * a + d * b) / det; // stationary point
+        if (px >= lo[0] && px <= hi[0] && py >= lo[1] && py <= hi[1])
+            best = std::min(best, f(px, py));
+    }
+    for (int k = 0; k < 2; ++k) // the four edges: 1-D minimisers, clamped
+    {
+        double const pxe = k ? hi[0] : lo[0], pye = k ? hi[1] : lo[1];
+        if (c > 0)
+            best = std::min(best, f(pxe, clamp(-(b * pxe + e) / c, lo[1], hi[1])));
+        if (a > 0)
+            best = std::min(best, f(clamp(-(b * pye + d) / a, lo[0], hi[0]), pye));
+    }
+    double const dr = 2.0 * std::sqrt(a) / H + 2.0 * std::sqrt(c) / W;
+    if (!(best > 1e-12) || !std::isfinite(best) || !std::isfinite(dr))
+        return 4.0;
+    double const rmin = std::sqrt(best) * 0.999;
+    if (dr >= 0.25 * rmin)
+        return 4.0;
+    return 2.0 * dr / rmin * 1.01 + 1e-6;
+}
+
+// Camera records of split rendering (spt_filter.cuh, filter_pair_cam: v = tC^2 + nkc with the tC chain of the general form).
+// They serve TWO uses in primary_hits_*: once per pixel and launch with the pixel's CENTRAL ray Dc (no jitter), to collect
+// the spheres that ANY camera sample of that pixel can hit, and -- for pixels whose list overflows -- per sample as before.
+// Per slot, with L = C - E, delta = pixel_cone_delta (0 would give the plain camera form), S = S_i + S_ray(E) the slack of
+// the general form (u = 2^-24: covers the exact sequence's and the chain's rounding, DESIGN.md "pre-filter bound"):
+//     exact test passes for a sample's ray D   =>   dist(C, line(E, D))^2 < r^2 + 2 S          (2 S: |D| is 1 within 2^-22)
+//     dist(C, line(E, Dc)) <= dist(C, line(E, D)) + |L| |D - Dc| < sqrt(r^2 + 2 S) + |L| delta =: R
+//     nkc = R^2 - |L|^2 + 2 S   (binary64, rounded up)   =>   v(Dc) = tC(Dc)^2 + nkc >= 0 in the chain's arithmetic.
+// S is evaluated with R in place of r.  Conservative for the per-sample use a fortiori (R >= r).
+int ensure_camera_blob(SptContext *c, const SptCamera *cam, uint32_t width, uint32_t height)
+{
+    const float *eye = cam->eye;
+    float key[16];
+    for (int k = 0; k < 12; ++k)
+        key[k] = cam->view[k];
+    key[12] = eye[0], key[13] = eye[1], key[14] = eye[2];
+    key[15] = 0.f;
+    if (c->dPairsCam && c->camW == width && c->camH == height && memcmp(key, c->camKey, sizeof(key)) == 0)
         return SPT_OK;
     uint32_t const nSlots = c->filter.nSlots;
     std::vector<unsigned char> blob = c->hostBlob;
@@ -196,6 +260,7 @@ int ensure_camera_blob(SptContext *c, const float eye[3])
         epsT = m * 9.5367431640625e-7 * 1.0000002;  // 2^-20 (Amax + B), not below the device's rounded-up value
         sRay += m * m * 3.8146973e-6 * 1.000001;    // + 2^-18 (Amax + B)^2
     }
+    double const delta = pixel_cone_delta(cam, width, height);
     for (uint32_t k = 0; k < nSlots; ++k)
     {
         double const cx = c->hostGeom[4 * k], cy = c->hostGeom[4 * k + 1], cz = c->hostGeom[4 * k + 2], r = c->hostGeom[4 * k + 3];
@@ -203,18 +268,34 @@ int ensure_camera_blob(SptContext *c, const float eye[3])
             continue;
         double const a2 = cx * cx + cy * cy + cz * cz;
         double const dx = cx - ex, dy = cy - ey, dz = cz - ez;
-        double const slack = spt::kSlackU * (a2 + r * r);
-        pairs[k / 2].nk[k & 1] = round_up_to_float(-(dx * dx + dy * dy + dz * dz - r * r) + slack + sRay - double(1e-3f));
+        double const l2 = dx * dx + dy * dy + dz * dz, l = std::sqrt(l2);
+        double R = r, S = 0.0;
+        for (int it = 0; it < 2; ++it) // the slack with the fattened radius in place of r
+        {
+            S = spt::kSlackU * (a2 + R * R) + sRay;
+            R = std::sqrt(r * r + 2.0 * S) + l * delta;
+        }
+        pairs[k / 2].nk[k & 1] = round_up_to_float((R * R - l2 + 2.0 * S) * (1.0 + 1e-12) + 1e-30);
     }
-    if (!c->dPairsCam)
-        SPT_CUDA_CHECK(cudaMalloc(&c->dPairsCam, blob.size() + 16));
-    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream)); // an earlier launch may still read the previous camera's records
-    SPT_CUDA_CHECK(cudaStreamSynchronize(c->auxStream));
+    // into the arena that is not in use (earlier launches may still read the other one), ordered by the stream
+    int const next = c->camArena ^ 1;
+    if (blob.size() + 16 > c->camArenaBytes[next])
+    {
+        SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        SPT_CUDA_CHECK(cudaStreamSynchronize(c->auxStream));
+        unsigned char *fresh = nullptr;
+        SPT_CUDA_CHECK(cudaMalloc(&fresh, blob.size() + 16));
+        cudaFree(c->dCamArena[next]);
+        c->dCamArena[next] = fresh;
+        c->camArenaBytes[next] = blob.size() + 16;
+    }
     if (!blob.empty())
-        SPT_CUDA_CHECK(cudaMemcpy(c->dPairsCam, blob.data(), blob.size(), cudaMemcpyHostToDevice));
-    c->camEye[0] = eye[0];
-    c->camEye[1] = eye[1];
-    c->camEye[2] = eye[2];
+        SPT_CUDA_CHECK(cudaMemcpyAsync(c->dCamArena[next], blob.data(), blob.size(), cudaMemcpyHostToDevice, c->stream));
+    c->camArena = next;
+    c->dPairsCam = reinterpret_cast<spt::FilterPair *>(c->dCamArena[next]);
+    memcpy(c->camKey, key, sizeof(key));
+    c->camW = width;
+    c->camH = height;
     c->camEpsT = round_up_to_float(epsT);
     return SPT_OK;
 }
@@ -256,8 +337,7 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
         return fail(SPT_ERR_NO_SCENE, "spt_cuda_set_scene has not been called");
     if (prm->variant != SPT_VARIANT_MEGAKERNEL && prm->variant != SPT_VARIANT_WAVEFRONT)
         return fail(SPT_ERR_INVALID, "unknown variant");
-    if (prm->lane_tiles > 64u)
-        return fail(SPT_ERR_INVALID, "SptParams.lane_tiles must be 0 (automatic) or 1..64");
+
     c->timing.trace_ms = 0.f;
     c->timing.launches = 0;
     c->timing.primary_ms = c->timing.secondary_ms = 0.f;
@@ -359,35 +439,54 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             // split rendering (spt_split.cuh): per chunk of samples, the primary kernel (camera form of the filter, all lanes
             // in step) writes the first-hit index of every camera sample, then the secondary kernel runs the bounce loop
             // on secondary rays only.  The per-pixel running sums continue across chunks.
-            int rc = ensure_camera_blob(c, cam->eye);
+            int rc = ensure_camera_blob(c, cam, prm->width, prm->height);
             if (rc)
                 return rc;
             p.filterCam = c->filter;
             p.filterCam.pairs = c->dPairsCam;
             p.filterCam.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairsCam + c->filter.nSlots / 2);
             p.filterCam.epsTCam = c->camEpsT;
-            size_t const pixels = size_t(segW) * std::min<size_t>(segH, size_t(myBands) * SPT_BAND_ROWS); // rows the launch covers
-            // Staging.  A lane owns its pixel for a whole chunk of samples and the warp waits for its slowest lane, so longer
-            // chunks waste fewer lane-iterations -- but the budget is the caller's (spt_cuda_set_staging_limit, 8 GiB unless
-            // raised), never a share of whatever the device has free.  When the sample range needs several chunks the budget
-            // is cut into TWO buffers that alternate: the camera kernel of chunk k+1 runs on the auxiliary stream while the
-            // bounce kernel of chunk k drains (its last CTAs leave SMs idle that the camera kernel's CTAs take).
-            size_t const recBytes = pixels * sizeof(float4); // one sample of every pixel of the launch
-            size_t const pad = 256;                          // the consumer prefetches four records past the one it reads
+            // Staging and work items.  The camera kernel stages one 16-byte record per pixel and sample; the budget is the caller's
+            // (spt_cuda_set_staging_limit, 8 GiB unless raised), never a share of whatever the device has free.  A lane of the bounce
+            // kernel owns its pixel for a whole launch and the warp waits for its slowest lane, so what matters is SAMPLES PER
+            // LAUNCH: the more of a pixel's samples one launch covers, the closer the lanes of a warp finish together (share of
+            // lanes holding a ray in the closest-hit trips on config 3: 88.7 % at 32 samples per launch, 94.5 % at 256).  When the
+            // whole call does not fit the budget it is therefore cut along the IMAGE first -- strips of tile rows, all samples of
+            // a strip in one launch while a strip keeps >= 2 waves of CTAs -- and only then along the samples.  The budget holds
+            // two buffers that alternate.  Strips touch disjoint pixels, so the bounce kernels of consecutive strips run
+            // concurrently (main and second auxiliary stream) and the tail of one fills with CTAs of the next; chunks of the same
+            // strip stay in stream order (the per-pixel running sums continue).  Camera kernels run on the first auxiliary stream.
             uint32_t const total = prm->sample_end - prm->sample_begin;
-            size_t const limit = std::max<size_t>(size_t(c->stagingLimit), 2 * (recBytes + pad));
-            uint32_t chunk = total;
+            size_t const rowBytes = size_t(segW) * SPT_BAND_ROWS * sizeof(float4); // one sample of every pixel of one tile row
+            size_t const pad = 256;                                                // the consumer prefetches four records past the one it reads
+            dim3 const sGridFull = streamed ? grid : dim3((segW + spt::SplitShape::kTileW - 1) / spt::SplitShape::kTileW, myBands);
+            uint32_t stripRows = myBands, chunk = total;
             if (prm->split_chunk)
                 chunk = std::min(chunk, prm->split_chunk);
-            if (size_t(chunk) * recBytes + pad > limit)
-                chunk = uint32_t(std::max<size_t>(1, (limit / 2 - pad) / recBytes));
-            uint32_t const nChunks = (total + chunk - 1) / chunk;
-            uint32_t const nBuffers = nChunks > 1 ? 2u : 1u;
-            size_t const bufBytes = (size_t(chunk) * recBytes + pad + 255) & ~size_t(255);
+            bool const fitsWhole = !prm->strip_rows && size_t(chunk) * myBands * rowBytes + pad <= size_t(c->stagingLimit);
+            if (prm->strip_rows)
+                stripRows = std::min(myBands, prm->strip_rows);
+            else if (!fitsWhole)
+            {
+                size_t const half = size_t(c->stagingLimit) / 2 > pad ? size_t(c->stagingLimit) / 2 - pad : 0;
+                uint64_t const slots = uint64_t(c->prop.multiProcessorCount) * (streamed ? 4u : 8u);
+                uint32_t const minStrip = std::min<uint32_t>(myBands, uint32_t((2 * slots + sGridFull.x - 1) / sGridFull.x));
+                stripRows = uint32_t(std::min<size_t>(myBands, half / (size_t(chunk) * rowBytes)));
+                if (stripRows < minStrip)
+                {
+                    stripRows = std::max(1u, minStrip);
+                    chunk = uint32_t(std::max<size_t>(1, std::min<size_t>(chunk, half / (size_t(stripRows) * rowBytes))));
+                }
+            }
+            uint32_t const nStrips = (myBands + stripRows - 1) / stripRows, nChunks = (total + chunk - 1) / chunk;
+            uint32_t const nItems = nStrips * nChunks;
+            uint32_t const nBuffers = nItems > 1 ? 2u : 1u;
+            size_t const bufBytes = (size_t(chunk) * stripRows * rowBytes + pad + 255) & ~size_t(255);
             if (bufBytes * nBuffers > c->firstHitsBytes)
             {
                 SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
                 SPT_CUDA_CHECK(cudaStreamSynchronize(c->auxStream));
+                SPT_CUDA_CHECK(cudaStreamSynchronize(c->auxStream2));
                 cudaFree(c->dFirstHits);
                 c->dFirstHits = nullptr;
                 c->firstHitsBytes = 0;
@@ -403,65 +502,64 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             void (*primary)(const spt::TraceParams) = streamed ? spt::primary_hits_streamed : spt::primary_hits_kernel<2, spt::SplitShape>;
             void (*secondary)(const spt::TraceParams) = streamed ? spt::trace_secondary_streamed : spt::trace_secondary<2, spt::SplitShape>;
             // the resident kernels run smaller CTAs than the rest (spt_split.cuh, SplitShape)
-            dim3 const sGrid = streamed ? grid : dim3((segW + spt::SplitShape::kTileW - 1) / spt::SplitShape::kTileW, myBands);
             dim3 const sBlock(streamed ? spt::kBlockThreads : spt::SplitShape::kThreads);
             SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
             SPT_CUDA_CHECK(cudaFuncSetAttribute(secondary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-            // Pixels per lane of the bounce kernel (spt_split.cuh, secondary_bounce_loop).  A warp leaves when its slowest lane
-            // does; with short chunks the lanes' totals differ a lot (few samples to average over), so each lane renders
-            // several pixels from tile rows far apart: about 256 samples per lane, as long as the grid keeps >= 8 waves.
-            uint32_t laneTiles = prm->lane_tiles;
-            if (laneTiles == 0)
-            {
-                laneTiles = std::max(1u, std::min(64u, 256u / std::max(1u, chunk)));
-                uint64_t const slots = uint64_t(c->prop.multiProcessorCount) * (streamed ? 4u : 8u);
-                while (laneTiles > 1 && uint64_t(sGrid.x) * ((myBands + laneTiles - 1) / laneTiles) < 8 * slots)
-                    laneTiles /= 2;
-            }
-            laneTiles = std::min(laneTiles, std::max(1u, myBands));
-            p.tileRows = myBands;
-            dim3 const sGrid2(sGrid.x, (myBands + laneTiles - 1) / laneTiles);
-            // camera kernels on the auxiliary stream (after everything queued on the main stream so far), bounce kernels on
-            // the main stream: P(k) needs buffer k % 2 free (S(k-2) done), S(k) needs P(k); S(k) after S(k-1) by stream order
-            // (the per-pixel running sums continue across chunks).  Every camera kernel is waited for by a bounce kernel on
-            // the main stream, so the main stream alone orders the caller's later work.
+            // P(i) needs buffer i % 2 free (S(i-2) done), S(i) needs P(i); everything the auxiliary streams do is waited for on
+            // the main stream before this function returns to its caller's stream order.
             bool const overlap = nBuffers > 1 && !(prm->flags & SPT_FLAG_SERIAL_CHUNKS);
             cudaStream_t const sp = overlap ? c->auxStream : c->stream;
-            while (c->evKernel.size() < size_t(nChunks) * 4)
+            cudaStream_t const sAlt = (overlap && nStrips > 1) ? c->auxStream2 : c->stream;
+            while (c->evKernel.size() < size_t(nItems) * 4)
             {
                 cudaEvent_t e = nullptr;
                 SPT_CUDA_CHECK(cudaEventCreate(&e));
                 c->evKernel.push_back(e);
             }
-            c->timedChunks = nChunks;
+            c->timedChunks = nItems;
             if (overlap)
             {
                 SPT_CUDA_CHECK(cudaEventRecord(c->evFork, c->stream));
                 SPT_CUDA_CHECK(cudaStreamWaitEvent(sp, c->evFork, 0));
+                if (sAlt != c->stream)
+                    SPT_CUDA_CHECK(cudaStreamWaitEvent(sAlt, c->evFork, 0));
             }
-            uint32_t k = 0;
-            for (uint32_t s0 = prm->sample_begin; s0 < prm->sample_end; s0 += chunk, ++k)
+            uint32_t i = 0;
+            for (uint32_t strip = 0; strip < nStrips; ++strip)
             {
-                uint32_t const b = k % nBuffers;
-                p.sampleBegin = s0;
-                p.sampleEnd = std::min(prm->sample_end, s0 + chunk);
-                p.firstHits = reinterpret_cast<float4 *>(reinterpret_cast<unsigned char *>(c->dFirstHits) + size_t(b) * bufBytes);
-                if (overlap && k >= 2)
-                    SPT_CUDA_CHECK(cudaStreamWaitEvent(sp, c->evSecondary[b], 0));
-                SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * k + 0], sp));
-                primary<<<sGrid, sBlock, smem, sp>>>(p);
-                SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * k + 1], sp));
-                if (overlap)
+                uint32_t const r0 = strip * stripRows, r1 = std::min(myBands, r0 + stripRows);
+                dim3 const sGrid(sGridFull.x, r1 - r0);
+                cudaStream_t const ss = (strip & 1u) ? sAlt : c->stream;
+                p.tileRowOffset = r0;
+                for (uint32_t s0 = prm->sample_begin; s0 < prm->sample_end; s0 += chunk, ++i)
                 {
-                    SPT_CUDA_CHECK(cudaEventRecord(c->evPrimary[b], sp));
-                    SPT_CUDA_CHECK(cudaStreamWaitEvent(c->stream, c->evPrimary[b], 0));
+                    uint32_t const b = i % nBuffers;
+                    p.sampleBegin = s0;
+                    p.sampleEnd = std::min(prm->sample_end, s0 + chunk);
+                    p.firstHits = reinterpret_cast<float4 *>(reinterpret_cast<unsigned char *>(c->dFirstHits) + size_t(b) * bufBytes);
+                    if (overlap && i >= 2)
+                        SPT_CUDA_CHECK(cudaStreamWaitEvent(sp, c->evSecondary[b], 0));
+                    SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * i + 0], sp));
+                    primary<<<sGrid, sBlock, smem, sp>>>(p);
+                    SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * i + 1], sp));
+                    if (overlap)
+                    {
+                        SPT_CUDA_CHECK(cudaEventRecord(c->evPrimary[b], sp));
+                        SPT_CUDA_CHECK(cudaStreamWaitEvent(ss, c->evPrimary[b], 0));
+                    }
+                    SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * i + 2], ss));
+                    secondary<<<sGrid, sBlock, smem, ss>>>(p);
+                    SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * i + 3], ss));
+                    if (overlap)
+                        SPT_CUDA_CHECK(cudaEventRecord(c->evSecondary[b], ss));
+                    c->timing.launches += 2;
                 }
-                SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * k + 2], c->stream));
-                secondary<<<sGrid2, sBlock, smem, c->stream>>>(p);
-                SPT_CUDA_CHECK(cudaEventRecord(c->evKernel[4 * k + 3], c->stream));
-                if (overlap)
-                    SPT_CUDA_CHECK(cudaEventRecord(c->evSecondary[b], c->stream));
-                c->timing.launches += 2;
+            }
+            p.tileRowOffset = 0;
+            if (sAlt != c->stream)
+            {
+                SPT_CUDA_CHECK(cudaEventRecord(c->evJoin, sAlt));
+                SPT_CUDA_CHECK(cudaStreamWaitEvent(c->stream, c->evJoin, 0));
             }
             c->timing.launches -= 1; // the common tail below counts one
         }
@@ -517,9 +615,11 @@ int create_one(SptContext **out, int device)
         ce = cudaStreamCreateWithFlags(&c->ownStream, cudaStreamNonBlocking);
     if (ce == cudaSuccess)
         ce = cudaStreamCreateWithFlags(&c->auxStream, cudaStreamNonBlocking);
+    if (ce == cudaSuccess)
+        ce = cudaStreamCreateWithFlags(&c->auxStream2, cudaStreamNonBlocking);
     for (int i = 0; i < 4 && ce == cudaSuccess; ++i)
         ce = cudaEventCreate(&c->ev[i]);
-    cudaEvent_t *const sync[] = {&c->evFork, &c->evPrimary[0], &c->evPrimary[1], &c->evSecondary[0], &c->evSecondary[1], &c->evDone};
+    cudaEvent_t *const sync[] = {&c->evFork, &c->evJoin, &c->evPrimary[0], &c->evPrimary[1], &c->evSecondary[0], &c->evSecondary[1], &c->evDone};
     for (cudaEvent_t *e : sync)
         if (ce == cudaSuccess)
             ce = cudaEventCreateWithFlags(e, cudaEventDisableTiming);
@@ -546,31 +646,31 @@ void destroy_one(SptContext *c)
     cudaStreamSynchronize(c->stream);
     if (c->auxStream)
         cudaStreamSynchronize(c->auxStream);
-    cudaFree(c->dGeom);
-    cudaFree(c->dShade);
-    cudaFree(c->dMat);
-    cudaFree(c->dPairs);
-    cudaFree(c->dBigIdx);
+    cudaFree(c->dSceneArena[0]);
+    cudaFree(c->dSceneArena[1]);
     cudaFree(c->dCounters);
     cudaFree(c->dAccum);
     cudaFree(c->dRgb);
     cudaFree(c->dProbe);
     cudaFree(c->dProgAccum);
     cudaFree(c->dProgRgb);
-    cudaFree(c->dPairsCam);
+    cudaFree(c->dCamArena[0]);
+    cudaFree(c->dCamArena[1]);
     cudaFree(c->dFirstHits);
     for (auto &e : c->ev)
         if (e)
             cudaEventDestroy(e);
     for (cudaEvent_t e : c->evKernel)
         cudaEventDestroy(e);
-    for (cudaEvent_t e : {c->evFork, c->evPrimary[0], c->evPrimary[1], c->evSecondary[0], c->evSecondary[1], c->evDone})
+    for (cudaEvent_t e : {c->evFork, c->evJoin, c->evPrimary[0], c->evPrimary[1], c->evSecondary[0], c->evSecondary[1], c->evDone})
         if (e)
             cudaEventDestroy(e);
     if (c->ownStream)
         cudaStreamDestroy(c->ownStream);
     if (c->auxStream)
         cudaStreamDestroy(c->auxStream);
+    if (c->auxStream2)
+        cudaStreamDestroy(c->auxStream2);
     delete c;
 }
 
@@ -587,65 +687,62 @@ struct HostScene
     float amax = 0.f;
 };
 
-// Build the new device scene completely, THEN retire the old one: a failed allocation leaves the context as it was.
+// The scene of a device lives in ONE allocation, packed [geometry | shading | materials | pre-filter blob | big-sphere list],
+// and every context keeps TWO such arenas that take turns: a new scene is copied (one asynchronous copy on the context's
+// stream) into the arena that is NOT in use, then the pointers switch.  Launches already queued keep reading the old arena;
+// in steady state (re-uploading scenes of the same size, as an end-to-end render loop does) nothing is allocated or freed;
+// and a failed allocation or copy leaves the context exactly as it was.
 int upload_scene(SptContext *c, const HostScene &hs)
 {
     SPT_CUDA_CHECK(cudaSetDevice(c->device));
-    float4 *dGeom = nullptr, *dShade = nullptr;
-    uint8_t *dMat = nullptr;
-    spt::FilterPair *dPairs = nullptr;
-    uint32_t *dBigIdx = nullptr;
-    cudaError_t ce = cudaMalloc(&dPairs, hs.blob.size() + 16);
-    if (ce == cudaSuccess)
-        ce = cudaMalloc(&dBigIdx, (hs.big.size() + 1) * sizeof(uint32_t));
-    if (ce == cudaSuccess)
-        ce = cudaMalloc(&dGeom, hs.n * sizeof(float4));
-    if (ce == cudaSuccess)
-        ce = cudaMalloc(&dShade, hs.n * sizeof(float4));
-    if (ce == cudaSuccess)
-        ce = cudaMalloc(&dMat, hs.n);
-    if (ce == cudaSuccess && !hs.blob.empty())
-        ce = cudaMemcpy(dPairs, hs.blob.data(), hs.blob.size(), cudaMemcpyHostToDevice);
-    if (ce == cudaSuccess && !hs.big.empty())
-        ce = cudaMemcpy(dBigIdx, hs.big.data(), hs.big.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
-    if (ce == cudaSuccess)
-        ce = cudaMemcpy(dGeom, hs.geom.data(), hs.n * sizeof(float4), cudaMemcpyHostToDevice);
-    if (ce == cudaSuccess)
-        ce = cudaMemcpy(dShade, hs.shade.data(), hs.n * sizeof(float4), cudaMemcpyHostToDevice);
-    if (ce == cudaSuccess)
-        ce = cudaMemcpy(dMat, hs.materials, hs.n, cudaMemcpyHostToDevice);
-    if (ce == cudaSuccess)
-        ce = cudaStreamSynchronize(c->stream); // launches that still read the old scene
-    if (ce == cudaSuccess)
-        ce = cudaStreamSynchronize(c->auxStream);
-    if (ce != cudaSuccess)
+    auto align = [](size_t v) { return (v + 255) & ~size_t(255); };
+    size_t const oGeom = 0, oShade = align(oGeom + hs.n * sizeof(float4)), oMat = align(oShade + hs.n * sizeof(float4)),
+                 oPairs = align(oMat + hs.n), oBig = align(oPairs + hs.blob.size() + 16), total = align(oBig + (hs.big.size() + 1) * sizeof(uint32_t));
+    int const next = c->sceneArena ^ 1;
+    if (total > c->sceneArenaBytes[next])
     {
-        cudaFree(dPairs);
-        cudaFree(dBigIdx);
-        cudaFree(dGeom);
-        cudaFree(dShade);
-        cudaFree(dMat);
-        return fail(SPT_ERR_CUDA, "spt_cuda_set_scene: upload failed, the previous scene is kept", ce);
+        // the arena about to be replaced may still be read by launches queued before the PREVIOUS upload
+        SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        SPT_CUDA_CHECK(cudaStreamSynchronize(c->auxStream));
+        unsigned char *fresh = nullptr;
+        cudaError_t const ce = cudaMalloc(&fresh, total);
+        if (ce != cudaSuccess)
+        {
+            (void)cudaGetLastError();
+            return fail(SPT_ERR_CUDA, "spt_cuda_set_scene: allocation failed, the previous scene is kept", ce);
+        }
+        cudaFree(c->dSceneArena[next]);
+        c->dSceneArena[next] = fresh;
+        c->sceneArenaBytes[next] = total;
     }
-    cudaFree(c->dGeom);
-    cudaFree(c->dShade);
-    cudaFree(c->dMat);
-    cudaFree(c->dPairs);
-    cudaFree(c->dBigIdx);
-    cudaFree(c->dPairsCam); // sized by the scene; ensure_camera_blob rebuilds it
-    c->dGeom = dGeom;
-    c->dShade = dShade;
-    c->dMat = dMat;
-    c->dPairs = dPairs;
-    c->dBigIdx = dBigIdx;
-    c->dPairsCam = nullptr;
-    c->camEye[0] = c->camEye[1] = c->camEye[2] = NAN;
+    // pack on the host, one copy
+    c->hostScenePacked.assign(total, 0);
+    unsigned char *h = c->hostScenePacked.data();
+    memcpy(h + oGeom, hs.geom.data(), hs.n * sizeof(float4));
+    memcpy(h + oShade, hs.shade.data(), hs.n * sizeof(float4));
+    memcpy(h + oMat, hs.materials, hs.n);
+    if (!hs.blob.empty())
+        memcpy(h + oPairs, hs.blob.data(), hs.blob.size());
+    if (!hs.big.empty())
+        memcpy(h + oBig, hs.big.data(), hs.big.size() * sizeof(uint32_t));
+    unsigned char *d = c->dSceneArena[next];
+    // (pageable source: the call returns once the bytes sit in the driver's staging memory, so `h` may be reused at once)
+    cudaError_t const ce = cudaMemcpyAsync(d, h, total, cudaMemcpyHostToDevice, c->stream);
+    if (ce != cudaSuccess)
+        return fail(SPT_ERR_CUDA, "spt_cuda_set_scene: upload failed, the previous scene is kept", ce);
+    c->sceneArena = next;
+    c->dGeom = reinterpret_cast<float4 *>(d + oGeom);
+    c->dShade = reinterpret_cast<float4 *>(d + oShade);
+    c->dMat = d + oMat;
+    c->dPairs = reinterpret_cast<spt::FilterPair *>(d + oPairs);
+    c->dBigIdx = reinterpret_cast<uint32_t *>(d + oBig);
+    c->camKey[0] = NAN; // the camera records are derived from the scene: rebuilt by the next split render
     c->hostBlob = hs.blob;
     c->hostGeom = hs.slotGeom;
-    c->filter.pairs = dPairs;
+    c->filter.pairs = c->dPairs;
     c->filter.nSlots = hs.nSlots;
-    c->filter.slotIdx = reinterpret_cast<const uint32_t *>(dPairs + hs.nSlots / 2);
-    c->filter.bigIdx = dBigIdx;
+    c->filter.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairs + hs.nSlots / 2);
+    c->filter.bigIdx = c->dBigIdx;
     c->filter.nBig = uint32_t(hs.big.size());
     c->filter.amax = hs.amax;
     {

@@ -446,6 +446,73 @@ __device__ __forceinline__ void filter_span_cam2(const FilterPair *rec, const ui
     }
 }
 
+// ---- pixel cone: the spheres ANY camera sample of a pixel can hit, collected once per pixel and launch -----------------
+// The camera records carry a radius fattened by |C - E| * delta, delta >= |D - Dc| for every jittered ray D of a pixel with
+// central ray Dc (host: pixel_cone_delta / ensure_camera_blob in spt_cuda.cu, where the bound is derived): a sphere that
+// passes the reference's exact test for some sample of the pixel passes the camera-form test for Dc.  cone_collect runs that
+// test over a span of slots for Dc and appends the sphere indices of the survivors to the lane's list -- a column of a
+// shared-memory array, entry k of thread t at list[k * THREADS + t] -- counting past `cap` without storing (overflow: the
+// caller falls back to filtering per sample).  Once per pixel and launch, so nothing here is hot; the per-sample work that
+// remains is the exact sequence on the listed spheres (cone_closest_hit), which alone decides the hit.
+template <int THREADS>
+__device__ __forceinline__ void cone_collect(const FilterPair *rec, const uint32_t *slotIdx, uint32_t spanSlots, const FilterRay &fr, uint32_t n,
+                                             bool live, uint16_t *list, uint32_t cap, uint32_t &count)
+{
+    uint32_t const nWords = (spanSlots + kWordSpheres - 1u) / kWordSpheres;
+#pragma unroll 1
+    for (uint32_t w = 0; w < nWords; ++w)
+    {
+        uint32_t const slots = min(kWordSpheres, spanSlots - w * kWordSpheres); // a multiple of kQuadSpheres
+        uint32_t mask = 0xFFFFFFFFu;
+#pragma unroll 1
+        for (uint32_t q = 0; q < slots / kQuadSpheres; ++q)
+        {
+#pragma unroll
+            for (uint32_t pp = 0; pp < kQuadSpheres / 2; ++pp)
+                filter_pair_cam(rec + pp, fr, mask);
+            rec += kQuadSpheres / 2;
+        }
+        uint32_t const sh = kWordSpheres - slots; // missing slots of a partial word: fail bits
+        if (sh)
+            mask = (mask << sh) | ((1u << sh) - 1u);
+        uint32_t cand = live ? ~mask : 0u;
+        while (cand)
+        {
+            uint32_t const j = __clz(cand);
+            cand &= ~(0x80000000u >> j);
+            uint32_t const i = slotIdx[w * kWordSpheres + j];
+            if (i < n) // padding records can only show up for NaN rays
+            {
+                if (count < cap)
+                    list[count * THREADS + threadIdx.x] = uint16_t(i);
+                ++count;
+            }
+        }
+    }
+}
+
+// FindClosestIntersectionSphere (Collision.hpp:87-109) for a camera ray of a pixel whose candidate list is complete: the big
+// spheres and the listed ones through the exact sequence.  Returns what closest_hit_strict returns.
+template <int THREADS, typename GeomPtr>
+__device__ __forceinline__ uint32_t cone_closest_hit(const FilterScene &fs, GeomPtr geom, uint32_t n, V3 dir, V3 org, const uint16_t *list,
+                                                     uint32_t count, uint32_t &exactEvals, bool live)
+{
+    uint32_t minIndex = n;
+    float minDistanceSq = FLT_MAX;
+    float const od = vdot(org, dir);
+    exact_big_spheres(fs, geom, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
+    if (live)
+    {
+        for (uint32_t k = 0; k < count; ++k)
+        {
+            uint32_t const i = list[k * THREADS + threadIdx.x];
+            exact_sphere<false>(geom[i], i, dir, org, od, minIndex, minDistanceSq);
+        }
+        exactEvals += count;
+    }
+    return minIndex;
+}
+
 // the same for a camera ray (org = the eye the records in `fs` were specialised for)
 template <typename GeomPtr>
 __device__ __forceinline__ uint32_t closest_hit_camera(const FilterScene &fs, GeomPtr geom, uint32_t n, V3 dir, V3 org,

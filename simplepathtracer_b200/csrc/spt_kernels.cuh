@@ -63,9 +63,7 @@ struct TraceParams
     // [(y - yBegin) * segW + (x - xBegin)][sample - sampleBegin]
     float4 *firstHits;
     FilterScene filterCam; // pre-filter records specialised for the eye (camera form)
-    // bounce kernels of split rendering: every lane walks the tile rows blockIdx.y, blockIdx.y + gridDim.y, ... < tileRows one
-    // pixel after the other (tileRows = tile rows the launch covers; gridDim.y = ceil(tileRows / tiles per lane))
-    uint32_t tileRows;
+    uint32_t tileRowOffset; // split rendering launches a strip of tile rows at a time: blockIdx.y counts from this row of the call
 };
 
 constexpr uint32_t kMissIndex = 0xFFFFFFFFu;
@@ -245,6 +243,7 @@ struct ShellSlots
 {
     unsigned long long st[32];
     uint32_t base[32];
+    uint32_t trips; // bounce kernel: closest-hit trips of this warp (SptCounters.warp_iterations), kept HERE, not in a register
 };
 
 #ifndef SPT_SHELL_LOCAL
@@ -482,7 +481,7 @@ __device__ __forceinline__ void lane_pixel_at(const TraceParams &p, uint32_t til
 template <typename S = DefaultShape>
 __device__ __forceinline__ void lane_pixel(const TraceParams &p, uint32_t &x, uint32_t &y, bool &inside)
 {
-    lane_pixel_at<S>(p, blockIdx.y, x, y, inside);
+    lane_pixel_at<S>(p, blockIdx.y + p.tileRowOffset, x, y, inside);
 }
 // row of this lane among the rows the LAUNCH covers (== y - yBegin unless the call renders interleaved bands)
 template <typename S = DefaultShape>

@@ -174,6 +174,38 @@ __device__ __forceinline__ void streamed_closest_hit_cam2(const FilterScene &fs,
     R.seq += nChunks;
 }
 
+// cone_collect (spt_filter.cuh) over the streamed list: ONE pass of the whole blob through the ring per launch, every warp
+// appending the survivors of each chunk to its lanes' lists.  Same calling rules as streamed_closest_hit.
+template <int THREADS>
+__device__ __forceinline__ void streamed_cone_collect(const FilterScene &fs, uint32_t n, V3 dir, V3 org, StreamRing &R, bool live, bool warpLive,
+                                                      uint16_t *list, uint32_t cap, uint32_t &count)
+{
+    constexpr uint32_t kAhead = kStages - 1u;
+    uint32_t const nChunks = (fs.nSlots + kChunkSlots - 1u) / kChunkSlots;
+    if (threadIdx.x == 0)
+        for (uint32_t c = 0; c < kAhead && c < nChunks; ++c)
+            stream_produce(fs, R.ring, R.fullBar, R.emptyBar, R.seq + c, c);
+    FilterRay const fr = make_filter_ray_cam(dir, vdot(org, dir), fs.epsTCam);
+    for (uint32_t c = 0; c < nChunks; ++c)
+    {
+        if (threadIdx.x == 0 && c + kAhead < nChunks)
+            stream_produce(fs, R.ring, R.fullBar, R.emptyBar, R.seq + c + kAhead, c + kAhead);
+        uint32_t const buf = (R.seq + c) % kStages, use = (R.seq + c) / kStages;
+        mbar_wait(R.fullBar + buf, use & 1u);
+        if (warpLive)
+        {
+            const unsigned char *chunk = R.ring + buf * kChunkBytes;
+            uint32_t const span = min(kChunkSlots, fs.nSlots - c * kChunkSlots);
+            cone_collect<THREADS>(reinterpret_cast<const FilterPair *>(chunk), reinterpret_cast<const uint32_t *>(chunk + kChunkRecordBytes), span,
+                                  fr, n, live, list, cap, count);
+        }
+        __syncwarp();
+        if ((threadIdx.x & 31u) == 0u)
+            mbar_arrive(R.emptyBar + buf);
+    }
+    R.seq += nChunks;
+}
+
 __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_streamed(const __grid_constant__ TraceParams p)
 {
     extern __shared__ __align__(128) unsigned char ring[];

@@ -628,20 +628,48 @@ def test_row_bands_compose_to_the_full_render(tracer, oracle, cam, scene_random,
     tracer.set_stream(None)
 
 
-# ----------------------------------------------------------------------------- staging limit (two alternating buffers, second stream)
-def test_staging_limit_forces_chunks_and_keeps_the_bits(tracer, oracle, cam, scene_random):
-    """spt_cuda_set_staging_limit: a tiny budget cuts the sample range into many chunks that alternate between the two
-    staging buffers (camera kernel of chunk k+1 on the auxiliary stream under the bounce kernel of chunk k); the per-pixel
-    running sums continue across chunks, so the accumulators are those of one launch -- and the oracle's."""
-    w, h, spp, depth = 100, 45, 11, 12
+# ----------------------------------------------------------------------------- staging limit: strips, chunks, auxiliary streams
+def test_staging_limit_strips_and_chunks_keep_the_bits(tracer, oracle, cam, scene_random, monkeypatch):
+    """spt_cuda_set_staging_limit / SptParams.strip_rows / split_chunk: a call that does not fit the budget is cut into strips
+    of tile rows and, below that, into sample chunks; work items alternate between two staging buffers, camera kernels run on
+    an auxiliary stream, the bounce kernels of neighbouring strips on two streams side by side.  Whatever the cut, the per-pixel
+    running sums continue across the chunks of a strip and strips touch disjoint pixels: the accumulators are the oracle's."""
+    w, h, spp, depth = 100, 45, 11, 12  # 6 tile rows of 8 (the last one 5 rows), 7 CTA columns
     tracer.set_scene(scene_random)
     oacc, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, pass_cap=10, seed=5)
     try:
-        for limit, launches in ((2 * (w * h * 16 + 512), 2 * 11 + 1), (5 * w * h * 16, 2 * 6 + 1), (0, 2 + 1)):
+        cases = [  # (staging limit, strip_rows, split_chunk, kernels launched = 2 per work item + resolve)
+            (0, 0, 0, 2 * 1 + 1),        # everything fits: one strip, one chunk
+            (0, 2, 0, 2 * 3 + 1),        # three strips, all samples each
+            (0, 4, 3, 2 * 2 * 4 + 1),    # two strips (4 + 2 tile rows) x four chunks (3 + 3 + 3 + 2)
+            (0, 1, 1, 2 * 6 * 11 + 1),   # one tile row, one sample per launch
+            (4 * w * 8 * 16 * 6, 0, 0, None),  # a budget of four samples of the image: the library cuts by itself
+            (1, 0, 0, None),             # absurdly small: one sample per launch, buffers as small as they can be
+        ]
+        for limit, strips, chunk, launches in cases:
             tracer.set_staging_limit(limit)
-            _, acc = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=5, want_accum=True)
-            assert_accum_equal(acc, oacc)
-            assert tracer.timing()["launches"] == launches, (limit, tracer.timing())
+            monkeypatch.setattr(tracer, "strip_rows", strips)
+            monkeypatch.setattr(tracer, "split_chunk", chunk)
+            for flags in (0, spt.FLAG_SERIAL_CHUNKS):
+                _, acc = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=5, want_accum=True, flags=flags)
+                assert_accum_equal(acc, oacc)
+                got = tracer.timing()["launches"]
+                assert got == launches if launches else got > 3, (limit, strips, chunk, got)
+        # a ragged segment, bands of another "rank" and strips together
+        seg = (3, 43, 7, 91)
+        monkeypatch.setattr(tracer, "strip_rows", 2)
+        monkeypatch.setattr(tracer, "split_chunk", 4)
+        tracer.set_staging_limit(0)
+        import torch
+
+        tracer.set_stream(torch.cuda.current_stream().cuda_stream)
+        total = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+        for rank in range(2):
+            tracer.accumulate(cam, w, h, 0, spp, depth, total, pass_cap=10, seed=5, seg=seg, bands=(2, rank))
+        torch.cuda.synchronize()
+        tracer.set_stream(None)
+        oseg, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, pass_cap=10, seed=5, seg=seg)
+        assert_accum_equal(total.cpu().numpy(), oseg)
     finally:
         tracer.set_staging_limit(0)
 
@@ -757,3 +785,32 @@ def test_shared_reciprocal_division_equals_fdiv_rn(tracer):
         assert bad == 0, (seed, tested, bad)
         total += tested
     assert total >= 4 << 30
+
+
+# ----------------------------------------------------------------------------- pixel-cone candidate lists of the camera kernel
+@pytest.mark.parametrize("size", [(16, 900), (900, 16), (3, 3), (257, 131), (1, 40)])
+@pytest.mark.parametrize("eye,look", [((0, 1, -3), (0, 1, 0)), ((0.3, 0.45, 8.0), (4, 0.3, 12)), ((40, 25, -60), (0, 0, 10)), ((0, 500, -2000), (0, 1, 5))])
+def test_pixel_cone_lists_never_lose_a_hit(tracer, oracle, scene_random, size, eye, look):
+    """The camera kernel tests every sphere ONCE per pixel and launch against the pixel's central ray with records fattened by
+    the pixel's angular footprint, and runs only the exact sequence on that list for every sample.  The list must contain every
+    sphere any jittered sample can hit: renders equal the oracle's bit for bit for extreme aspect ratios (quirk Q1 stretches the
+    ray fan: px reaches 2 W / H - 1), tiny images (footprints of tens of degrees: lists overflow, the per-sample filter takes
+    over), an eye inside the sphere field, and far / off-axis eyes."""
+    w, h = size
+    cam = oracle.camera(eye=eye, look=look)
+    spp, depth = 6, 4
+    tracer.set_scene(scene_random)
+    _, acc = tracer.render(cam, w, h, spp, depth, pass_cap=10, seed=9, want_accum=True)
+    oacc, _ = oracle.render_accum(scene_random, cam, w, h, spp, depth, pass_cap=10, seed=9)
+    assert_accum_equal(acc, oacc)
+
+
+def test_pixel_cone_lists_streamed_and_dense(tracer, oracle, cam):
+    """The same on the streamed list (one pass of the blob through the TMA ring per launch) for a lattice whose far rows put
+    more spheres into one pixel footprint than a list holds (those CTAs stream per sample), at two image sizes."""
+    scene = spt.generate_lattice(7, 48)
+    tracer.set_scene(scene)
+    for (w, h) in ((120, 64), (40, 300)):
+        _, acc = tracer.render(cam, w, h, 3, 6, pass_cap=10, seed=2, want_accum=True, flags=spt.FLAG_STREAMED)
+        oacc, _ = oracle.render_accum(scene, cam, w, h, 3, 6, pass_cap=10, seed=2)
+        assert_accum_equal(acc, oacc)

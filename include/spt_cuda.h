@@ -177,10 +177,11 @@ enum { SPT_PARTITION_AUTO = 0, SPT_PARTITION_SAMPLES = 1, SPT_PARTITION_BANDS = 
 SPT_API int spt_cuda_set_partition(SptContext *ctx, int partition); /* multi-device contexts; AUTO = samples when a call has >= n of them */
 SPT_API void spt_cuda_destroy(SptContext *ctx);
 /* Split rendering stages one 16-byte record per camera sample in device memory.  `bytes` bounds the staging per device (two
- * buffers that alternate); 0 restores the default, SPT_DEFAULT_STAGING_BYTES.  A call that does not fit is cut into strips of
- * tile rows first (all samples of a strip in one pair of launches: the lanes of a warp finish closer together the more of a
- * pixel's samples one launch covers) and into sample chunks only below two waves of CTAs per strip; camera kernels and the
- * bounce kernels of neighbouring strips overlap on auxiliary streams.  The library never sizes this from the free device memory. */
+ * buffers that alternate); 0 restores the default, SPT_DEFAULT_STAGING_BYTES.  A call that does not fit is cut into chunks of
+ * samples (whole segment per pair of launches; strips of tile rows only when not even 16 samples of the segment fit); camera
+ * kernels, and the bounce kernels of neighbouring strips, overlap on auxiliary streams.  Longer chunks keep more lanes busy
+ * (config 3: 8 GiB = 32 samples per launch, 64 GiB = 256: +5 %), so an application that owns the GPU may raise the limit.
+ * The library never sizes this from the free device memory. */
 #define SPT_DEFAULT_STAGING_BYTES (8ull << 30)
 SPT_API int spt_cuda_set_staging_limit(SptContext *ctx, uint64_t bytes);
 /* run on a caller stream (cudaStream_t passed as void*; NULL is the legacy default stream) instead of

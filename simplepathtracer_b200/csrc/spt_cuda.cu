@@ -447,15 +447,17 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             p.filterCam.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairsCam + c->filter.nSlots / 2);
             p.filterCam.epsTCam = c->camEpsT;
             // Staging and work items.  The camera kernel stages one 16-byte record per pixel and sample; the budget is the caller's
-            // (spt_cuda_set_staging_limit, 8 GiB unless raised), never a share of whatever the device has free.  A lane of the bounce
-            // kernel owns its pixel for a whole launch and the warp waits for its slowest lane, so what matters is SAMPLES PER
-            // LAUNCH: the more of a pixel's samples one launch covers, the closer the lanes of a warp finish together (share of
-            // lanes holding a ray in the closest-hit trips on config 3: 88.7 % at 32 samples per launch, 94.5 % at 256).  When the
-            // whole call does not fit the budget it is therefore cut along the IMAGE first -- strips of tile rows, all samples of
-            // a strip in one launch while a strip keeps >= 2 waves of CTAs -- and only then along the samples.  The budget holds
-            // two buffers that alternate.  Strips touch disjoint pixels, so the bounce kernels of consecutive strips run
-            // concurrently (main and second auxiliary stream) and the tail of one fills with CTAs of the next; chunks of the same
-            // strip stay in stream order (the per-pixel running sums continue).  Camera kernels run on the first auxiliary stream.
+            // (spt_cuda_set_staging_limit, 8 GiB unless raised), never a share of whatever the device has free.  A call that does
+            // not fit is cut into work items = (strip of tile rows) x (chunk of samples); two staging buffers alternate.  Measured
+            // on config 3 (profiles/r2_ab_work_items.txt): a lane of the bounce kernel owns its pixel for a whole launch and the
+            // warp waits for its slowest lane, so more samples per launch keep more lanes busy (88.7 % of the lanes hold a ray at
+            // 32 samples per launch, 94.5 % at 256, 96.0 % at 1024) -- but a launch's CTAs then run proportionally longer, and with
+            // the strips that a fixed budget forces (few waves of long CTAs) the tail of every launch costs more than the
+            // balance gains: 8 GiB as 270 rows x 32 samples 8 368 Msamples/s, 68 x 128 8 149, 34 x 256 7 852, 17 x 512 7 487.  So
+            // the cut is along the SAMPLES, whole image per launch; strips only when not even 16 samples of the image fit.
+            // Streams: camera kernels on the first auxiliary stream (the tail of a bounce kernel fills with the next camera
+            // kernel's CTAs); strips touch disjoint pixels, so the bounce kernels of consecutive strips run side by side (main
+            // and second auxiliary stream); chunks of one strip stay in stream order (the per-pixel running sums continue).
             uint32_t const total = prm->sample_end - prm->sample_begin;
             size_t const rowBytes = size_t(segW) * SPT_BAND_ROWS * sizeof(float4); // one sample of every pixel of one tile row
             size_t const pad = 256;                                                // the consumer prefetches four records past the one it reads
@@ -469,13 +471,19 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
             else if (!fitsWhole)
             {
                 size_t const half = size_t(c->stagingLimit) / 2 > pad ? size_t(c->stagingLimit) / 2 - pad : 0;
-                uint64_t const slots = uint64_t(c->prop.multiProcessorCount) * (streamed ? 4u : 8u);
-                uint32_t const minStrip = std::min<uint32_t>(myBands, uint32_t((2 * slots + sGridFull.x - 1) / sGridFull.x));
-                stripRows = uint32_t(std::min<size_t>(myBands, half / (size_t(chunk) * rowBytes)));
-                if (stripRows < minStrip)
-                {
-                    stripRows = std::max(1u, minStrip);
-                    chunk = uint32_t(std::max<size_t>(1, std::min<size_t>(chunk, half / (size_t(stripRows) * rowBytes))));
+                uint32_t const minChunk = std::min(chunk, 16u);
+                size_t const whole = half / (size_t(myBands) * rowBytes); // samples of the whole image one buffer holds
+                if (whole >= minChunk)
+                    chunk = uint32_t(std::min<size_t>(chunk, whole));
+                else
+                { // a very large image or a very small budget: strips of minChunk samples, shorter chunks only below one tile row
+                    chunk = minChunk;
+                    stripRows = uint32_t(std::min<size_t>(myBands, half / (size_t(chunk) * rowBytes)));
+                    if (stripRows == 0)
+                    {
+                        stripRows = 1;
+                        chunk = uint32_t(std::max<size_t>(1, std::min<size_t>(chunk, half / rowBytes)));
+                    }
                 }
             }
             uint32_t const nStrips = (myBands + stripRows - 1) / stripRows, nChunks = (total + chunk - 1) / chunk;

@@ -228,6 +228,21 @@ SPT_API int spt_cuda_first_hit(SptContext *ctx, const SptCamera *cam, uint32_t w
 SPT_API int spt_cuda_closest_hit(SptContext *ctx, uint32_t count, const float *dir3, const float *org3, uint32_t flags,
                          uint32_t *idx, uint32_t *exact_evals);
 
+/* spt_cuda_closest_hit WITHOUT any device allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same arguments, same kernel, same results as spt_cuda_closest_hit; the device staging of rays and answers is a
+ * file-scope `static __device__` array of the library (SPT_STATIC_SCRATCH_RAYS * 32 bytes = 2 MiB, held by every GPU that
+ * loads the library until the process exits) instead of the context's cudaMalloc'ed probe buffer.  The call allocates and
+ * frees nothing (no cudaMalloc / cudaFree, no allocating library routine); spt_cuda_set_scene must have been called before.
+ *   - count > SPT_STATIC_SCRATCH_RAYS is rejected with SPT_ERR_INVALID and a message naming the limit.
+ *   - The array is ONE per device and process, shared by every context and every call, and keeps the last call's contents:
+ *     each call first overwrites its own answer region (0xFF) and every word it returns is rewritten by its kernel, so nothing
+ *     of an earlier call can be returned; but two calls that overlap on the same GPU (two contexts, or two host threads using
+ *     two contexts) RACE on it.  Calls through one context are serialised by the context's lock.  Blocking. */
+#define SPT_STATIC_SCRATCH_RAYS 65536u
+SPT_API int spt_cuda_closest_hit_static(SptContext *ctx, uint32_t count, const float *dir3, const float *org3, uint32_t flags,
+                                uint32_t *idx, uint32_t *exact_evals);
+
 SPT_API int spt_cuda_get_counters(SptContext *ctx, SptCounters *out); /* accumulated since the last reset */
 SPT_API int spt_cuda_reset_counters(SptContext *ctx);
 SPT_API int spt_cuda_get_timing(SptContext *ctx, SptTiming *out);

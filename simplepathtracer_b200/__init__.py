@@ -35,6 +35,7 @@ from .binding import (  # noqa: F401
     PARTITION_SAMPLES,
     PARTITION_BANDS,
     DEFAULT_STAGING_BYTES,
+    STATIC_SCRATCH_RAYS,
     init_spheres,
     generate_spheres,
     generate_metal_glass,

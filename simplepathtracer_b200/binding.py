@@ -18,6 +18,7 @@ LIB_NAME = "libspt_cuda.so"
 ABI_VERSION = 3  # SPT_ABI_VERSION of include/spt_cuda.h
 PARTITION_AUTO, PARTITION_SAMPLES, PARTITION_BANDS = 0, 1, 2
 DEFAULT_STAGING_BYTES = 8 << 30  # SPT_DEFAULT_STAGING_BYTES
+STATIC_SCRATCH_RAYS = 65536  # SPT_STATIC_SCRATCH_RAYS
 MEGAKERNEL, WAVEFRONT = 0, 1
 FLAG_STRICT_LOOP, FLAG_COUNTERS, FLAG_CROSS_CHECK, FLAG_STREAMED, FLAG_RESIDENT, FLAG_SPLIT, FLAG_SINGLE_KERNEL = 1, 2, 4, 8, 16, 32, 64
 FLAG_SERIAL_CHUNKS = 128
@@ -180,7 +181,7 @@ EXPORTS = [
     "spt_cuda_destroy", "spt_cuda_set_stream", "spt_cuda_device_info", "spt_cuda_set_scene",
     "spt_cuda_render", "spt_cuda_accumulate", "spt_cuda_resolve", "spt_cuda_synchronize", "spt_cuda_first_hit",
     "spt_cuda_progressive_begin", "spt_cuda_progressive_add", "spt_cuda_progressive_image", "spt_cuda_progressive_load",
-    "spt_cuda_closest_hit", "spt_cuda_get_counters", "spt_cuda_reset_counters", "spt_cuda_get_timing",
+    "spt_cuda_closest_hit", "spt_cuda_closest_hit_static", "spt_cuda_get_counters", "spt_cuda_reset_counters", "spt_cuda_get_timing",
     "spt_cuda_measure_fp32_peak", "spt_cuda_self_check_division", "spt_cuda_last_error", "spt_cuda_version", "spt_cuda_abi_version",
 ]
 HOST_EXPORTS = [
@@ -228,6 +229,8 @@ def load_library():
     L.spt_cuda_first_hit.argtypes = [C.c_void_p, C.POINTER(_CCamera), C.c_uint32, C.c_uint32, Segment, C.c_uint32, C.c_void_p,
                                      C.c_void_p, C.c_void_p]
     L.spt_cuda_closest_hit.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+    if hasattr(L, "spt_cuda_closest_hit_static"):  # absent from libraries built before it existed (A/B runs via SPT_CUDA_LIB)
+        L.spt_cuda_closest_hit_static.argtypes = L.spt_cuda_closest_hit.argtypes
     L.spt_cuda_get_counters.argtypes = [C.c_void_p, C.POINTER(Counters)]
     L.spt_cuda_reset_counters.argtypes = [C.c_void_p]
     L.spt_cuda_get_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
@@ -423,6 +426,16 @@ class PathTracer:
         ev = np.empty(dirs.shape[0], np.uint32) if want_evals else None
         self._check(self.L.spt_cuda_closest_hit(self.h, dirs.shape[0], dirs.ctypes.data, orgs.ctypes.data, flags, idx.ctypes.data,
                                                 ev.ctypes.data if want_evals else None))
+        return (idx, ev) if want_evals else idx
+
+    def closest_hit_static(self, dirs: Sequence, orgs: Sequence, flags=0, want_evals=False):
+        """spt_cuda_closest_hit_static: the same through the library's static device scratch -- no device allocation."""
+        dirs = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+        orgs = np.ascontiguousarray(orgs, np.float32).reshape(-1, 3)
+        idx = np.empty(dirs.shape[0], np.uint32)
+        ev = np.empty(dirs.shape[0], np.uint32) if want_evals else None
+        self._check(self.L.spt_cuda_closest_hit_static(self.h, dirs.shape[0], dirs.ctypes.data, orgs.ctypes.data, flags, idx.ctypes.data,
+                                                       ev.ctypes.data if want_evals else None))
         return (idx, ev) if want_evals else idx
 
     def counters(self) -> dict:

@@ -39,6 +39,11 @@ int fail(int code, const char *what, cudaError_t ce = cudaSuccess)
     } while (0)
 } // namespace
 
+// Scratch of spt_cuda_closest_hit_static (include/spt_cuda.h): rays in, answers out, for callers that must not allocate.
+// In HOST code this name is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress (create_one,
+// once per device, with that device current) and is what the kernel is given.  [dir3 | org3 | idx | evals], 32 bytes per ray.
+static __device__ __align__(256) unsigned char g_staticScratch[size_t(SPT_STATIC_SCRATCH_RAYS) * 32u];
+
 struct SptContext
 {
     int device = 0;
@@ -93,6 +98,8 @@ struct SptContext
     uint32_t progW = 0, progH = 0;
     void *dProbe = nullptr;
     size_t probeBytes = 0;
+    void *dStaticScratch = nullptr; // device address of g_staticScratch on this context's device (cudaGetSymbolAddress)
+    cudaError_t staticScratchError = cudaSuccess;
     size_t maxSmemOptin = 0;
 
     // multi-device contexts (spt_cuda_create_multi): `all` = this context followed by one internal context per further device
@@ -642,6 +649,14 @@ int create_one(SptContext **out, int device)
     }
     c->stream = c->ownStream;
     c->maxSmemOptin = c->prop.sharedMemPerBlockOptin;
+    // the static scratch array's address on THIS device (cudaSetDevice(device) above is still in force); a failure is kept
+    // for spt_cuda_closest_hit_static to report and does not fail the context
+    c->staticScratchError = cudaGetSymbolAddress(&c->dStaticScratch, g_staticScratch);
+    if (c->staticScratchError != cudaSuccess)
+    {
+        c->dStaticScratch = nullptr;
+        (void)cudaGetLastError();
+    }
     *out = c;
     return SPT_OK;
 }
@@ -1343,6 +1358,45 @@ int spt_cuda_closest_hit(SptContext *c, uint32_t count, const float *dir3, const
     uint32_t const mode = (flags & SPT_FLAG_STRICT_LOOP) ? 1u : ((flags & SPT_FLAG_CROSS_CHECK) ? 2u : 0u);
     SPT_CUDA_CHECK(cudaMemcpyAsync(dDir, dir3, size_t(count) * 12, cudaMemcpyHostToDevice, c->stream));
     SPT_CUDA_CHECK(cudaMemcpyAsync(dOrg, org3, size_t(count) * 12, cudaMemcpyHostToDevice, c->stream));
+    spt::closest_hit_kernel<<<(count + 255) / 256, 256, 0, c->stream>>>(c->dGeom, c->n, c->filter, mode, count, dDir, dOrg, dIdx,
+                                                                          dEvals);
+    SPT_CUDA_CHECK(cudaGetLastError());
+    SPT_CUDA_CHECK(cudaMemcpyAsync(idx, dIdx, size_t(count) * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (exact_evals)
+        SPT_CUDA_CHECK(cudaMemcpyAsync(exact_evals, dEvals, size_t(count) * 4, cudaMemcpyDeviceToHost, c->stream));
+    SPT_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    return SPT_OK;
+}
+
+int spt_cuda_closest_hit_static(SptContext *c, uint32_t count, const float *dir3, const float *org3, uint32_t flags, uint32_t *idx,
+                                uint32_t *exact_evals)
+{
+    if (!c || !dir3 || !org3 || !idx)
+        return fail(SPT_ERR_INVALID, "null argument");
+    if (count > SPT_STATIC_SCRATCH_RAYS)
+    {
+        char msg[160];
+        snprintf(msg, sizeof(msg), "spt_cuda_closest_hit_static: %u rays exceed the static scratch (SPT_STATIC_SCRATCH_RAYS = %u); split the call",
+                 count, unsigned(SPT_STATIC_SCRATCH_RAYS));
+        return fail(SPT_ERR_INVALID, msg);
+    }
+    std::lock_guard<std::mutex> g(c->lock);
+    SPT_CUDA_CHECK(cudaSetDevice(c->device));
+    if (!c->dStaticScratch)
+        return fail(SPT_ERR_CUDA, "cudaGetSymbolAddress of the static scratch array failed at context creation", c->staticScratchError);
+    if (c->n == 0)
+        return fail(SPT_ERR_NO_SCENE, "spt_cuda_set_scene has not been called");
+    if (count == 0)
+        return SPT_OK;
+    // the same carving as spt_cuda_closest_hit's probe buffer, inside the static array
+    float *dDir = static_cast<float *>(c->dStaticScratch);
+    float *dOrg = dDir + size_t(count) * 3;
+    uint32_t *dIdx = reinterpret_cast<uint32_t *>(dOrg + size_t(count) * 3);
+    uint32_t *dEvals = dIdx + count;
+    uint32_t const mode = (flags & SPT_FLAG_STRICT_LOOP) ? 1u : ((flags & SPT_FLAG_CROSS_CHECK) ? 2u : 0u);
+    SPT_CUDA_CHECK(cudaMemcpyAsync(dDir, dir3, size_t(count) * 12, cudaMemcpyHostToDevice, c->stream));
+    SPT_CUDA_CHECK(cudaMemcpyAsync(dOrg, org3, size_t(count) * 12, cudaMemcpyHostToDevice, c->stream));
+    SPT_CUDA_CHECK(cudaMemsetAsync(dIdx, 0xFF, size_t(count) * 8, c->stream)); // the array keeps the last call's answers: not these
     spt::closest_hit_kernel<<<(count + 255) / 256, 256, 0, c->stream>>>(c->dGeom, c->n, c->filter, mode, count, dDir, dOrg, dIdx,
                                                                           dEvals);
     SPT_CUDA_CHECK(cudaGetLastError());

@@ -9,6 +9,7 @@
  *   spt_host_save_bmp          stbi_write_bmp as called by io::SaveImage  include/IOHelpers.hpp:24-27
  *   spt_host_save_scene / spt_host_load_scene   the SoA scene globals + camera as a file (include/spt_host/SceneFile.hpp)
  *   spt_host_save_pfm          linear-float companion of the BMP (no reference counterpart)
+ *   spt_host_save_hdr          the same values as Radiance RGBE (what third_party/stb/stb_image_write.h:183 stbi_write_hdr serialises)
  *   spt_host_save_accum / spt_host_load_accum   accumulator checkpoint for resume (no reference counterpart)
  *
  * Generators return the sphere count; arrays are filled when cap >= count (call with cap = 0 to size).
@@ -47,6 +48,7 @@ SPT_API int spt_host_save_scene(const char *path, uint32_t n, const float *cente
 SPT_API uint32_t spt_host_load_scene(const char *path, uint32_t cap, float *centers4, float *radii, uint8_t *materials, float *colors4,
                              float *fuzz, float camera16[16]);
 SPT_API int spt_host_save_pfm(const char *path, uint32_t width, uint32_t height, const float *accum4);
+SPT_API int spt_host_save_hdr(const char *path, uint32_t width, uint32_t height, const float *accum4);
 SPT_API int spt_host_save_accum(const char *path, uint32_t width, uint32_t height, uint32_t samples_done, uint32_t depth, uint64_t seed,
                         const float *accum4);
 /* returns 1 and fills samples_done / depth / seed / accum4 (width*height*4) when the file matches the image size */

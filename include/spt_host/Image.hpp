@@ -9,6 +9,8 @@
 
 #include "Scene.hpp"
 
+#include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <string>
 #include <vector>
@@ -74,6 +76,45 @@ inline bool WritePfm(char const *path, uint32_t width, uint32_t height, float co
                 row[size_t(x) * 3u + k] = a[k] * inv / 255.f;
         }
         std::fwrite(row.data(), sizeof(float), row.size(), f);
+    }
+    return std::fclose(f) == 0;
+}
+
+// The other linear-float format SURVEY 8f-3 names: Radiance RGBE (.hdr), what the vendored stbi_write_hdr
+// (third_party/stb/stb_image_write.h:183) would serialise.  Header "#?RADIANCE", "FORMAT=32-bit_rle_rgbe", blank line,
+// resolution "-Y <h> +X <w>"; then rows TOP first, four bytes per pixel, flat (no run-length coding: every reader takes flat
+// scanlines).  A pixel is (r, g, b) * 2^-e rounded down to 8 bits each, e = exponent of the largest channel, stored as
+// e + 128; channels below 1e-32 become (0, 0, 0, 0).  Same values as WritePfm (mean radiance / 255, linear).
+inline bool WriteHdr(char const *path, uint32_t width, uint32_t height, float const *accum4)
+{
+    FILE *f = std::fopen(path, "wb");
+    if (!f)
+        return false;
+    std::fprintf(f, "#?RADIANCE\nFORMAT=32-bit_rle_rgbe\nEXPOSURE=1.0\n\n-Y %u +X %u\n", height, width);
+    std::vector<uint8_t> row(size_t(width) * 4u);
+    for (uint32_t y = height; y-- > 0;) // accumulator row y = 0 is the BOTTOM of the picture
+    {
+        for (uint32_t x = 0; x < width; ++x)
+        {
+            float const *a = accum4 + (size_t(y) * width + x) * 4u;
+            float const inv = 1.f / a[3];
+            float c[3];
+            for (int k = 0; k < 3; ++k)
+                c[k] = a[k] * inv / 255.f;
+            float const top = std::max(c[0], std::max(c[1], c[2]));
+            uint8_t *o = row.data() + size_t(x) * 4u;
+            if (!(top >= 1e-32f))
+                o[0] = o[1] = o[2] = o[3] = 0;
+            else
+            {
+                int e = 0;
+                float const scale = std::frexp(top, &e) * 256.f / top; // top * scale in [128, 256)
+                for (int k = 0; k < 3; ++k)
+                    o[k] = uint8_t(c[k] > 0.f ? c[k] * scale : 0.f);
+                o[3] = uint8_t(e + 128);
+            }
+        }
+        std::fwrite(row.data(), 1, row.size(), f);
     }
     return std::fclose(f) == 0;
 }

@@ -45,6 +45,7 @@ from .binding import (  # noqa: F401
     save_scene_file,
     load_scene_file,
     save_pfm,
+    save_hdr,
     save_accum,
     load_accum,
 )

@@ -187,7 +187,7 @@ EXPORTS = [
 HOST_EXPORTS = [
     "spt_host_init_spheres", "spt_host_generate_spheres", "spt_host_generate_metal_glass", "spt_host_generate_lattice",
     "spt_host_save_scene", "spt_host_load_scene",
-    "spt_host_camera_basis", "spt_host_save_bmp", "spt_host_save_pfm", "spt_host_save_accum", "spt_host_load_accum",
+    "spt_host_camera_basis", "spt_host_save_bmp", "spt_host_save_pfm", "spt_host_save_hdr", "spt_host_save_accum", "spt_host_load_accum",
 ]
 
 _LIB = None
@@ -251,6 +251,7 @@ def load_library():
     L.spt_host_load_scene.argtypes = [C.c_char_p, C.c_uint32, f32p, f32p, u8p, f32p, f32p, f32p]
     L.spt_host_load_scene.restype = C.c_uint32
     L.spt_host_save_pfm.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, f32p]
+    L.spt_host_save_hdr.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, f32p]
     L.spt_host_save_accum.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, f32p]
     L.spt_host_load_accum.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, u32p, u32p, C.POINTER(C.c_uint64), f32p]
     _LIB = L
@@ -516,6 +517,14 @@ def save_pfm(path: str, accum: np.ndarray) -> None:
     accum = np.ascontiguousarray(accum, np.float32)
     h, w = accum.shape[:2]
     if not load_library().spt_host_save_pfm(path.encode(), w, h, accum.ctypes.data_as(f32p)):
+        raise SptError("cannot write " + path)
+
+
+def save_hdr(path: str, accum: np.ndarray) -> None:
+    """The same linear image as Radiance RGBE (.hdr, flat scanlines, top row first)."""
+    accum = np.ascontiguousarray(accum, np.float32)
+    h, w = accum.shape[:2]
+    if not load_library().spt_host_save_hdr(path.encode(), w, h, accum.ctypes.data_as(f32p)):
         raise SptError("cannot write " + path)
 
 

@@ -100,6 +100,10 @@ int spt_host_save_pfm(const char *path, uint32_t width, uint32_t height, const f
 {
     return io::WritePfm(path, width, height, accum4) ? 1 : 0;
 }
+int spt_host_save_hdr(const char *path, uint32_t width, uint32_t height, const float *accum4)
+{
+    return io::WriteHdr(path, width, height, accum4) ? 1 : 0;
+}
 int spt_host_save_accum(const char *path, uint32_t width, uint32_t height, uint32_t samples_done, uint32_t depth, uint64_t seed,
                         const float *accum4)
 {

@@ -8,6 +8,9 @@
 //                [--progressive P]   P passes over the samples on a persistent accumulator; prints k/P and rewrites
 //                                    the image after each (the reference's live preview, Renderer.hpp:157-164)
 //                [--pfm file.pfm]    also write the linear float image (needs --progressive >= 1)
+//                [--hdr file.hdr]    the same image as Radiance RGBE (what stbi_write_hdr serialises)
+//                [--repeat R]        render R times in this process and print one Duration line each (the first render of a
+//                                    process also allocates the staging buffers and loads the kernels)
 //                [--checkpoint file] resume from the accumulators in `file` when it was written for THIS render (size, depth,
 //                                    seed, scene, camera, tracer), rewrite it after every pass
 //                [--gpus N]          one render spread over CUDA devices 0..N-1 by the library (spt_cuda_create_multi)
@@ -31,8 +34,8 @@
 int main(int argc, char **argv)
 {
     std::string scene = "reference", tracer = "recursive", out;
-    std::string pfm, checkpoint, dumpScene, deviceList;
-    uint32_t seed = 1, width = 1440, height = 1440, spp = 100, depth = 10, tiles = 1, progressive = 0, gpus = 1, stagingMib = 0;
+    std::string pfm, hdr, checkpoint, dumpScene, deviceList;
+    uint32_t seed = 1, width = 1440, height = 1440, spp = 100, depth = 10, tiles = 1, progressive = 0, gpus = 1, stagingMib = 0, repeat = 1;
     for (int i = 1; i + 1 < argc; i += 2)
     {
         std::string const k = argv[i], v = argv[i + 1];
@@ -47,6 +50,8 @@ int main(int argc, char **argv)
         else if (k == "--out") out = v;
         else if (k == "--progressive") progressive = uint32_t(std::stoul(v));
         else if (k == "--pfm") pfm = v;
+        else if (k == "--hdr") hdr = v;
+        else if (k == "--repeat") repeat = std::max<uint32_t>(1u, uint32_t(std::stoul(v)));
         else if (k == "--dump-scene") dumpScene = v;
         else if (k == "--checkpoint") checkpoint = v;
         else if (k == "--gpus") gpus = uint32_t(std::stoul(v));
@@ -85,8 +90,23 @@ int main(int argc, char **argv)
     if (stagingMib)
         spt_cuda::SetStagingLimit(uint64_t(stagingMib) << 20);
 
-    if ((!pfm.empty() || !checkpoint.empty()) && progressive == 0)
+    if ((!pfm.empty() || !hdr.empty() || !checkpoint.empty()) && progressive == 0)
         progressive = 1;
+    // context(s) and scene upload are set-up, as window and GL are in the reference (Renderer.hpp:316-333): not in Duration
+    auto const tSetup = std::chrono::high_resolution_clock::now();
+    try
+    {
+        spt_cuda::Acquire();
+    }
+    catch (std::exception const &e)
+    {
+        std::cerr << e.what() << "\n";
+        return 1;
+    }
+    std::cout << "Setup: " << std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::high_resolution_clock::now() - tSetup).count()
+              << " ms\n";
+    for (uint32_t rep = 0; rep < repeat; ++rep)
+    {
     auto const t0 = std::chrono::high_resolution_clock::now();
     try
     {
@@ -119,6 +139,8 @@ int main(int argc, char **argv)
                 first, resume.empty() ? nullptr : resume.data(), accum.data(), !checkpoint.empty());
             if (!pfm.empty() && !io::WritePfm(pfm.c_str(), width, height, accum.data()))
                 std::cerr << "cannot write " << pfm << "\n";
+            if (!hdr.empty() && !io::WriteHdr(hdr.c_str(), width, height, accum.data()))
+                std::cerr << "cannot write " << hdr << "\n";
         }
         else
         {
@@ -150,6 +172,7 @@ int main(int argc, char **argv)
     std::cout << "Duration: " << std::chrono::duration_cast<std::chrono::milliseconds>(dt).count() << " ms\n"; // Renderer.hpp:297
     double const sec = std::chrono::duration<double>(dt).count();
     std::cout << "Spheres: " << g_sphereNumber << "  Msamples/s: " << double(width) * height * spp / sec / 1e6 << "\n";
+    }
     if (!io::SaveImage(out.empty() ? nullptr : out.c_str()))
     {
         std::cerr << "cannot write image\n";

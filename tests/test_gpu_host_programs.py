@@ -73,9 +73,9 @@ def test_headless_progressive_checkpoint_resume(tmp_path, oracle):
     w, h, spp, depth, seed = 80, 48, 12, 6, 5
     base = [exe, "--scene", "reference", "--seed", str(seed), "--width", str(w), "--height", str(h), "--depth", str(depth), "--tracer", "task"]
     one, prog, half = str(tmp_path / "one.bmp"), str(tmp_path / "prog.bmp"), str(tmp_path / "half.bmp")
-    pfm, ck = str(tmp_path / "img.pfm"), str(tmp_path / "render.sptacc")
+    pfm, ck, hdr = str(tmp_path / "img.pfm"), str(tmp_path / "render.sptacc"), str(tmp_path / "img.hdr")
     assert subprocess.run(base + ["--spp", str(spp), "--out", one]).returncode == 0
-    r = subprocess.run(base + ["--spp", str(spp), "--out", prog, "--progressive", "4", "--pfm", pfm], capture_output=True, text=True)
+    r = subprocess.run(base + ["--spp", str(spp), "--out", prog, "--progressive", "4", "--pfm", pfm, "--hdr", hdr], capture_output=True, text=True)
     assert r.returncode == 0 and "4/4" in r.stdout and f"({spp} spp)" in r.stdout, r.stdout + r.stderr
     assert open(one, "rb").read() == open(prog, "rb").read()
     # stop half way, then resume from the checkpoint
@@ -94,6 +94,13 @@ def test_headless_progressive_checkpoint_resume(tmp_path, oracle):
     assert np.array_equal(got[0], acc)
     want = (acc[..., :3] * (np.float32(1) / acc[..., 3:4])) / np.float32(255)
     assert np.array_equal(read_pfm(pfm), want.astype(np.float32))
+    # the Radiance file holds the same picture at the format's resolution (top row first, 8-bit mantissa, truncated)
+    raw = open(hdr, "rb").read()
+    body = raw[raw.index(b"+X %d\n" % w) + len(b"+X %d\n" % w):]
+    px = np.frombuffer(body, np.uint8).reshape(h, w, 4)[::-1]
+    dec = px[..., :3].astype(np.float64) * np.ldexp(1.0, px[..., 3].astype(np.int32) - 136)[..., None]
+    top = want.max(axis=-1, keepdims=True).astype(np.float64)
+    assert np.all(dec <= want * (1 + 1e-6) + 1e-30) and np.all(want - dec <= top / 128 + 1e-30)
 
 
 def test_headless_scene_file(tmp_path):

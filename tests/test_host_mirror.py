@@ -85,6 +85,30 @@ def test_pfm_and_accumulator_checkpoint_files(tmp_path):
     assert spt.load_accum(str(tmp_path / "missing"), 7, 5) is None
 
 
+def test_hdr_file_decodes_to_the_linear_image(tmp_path):
+    """Radiance RGBE next to the PFM (SURVEY 8f-3 names .hdr / stbi_write_hdr): header, row order, and every pixel within
+    the format's own resolution (8-bit mantissa under the largest channel's exponent, truncated)."""
+    rng = np.random.default_rng(5)
+    acc = np.zeros((6, 9, 4), np.float32)
+    acc[..., :3] = rng.uniform(0, 255 * 4, size=(6, 9, 3)) * rng.choice([1e-6, 1e-2, 1.0, 40.0], size=(6, 9, 1))
+    acc[..., 3] = 4
+    acc[0, 0, :3] = 0  # black pixel: (0, 0, 0, 0)
+    path = str(tmp_path / "a.hdr")
+    spt.save_hdr(path, acc)
+    raw = open(path, "rb").read()
+    head = b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\nEXPOSURE=1.0\n\n-Y 6 +X 9\n"
+    assert raw.startswith(head) and len(raw) == len(head) + 6 * 9 * 4
+    px = np.frombuffer(raw[len(head):], np.uint8).reshape(6, 9, 4)[::-1]  # file rows run top to bottom
+    want = (acc[..., :3] * (np.float32(1) / acc[..., 3:4])) / np.float32(255)
+    assert tuple(px[0, 0]) == (0, 0, 0, 0)
+    scale = np.ldexp(1.0, px[..., 3].astype(np.int32) - 136)[..., None]  # mantissa * 2^(e - 128 - 8)
+    got = px[..., :3].astype(np.float64) * scale
+    top = want.max(axis=-1, keepdims=True).astype(np.float64)
+    lit = top[..., 0] > 0
+    assert np.all(got[lit] <= want[lit] * (1 + 1e-6)) and np.all(want[lit] - got[lit] <= top[lit] / 128 + 1e-30)
+    assert np.all(px[..., :3].max(axis=-1)[lit] >= 128)  # normalised: the largest channel uses the full mantissa
+
+
 def test_scene_file_round_trip(tmp_path):
     for sc in (spt.generate_spheres(2), spt.generate_metal_glass(4, 500), spt.generate_lattice(5, 16)):
         path = str(tmp_path / "scene.sptscene")

@@ -230,6 +230,10 @@ def run_native_arm(args, wl):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # a HOST-side group for the end-to-end leg: while rank 0's process drives all GPUs through one multi-device context, the
+        # other ranks must wait without a kernel on their GPU -- an NCCL barrier is a spinning kernel, and two processes on one
+        # GPU time-slice (session 8: 1 128 ms per render with the peers parked in an NCCL barrier against 512 ms device-timed)
+        host_group = dist.new_group(backend="gloo")
 
     spt.build_library()
     scene = load_scene(wl["scene"])
@@ -395,6 +399,7 @@ def run_native_arm(args, wl):
     e2e_pt = pt
     if world > 1:
         barrier()
+        dist.barrier(group=host_group)
         if rank == 0:
             e2e_pt = spt.PathTracer(list(range(world)))
             e2e_pt.set_staging_limit(staging)
@@ -415,6 +420,8 @@ def run_native_arm(args, wl):
         e2e_launches = e2e_pt.timing()["launches"]
         if world > 1:
             e2e_pt.close()
+    if world > 1:
+        dist.barrier(group=host_group)  # host wait: no kernel on the peers' GPUs during rank 0's renders
     barrier()
     e2e = None
     if rank == 0:

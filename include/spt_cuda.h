@@ -93,9 +93,13 @@ enum {
     SPT_FLAG_SINGLE_KERNEL = 64u, /* megakernel: do not split; camera and secondary segments in one kernel */
     SPT_FLAG_RESIDENT = 16u,   /* megakernel: keep the whole list resident in shared memory whenever it fits at all, even at
                                   the price of fewer CTAs per SM */
-    SPT_FLAG_SERIAL_CHUNKS = 128u /* split rendering, measurement: every kernel of every chunk on the main stream, one after the
+    SPT_FLAG_SERIAL_CHUNKS = 128u, /* split rendering, measurement: every kernel of every chunk on the main stream, one after the
                                   other (no camera kernel under the tail of the previous bounce kernel), so that
                                   SptTiming.primary_ms / secondary_ms are the kernels' own durations */
+    SPT_FLAG_OWN_PIXELS = 256u /* split rendering, comparison: every lane of the bounce kernel traces the samples of its own pixel
+                                  only.  The default shares the samples of a warp's 8x4-pixel tile among its 32 lanes (a lane
+                                  whose pixel is through takes samples of the pixel with the most left) and adds each pixel's
+                                  samples in order afterwards: same bits, fewer idle lanes */
 };
 /* geometry + pre-filter bytes (36 B per sphere) up to which the whole list is staged once per CTA; four CTAs per SM
  * stay resident below it.  Longer lists stream (spt_streamed.cuh). */

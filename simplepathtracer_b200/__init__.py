@@ -27,6 +27,7 @@ from .binding import (  # noqa: F401
     FLAG_SPLIT,
     FLAG_SINGLE_KERNEL,
     FLAG_SERIAL_CHUNKS,
+    FLAG_OWN_PIXELS,
     DIFFUSE,
     REFLECTIVE,
     REFRACTIVE,

@@ -515,7 +515,11 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
                 c->firstHitsBytes = bufBytes * nBuffers;
             }
             void (*primary)(const spt::TraceParams) = streamed ? spt::primary_hits_streamed : spt::primary_hits_kernel<2, spt::SplitShape>;
-            void (*secondary)(const spt::TraceParams) = streamed ? spt::trace_secondary_streamed : spt::trace_secondary<2, spt::SplitShape>;
+            // samples shared inside the warp (spt_split.cuh, AccDeposit) unless the caller opts out or a chunk does not fit the task word
+            bool const share = !(prm->flags & SPT_FLAG_OWN_PIXELS) && chunk < spt::kTaskSampleMask;
+            void (*secondary)(const spt::TraceParams) =
+                streamed ? (share ? spt::trace_secondary_streamed<true> : spt::trace_secondary_streamed<false>)
+                         : (share ? spt::trace_secondary<2, spt::SplitShape, true> : spt::trace_secondary<2, spt::SplitShape, false>);
             // the resident kernels run smaller CTAs than the rest (spt_split.cuh, SplitShape)
             dim3 const sBlock(streamed ? spt::kBlockThreads : spt::SplitShape::kThreads);
             SPT_CUDA_CHECK(cudaFuncSetAttribute(primary, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));

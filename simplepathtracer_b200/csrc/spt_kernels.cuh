@@ -209,6 +209,7 @@ struct AccRegs // in the lane's registers (L.sum, L.count)
         L.count = fadd(L.count, 1.f);
     }
     __device__ __forceinline__ void count_only() const { L.count = fadd(L.count, 1.f); }
+    __device__ __forceinline__ void drop() const {} // a dropped path leaves no trace in the pixel (TaskBasedPathTracer.hpp:196-198)
 };
 struct AccShared // in a per-lane float4 slot of shared memory: touched once per finished sample, never held in registers
 {
@@ -228,6 +229,7 @@ struct AccShared // in a per-lane float4 slot of shared memory: touched once per
         a.w = fadd(a.w, 1.f);
         sts128(slot, a);
     }
+    __device__ __forceinline__ void drop() const {}
 };
 
 // Warp-cooperative rejection sampling of the shell vector (Random.hpp:115-141).
@@ -434,6 +436,7 @@ __device__ __forceinline__ void shade_surface(const TraceParams &p, GeomPtr geom
         if (p.passCap && L.specular >= p.passCap)
         {
             ++dropped; // the task tracer's pass loop ends (TaskBasedPathTracer.hpp:81): dropped, not counted
+            acc.drop();
             L.mode = MODE_NEW;
         }
         else if (L.specular >= kSpecularSafetyCap)

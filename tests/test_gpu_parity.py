@@ -593,6 +593,31 @@ def test_split_render_segment_and_other_camera(tracer, oracle, scene_random):
         assert_accum_equal(acc, oacc)
 
 
+@pytest.mark.parametrize("feed", [0, spt.FLAG_STREAMED])
+@pytest.mark.parametrize("pass_cap", [0, 10, 2])
+def test_samples_shared_inside_the_warp_keep_the_bits(tracer, oracle, cam, scene_random, scene_metal_glass, feed, pass_cap, monkeypatch):
+    """The bounce kernel's default shares the samples of a warp's 8x4 tile among its lanes (a finished sample is deposited into
+    its staging record, every pixel's deposits are added in sample order afterwards); SPT_FLAG_OWN_PIXELS keeps one lane = one
+    pixel.  Both leave the oracle's accumulators, drops and counts included, on ragged images (lanes without a pixel work for
+    their neighbours), over several chunks, resident and ring feed; sharing makes fewer closest-hit trips per warp."""
+    for scene, (w, h, spp, depth) in ((scene_random, (107, 61, 9, 12)), (scene_metal_glass, (50, 29, 6, 50))):
+        tracer.set_scene(scene)
+        oacc, octr = oracle.render_accum(scene, cam, w, h, spp, depth, pass_cap=pass_cap, seed=23)
+        trips = {}
+        for chunk in (0, 4):
+            monkeypatch.setattr(tracer, "split_chunk", chunk)
+            for own in (0, spt.FLAG_OWN_PIXELS):
+                tracer.reset_counters()
+                rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=pass_cap, seed=23, want_accum=True, flags=feed | own | spt.FLAG_COUNTERS)
+                c = tracer.counters()
+                assert_accum_equal(acc, oacc)
+                assert np.array_equal(rgb, oracle.resolve(oacc))
+                assert c["segments"] == octr["segments"] and c["dropped"] == octr["dropped"]
+                trips[(chunk, own)] = c["warp_iterations"]
+        if not feed:  # (the ring's loop is CTA-uniform: its trip count is the CTA's)
+            assert trips[(0, 0)] < trips[(0, spt.FLAG_OWN_PIXELS)]
+
+
 # ----------------------------------------------------------------------------- interleaved row bands (multi-GPU pixel partition)
 @pytest.mark.parametrize("variant,flags", [(spt.MEGAKERNEL, 0), (spt.MEGAKERNEL, spt.FLAG_SINGLE_KERNEL), (spt.MEGAKERNEL, spt.FLAG_STREAMED),
                                            (spt.MEGAKERNEL, spt.FLAG_STRICT_LOOP), (spt.WAVEFRONT, 0)])

@@ -5,16 +5,21 @@
 // is how the closest-hit loop is fed.  The pre-filter blob is cut into chunks of kChunkSlots slots (10 KB:
 // 8 KB of records + 2 KB of slot->index map) that stream through a kStages-deep ring in shared memory:
 //
-//   producer   one elected thread; per chunk: wait empty[buf] (all 8 warps released the previous tenant),
-//              mbarrier.arrive.expect_tx on full[buf], two cp.async.bulk (TMA) copies global -> shared
-//   consumers  all 8 warps; per chunk: wait full[buf], run the pre-filter span over it with warp-uniform
-//              (broadcast) LDS.128, exact sequence on the candidates (geometry through L1/L2: ~2 per ray),
-//              __syncwarp, one mbarrier.arrive on empty[buf] per warp
+//   consumers  all 8 warps; per chunk: wait full[buf] (the bytes have landed), run the pre-filter span over it with
+//              warp-uniform (broadcast) LDS.128, exact sequence on the candidates (geometry through L1/L2: ~2 per ray),
+//              __syncwarp, one count on released[buf] per warp
+//   producer   whoever RELEASES a buffer last: the warp whose count completes released[buf] knows that nobody reads the
+//              buffer any more and refills it at once with the chunk kStages further on (mbarrier.arrive.expect_tx on
+//              full[buf], two cp.async.bulk (TMA) copies global -> shared).  Nobody ever waits for a buffer to become
+//              free.  (Round 1 had one elected thread producing kStages - 1 chunks ahead behind an "empty" mbarrier: ncu on
+//              config 5 showed that thread spinning on it -- its warp, a consumer like the others, then ran late for the
+//              whole CTA -- and 8 % of all executed instructions in try_wait loops.)
 //
 // so the CTA walks the list in loose lockstep (warps may drift by up to kStages - 1 chunks) and every record
 // is fetched from L2 once per CTA instead of once per warp.  One __syncthreads_or per ray segment decides
-// whether any lane of the CTA still has work; the chunk ring is drained at every segment, so no copy is
-// ever in flight when the CTA exits.
+// whether any lane of the CTA still has work; the ring is drained at every segment (the last kStages chunks are
+// not refilled), so no copy is ever in flight when the CTA exits and thread 0 may start the next segment's first
+// kStages chunks without asking.
 #pragma once
 
 #include "spt_kernels.cuh"
@@ -23,15 +28,21 @@ namespace spt
 {
 
 constexpr uint32_t kChunkSlots = 512;                                           // slots per chunk (16 mask words)
-constexpr uint32_t kStages = 4;                                                 // ring depth
+#ifndef SPT_RING_STAGES
+#define SPT_RING_STAGES 3 // 30 KB of ring + the lane stash: four eight-warp CTAs per SM (four stages: three)
+#endif
+constexpr uint32_t kStages = SPT_RING_STAGES;                                   // ring depth
 constexpr uint32_t kChunkRecordBytes = kChunkSlots / 2u * uint32_t(sizeof(FilterPair)); // 8192
 constexpr uint32_t kChunkBytes = kChunkRecordBytes + kChunkSlots * 4u;          // 10240
-constexpr uint32_t kStreamSmemBytes = kStages * kChunkBytes;                    // 40960
+constexpr uint32_t kStreamSmemBytes = kStages * kChunkBytes;
+constexpr uint32_t kRingWarps = kBlockThreads / 32u;
 
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
 {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count));
 }
+// (try_wait suspends the thread until the phase completes or a system time limit passes; an explicit suspendTimeHint makes
+// ptxas emit a NANOSLEEP loop that executes MORE instructions while waiting -- session 12 -- so there is none)
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 {
     uint32_t const addr = smem_addr(bar);
@@ -46,22 +57,24 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
                      : "memory");
     }
 }
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
-{
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
-}
 
-// producer side, one thread: chunk `c` of the blob as the `seq`-th tenant of the ring
-__device__ __forceinline__ void stream_produce(const FilterScene &fs, unsigned char *ring, uint64_t *fullBar, uint64_t *emptyBar,
-                                               uint32_t seq, uint32_t c)
+// The ring as the kernels carry it around
+struct StreamRing
 {
-    uint32_t const buf = seq % kStages, use = seq / kStages;
-    if (use > 0u)
-        mbar_wait(emptyBar + buf, (use - 1u) & 1u); // every warp has released the previous tenant
+    unsigned char *ring;
+    uint64_t *fullBar;
+    uint32_t *released; // per buffer: warps that are through with its current tenant
+    uint32_t seq;       // chunks this CTA has streamed so far: the ring position
+};
+
+// one thread: chunk `c` of the blob as the `seq`-th tenant of the ring (its buffer is known to be free)
+__device__ __forceinline__ void stream_produce(const FilterScene &fs, const StreamRing &R, uint32_t seq, uint32_t c)
+{
+    uint32_t const buf = seq % kStages;
     uint32_t const slots = min(kChunkSlots, fs.nSlots - c * kChunkSlots);
     uint32_t const recBytes = slots / 2u * uint32_t(sizeof(FilterPair)), idxBytes = slots * 4u;
-    unsigned char *dst = ring + buf * kChunkBytes;
-    uint32_t const bar = smem_addr(fullBar + buf);
+    unsigned char *dst = R.ring + buf * kChunkBytes;
+    uint32_t const bar = smem_addr(R.fullBar + buf);
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(recBytes + idxBytes) : "memory");
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst)),
                  "l"(fs.pairs + size_t(c) * (kChunkSlots / 2u)), "r"(recBytes), "r"(bar)
@@ -72,68 +85,78 @@ __device__ __forceinline__ void stream_produce(const FilterScene &fs, unsigned c
                  : "memory");
 }
 
-// The ring as the kernels carry it around
-struct StreamRing
-{
-    unsigned char *ring;
-    uint64_t *fullBar, *emptyBar;
-    uint32_t seq; // chunks this CTA has streamed so far: the ring position
-};
-
-__device__ __forceinline__ void stream_ring_init(StreamRing &R, unsigned char *ring, uint64_t *fullBar, uint64_t *emptyBar)
+__device__ __forceinline__ void stream_ring_init(StreamRing &R, unsigned char *ring, uint64_t *fullBar, uint32_t *released)
 {
     R.ring = ring;
     R.fullBar = fullBar;
-    R.emptyBar = emptyBar;
+    R.released = released;
     R.seq = 0;
     if (threadIdx.x == 0)
     {
         for (uint32_t s = 0; s < kStages; ++s)
         {
             mbar_init(fullBar + s, 1u);
-            mbar_init(emptyBar + s, kBlockThreads / 32u);
+            released[s] = 0u;
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
 }
 
-// FindClosestIntersectionSphere (Collision.hpp:87-109) over the streamed list.  Called by EVERY thread of the CTA, after
-// a CTA-wide barrier that follows the previous call (no warp reads the ring any more: the producer starts over at
-// chunk 0).  live = the lane has a ray; warpLive = some lane of the warp has (a warp without any only keeps the
-// barriers moving).  CAM: camera form of the records (fs = the eye-specialised blob).
-template <bool CAM>
-__device__ __forceinline__ uint32_t streamed_closest_hit(const FilterScene &fs, const float4 *geom, uint32_t n, V3 dir, V3 org,
-                                                         StreamRing &R, uint32_t &exactEvals, bool live, bool warpLive)
+// One pass of the whole blob through the ring: body(records, slot map, slots of the chunk) runs in every warp with a live
+// lane, chunk after chunk.  Called by EVERY thread of the CTA, after a CTA-wide barrier that follows the previous pass (the
+// ring is drained: thread 0 starts the first kStages chunks at once) and that also counted the warps with a live lane
+// (stream_live_warps).  A warp without one takes no part: it neither waits for chunks nor counts on them -- it goes straight
+// to the CTA's next barrier, which costs no issue slots (ncu, config 5: a tenth of the bounce kernel's issue slots went into
+// try_wait loops of warps that had nothing to trace).
+template <typename Body>
+__device__ __forceinline__ void stream_pass(const FilterScene &fs, StreamRing &R, bool warpLive, uint32_t liveWarps, Body body)
 {
-    constexpr uint32_t kAhead = kStages - 1u;
     uint32_t const nChunks = (fs.nSlots + kChunkSlots - 1u) / kChunkSlots;
     if (threadIdx.x == 0)
-        for (uint32_t c = 0; c < kAhead && c < nChunks; ++c)
-            stream_produce(fs, R.ring, R.fullBar, R.emptyBar, R.seq + c, c);
+        for (uint32_t c = 0; c < kStages && c < nChunks; ++c)
+            stream_produce(fs, R, R.seq + c, c);
+    if (warpLive)
+        for (uint32_t c = 0; c < nChunks; ++c)
+        {
+            uint32_t const buf = (R.seq + c) % kStages, use = (R.seq + c) / kStages;
+            mbar_wait(R.fullBar + buf, use & 1u);
+            const unsigned char *chunk = R.ring + buf * kChunkBytes;
+            body(reinterpret_cast<const FilterPair *>(chunk), reinterpret_cast<const uint32_t *>(chunk + kChunkRecordBytes),
+                 min(kChunkSlots, fs.nSlots - c * kChunkSlots));
+            __syncwarp(); // the warp's reads of the buffer are done
+            if ((threadIdx.x & 31u) == 0u && atomicAdd(R.released + buf, 1u) == liveWarps - 1u)
+            {
+                // the last warp to let go of the buffer refills it (the others are past it; the next round of counts on this
+                // buffer starts only after its new tenant has landed and been read)
+                R.released[buf] = 0u;
+                if (c + kStages < nChunks)
+                    stream_produce(fs, R, R.seq + c + kStages, c + kStages);
+            }
+        }
+    R.seq += nChunks;
+}
+// the CTA-wide barrier in front of a pass: how many warps have a live lane (0: nobody, the caller's loop ends)
+__device__ __forceinline__ uint32_t stream_live_warps(bool warpLive)
+{
+    return uint32_t(__syncthreads_count(((threadIdx.x & 31u) == 0u && warpLive) ? 1 : 0));
+}
+
+// FindClosestIntersectionSphere (Collision.hpp:87-109) over the streamed list.  live = the lane has a ray; warpLive = some
+// lane of the warp has (a warp without any only keeps the counts moving).  CAM: camera form of the records (fs = the
+// eye-specialised blob).
+template <bool CAM>
+__device__ __forceinline__ uint32_t streamed_closest_hit(const FilterScene &fs, const float4 *geom, uint32_t n, V3 dir, V3 org,
+                                                         StreamRing &R, uint32_t &exactEvals, bool live, bool warpLive, uint32_t liveWarps)
+{
     uint32_t minIndex = n;
     float minDistanceSq = FLT_MAX;
     float const od = vdot(org, dir);
     exact_big_spheres(fs, geom, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
     FilterRay const fr = CAM ? make_filter_ray_cam(dir, od, fs.epsTCam) : make_filter_ray(dir, org, od, fs.amax, fs.nearOO);
-    for (uint32_t c = 0; c < nChunks; ++c)
-    {
-        if (threadIdx.x == 0 && c + kAhead < nChunks)
-            stream_produce(fs, R.ring, R.fullBar, R.emptyBar, R.seq + c + kAhead, c + kAhead);
-        uint32_t const buf = (R.seq + c) % kStages, use = (R.seq + c) / kStages;
-        mbar_wait(R.fullBar + buf, use & 1u);
-        if (warpLive)
-        {
-            const unsigned char *chunk = R.ring + buf * kChunkBytes;
-            uint32_t const span = min(kChunkSlots, fs.nSlots - c * kChunkSlots);
-            filter_span<CAM>(reinterpret_cast<const FilterPair *>(chunk), reinterpret_cast<const uint32_t *>(chunk + kChunkRecordBytes),
-                             span, fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
-        }
-        __syncwarp();
-        if ((threadIdx.x & 31u) == 0u)
-            mbar_arrive(R.emptyBar + buf);
-    }
-    R.seq += nChunks;
+    stream_pass(fs, R, warpLive, liveWarps, [&](const FilterPair *rec, const uint32_t *slotIdx, uint32_t span) {
+        filter_span<CAM>(rec, slotIdx, span, fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
+    });
     return minIndex;
 }
 
@@ -141,81 +164,41 @@ __device__ __forceinline__ uint32_t streamed_closest_hit(const FilterScene &fs, 
 // bound by the shared-memory wavefronts of the record loads, which two rays share (spt_split.cuh).
 __device__ __forceinline__ void streamed_closest_hit_cam2(const FilterScene &fs, const float4 *geom, uint32_t n, V3 org, V3 dirA, V3 dirB,
                                                           uint32_t &idxA, uint32_t &idxB, StreamRing &R, uint32_t &exactEvals, bool liveA,
-                                                          bool liveB, bool warpLive)
+                                                          bool liveB, bool warpLive, uint32_t liveWarps)
 {
-    constexpr uint32_t kAhead = kStages - 1u;
-    uint32_t const nChunks = (fs.nSlots + kChunkSlots - 1u) / kChunkSlots;
-    if (threadIdx.x == 0)
-        for (uint32_t c = 0; c < kAhead && c < nChunks; ++c)
-            stream_produce(fs, R.ring, R.fullBar, R.emptyBar, R.seq + c, c);
     idxA = idxB = n;
     float distA = FLT_MAX, distB = FLT_MAX;
     float const odA = vdot(org, dirA), odB = vdot(org, dirB);
     exact_big_spheres(fs, geom, dirA, org, odA, idxA, distA, exactEvals, liveA);
     exact_big_spheres(fs, geom, dirB, org, odB, idxB, distB, exactEvals, liveB);
     FilterRay const fa = make_filter_ray_cam(dirA, odA, fs.epsTCam), fb = make_filter_ray_cam(dirB, odB, fs.epsTCam);
-    for (uint32_t c = 0; c < nChunks; ++c)
-    {
-        if (threadIdx.x == 0 && c + kAhead < nChunks)
-            stream_produce(fs, R.ring, R.fullBar, R.emptyBar, R.seq + c + kAhead, c + kAhead);
-        uint32_t const buf = (R.seq + c) % kStages, use = (R.seq + c) / kStages;
-        mbar_wait(R.fullBar + buf, use & 1u);
-        if (warpLive)
-        {
-            const unsigned char *chunk = R.ring + buf * kChunkBytes;
-            uint32_t const span = min(kChunkSlots, fs.nSlots - c * kChunkSlots);
-            filter_span_cam2(reinterpret_cast<const FilterPair *>(chunk), reinterpret_cast<const uint32_t *>(chunk + kChunkRecordBytes), span,
-                             fa, fb, geom, n, org, dirA, odA, dirB, odB, idxA, distA, idxB, distB, exactEvals, liveA, liveB);
-        }
-        __syncwarp();
-        if ((threadIdx.x & 31u) == 0u)
-            mbar_arrive(R.emptyBar + buf);
-    }
-    R.seq += nChunks;
+    stream_pass(fs, R, warpLive, liveWarps, [&](const FilterPair *rec, const uint32_t *slotIdx, uint32_t span) {
+        filter_span_cam2(rec, slotIdx, span, fa, fb, geom, n, org, dirA, odA, dirB, odB, idxA, distA, idxB, distB, exactEvals, liveA, liveB);
+    });
 }
 
 // cone_collect (spt_filter.cuh) over the streamed list: ONE pass of the whole blob through the ring per launch, every warp
-// appending the survivors of each chunk to its lanes' lists.  Same calling rules as streamed_closest_hit.
+// appending the survivors of each chunk to its lanes' lists.
 template <int THREADS>
 __device__ __forceinline__ void streamed_cone_collect(const FilterScene &fs, uint32_t n, V3 dir, V3 org, StreamRing &R, bool live, bool warpLive,
-                                                      uint16_t *list, uint32_t cap, uint32_t &count)
+                                                      uint32_t liveWarps, uint16_t *list, uint32_t cap, uint32_t &count)
 {
-    constexpr uint32_t kAhead = kStages - 1u;
-    uint32_t const nChunks = (fs.nSlots + kChunkSlots - 1u) / kChunkSlots;
-    if (threadIdx.x == 0)
-        for (uint32_t c = 0; c < kAhead && c < nChunks; ++c)
-            stream_produce(fs, R.ring, R.fullBar, R.emptyBar, R.seq + c, c);
     FilterRay const fr = make_filter_ray_cam(dir, vdot(org, dir), fs.epsTCam);
-    for (uint32_t c = 0; c < nChunks; ++c)
-    {
-        if (threadIdx.x == 0 && c + kAhead < nChunks)
-            stream_produce(fs, R.ring, R.fullBar, R.emptyBar, R.seq + c + kAhead, c + kAhead);
-        uint32_t const buf = (R.seq + c) % kStages, use = (R.seq + c) / kStages;
-        mbar_wait(R.fullBar + buf, use & 1u);
-        if (warpLive)
-        {
-            const unsigned char *chunk = R.ring + buf * kChunkBytes;
-            uint32_t const span = min(kChunkSlots, fs.nSlots - c * kChunkSlots);
-            cone_collect<THREADS>(reinterpret_cast<const FilterPair *>(chunk), reinterpret_cast<const uint32_t *>(chunk + kChunkRecordBytes), span,
-                                  fr, n, live, list, cap, count);
-        }
-        __syncwarp();
-        if ((threadIdx.x & 31u) == 0u)
-            mbar_arrive(R.emptyBar + buf);
-    }
-    R.seq += nChunks;
+    stream_pass(fs, R, warpLive, liveWarps, [&](const FilterPair *rec, const uint32_t *slotIdx, uint32_t span) {
+        cone_collect<THREADS>(rec, slotIdx, span, fr, n, live, list, cap, count);
+    });
 }
 
 __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_streamed(const __grid_constant__ TraceParams p)
 {
     extern __shared__ __align__(128) unsigned char ring[];
     __shared__ __align__(8) uint64_t fullBar[kStages];
-    __shared__ __align__(8) uint64_t emptyBar[kStages];
+    __shared__ uint32_t released[kStages];
     __shared__ ShellSlots shellSlots[kBlockThreads / 32];
     ShellSlots &slots = shellSlots[threadIdx.x >> 5];
 
     StreamRing R;
-    stream_ring_init(R, ring, fullBar, emptyBar);
+    stream_ring_init(R, ring, fullBar, released);
 
     const float4 *geom = p.geom; // exact geometry through L1/L2: only candidates and shading touch it
     FilterScene const fs = p.filter;
@@ -268,12 +251,13 @@ __global__ void __launch_bounds__(kBlockThreads, SPT_MIN_BLOCKS) trace_streamed(
                 ++L.sample;
             }
         }
-        // also the barrier after which no warp reads the ring any more: the producer may start over
-        if (!__syncthreads_or(live ? 1 : 0))
-            break;
+        // also the barrier after which no warp reads the ring any more: the next pass may start
         bool const warpLive = __any_sync(0xffffffffu, live);
+        uint32_t const liveWarps = stream_live_warps(warpLive);
+        if (!liveWarps)
+            break;
 
-        uint32_t const minIndex = streamed_closest_hit<false>(fs, geom, p.n, L.dir, L.org, R, exactEvals, live, warpLive);
+        uint32_t const minIndex = streamed_closest_hit<false>(fs, geom, p.n, L.dir, L.org, R, exactEvals, live, warpLive, liveWarps);
         segments += live ? 1u : 0u;
         shade_step(p, geom, L, minIndex, dropped, live, slots);
     }

@@ -20,6 +20,6 @@ for f in sorted(glob.glob('$o/bench_n*.json')):
     except Exception as e:
         print(f,'FAILED',e); print(open(f.replace('.json','.err')).read()[-1500:])
 P
-simplepathtracer_b200/host/spt_headless --scene random --seed 1 --width 1920 --height 1080 --spp 256 --depth 50 --tracer task --gpus $N --out $o/h_n.bmp | tail -2
-simplepathtracer_b200/host/spt_headless --scene random --seed 1 --width 1920 --height 1080 --spp 256 --depth 50 --tracer task --out $o/h_1.bmp | tail -2
+simplepathtracer_b200/host/spt_headless --scene random --seed 1 --width 1920 --height 1080 --spp 1024 --depth 50 --tracer task --gpus $N --repeat 3 --out $o/h_n.bmp | tail -7
+simplepathtracer_b200/host/spt_headless --scene random --seed 1 --width 1920 --height 1080 --spp 1024 --depth 50 --tracer task --repeat 3 --out $o/h_1.bmp | tail -7
 rm -f $o/*.bmp

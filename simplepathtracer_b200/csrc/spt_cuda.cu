@@ -768,6 +768,7 @@ int upload_scene(SptContext *c, const HostScene &hs)
     c->hostGeom = hs.slotGeom;
     c->filter.pairs = c->dPairs;
     c->filter.nSlots = hs.nSlots;
+    c->filter.shape = spt::span_shape(hs.nSlots);
     c->filter.slotIdx = reinterpret_cast<const uint32_t *>(c->dPairs + hs.nSlots / 2);
     c->filter.bigIdx = c->dBigIdx;
     c->filter.nBig = uint32_t(hs.big.size());

@@ -53,6 +53,23 @@ struct __align__(16) FilterPair
     float cx[2], cy[2], cz[2], nk[2];
 };
 
+// Loop shape of a span of slots (a multiple of kQuadSpheres): mask words, words with all 16 records, quads (4 records) in the
+// last word.  For the resident list it is computed on the host and read from the kernel's parameter bank: ncu on the bounce kernel
+// showed ptxas recomputing it from nSlots in vector registers on every trip of the word loop when registers are short (12 control
+// instructions per trip instead of 3).
+struct SpanShape
+{
+    uint32_t nWords, nFull, tailQuads;
+};
+__host__ __device__ __forceinline__ SpanShape span_shape(uint32_t spanSlots)
+{
+    SpanShape s;
+    s.nWords = (spanSlots + 31u) / 32u;
+    s.tailQuads = s.nWords ? (spanSlots - (s.nWords - 1u) * 32u) / 8u : 0u; // 1..4 quads in the last word
+    s.nFull = s.tailQuads == 4u ? s.nWords : (s.nWords ? s.nWords - 1u : 0u); // words with all 16 records
+    return s;
+}
+
 // The filter works on SLOTS: the filterable spheres in index order, compacted (the big spheres take no slot)
 // and padded with never-pass records to a multiple of kQuadSpheres.  slotIdx maps a slot back to its sphere
 // index (0xFFFFFFFF for padding).  `pairs` and `slotIdx` are ONE device allocation ([records | indices]) so that a
@@ -62,6 +79,7 @@ struct FilterScene
     const FilterPair *pairs;  // nSlots / 2 records
     const uint32_t *slotIdx;  // nSlots entries
     uint32_t nSlots;          // multiple of kQuadSpheres
+    SpanShape shape;          // span_shape(nSlots), filled on the host
     const uint32_t *bigIdx;   // spheres always evaluated exactly
     uint32_t nBig;
     float amax;               // max |C_i| over filtered spheres
@@ -251,13 +269,11 @@ __device__ __forceinline__ bool resolve_now(uint32_t pend, uint32_t w, uint32_t 
 }
 
 template <bool CAM = false, typename GeomPtr>
-__device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_t *slotIdx, uint32_t spanSlots, const FilterRay &fr,
+__device__ __forceinline__ void filter_span(const FilterPair *rec, const uint32_t *slotIdx, SpanShape const shape, const FilterRay &fr,
                                             GeomPtr geom, uint32_t n, V3 dir, V3 org, float od, uint32_t &minIndex,
                                             float &minDistanceSq, uint32_t &exactEvals, bool live)
 {
-    uint32_t const nWords = (spanSlots + kWordSpheres - 1u) / kWordSpheres;
-    uint32_t const tailQuads = (spanSlots - (nWords - 1u) * kWordSpheres) / kQuadSpheres; // 1..4 quads in the last word
-    uint32_t const nFull = tailQuads == kWordSpheres / kQuadSpheres ? nWords : nWords - 1u; // words with all 16 records
+    uint32_t const nWords = shape.nWords, tailQuads = shape.tailQuads, nFull = shape.nFull;
     // candidate masks of the last (up to kSuperWords + 1) words filtered, newest in c0 (a shift register: no per-word selects)
     uint32_t c0 = 0u, c1 = 0u, c2 = 0u, c3 = 0u, c4 = 0u, pend = 0u;
 #pragma unroll 1
@@ -369,7 +385,7 @@ __device__ __forceinline__ uint32_t closest_hit_filtered(const FilterScene &fs, 
     float const od = vdot(org, dir);
     exact_big_spheres(fs, geom, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
     FilterRay const fr = make_filter_ray(dir, org, od, fs.amax, fs.nearOO);
-    filter_span(fs.pairs, fs.slotIdx, fs.nSlots, fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
+    filter_span(fs.pairs, fs.slotIdx, fs.shape, fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
     return minIndex;
 }
 
@@ -399,14 +415,12 @@ __device__ __forceinline__ void filter_pair_cam2(const FilterPair *__restrict__ 
 
 // filter_span for two camera rays (A, B) sharing the origin; liveA / liveB as `live` in filter_span
 template <typename GeomPtr>
-__device__ __forceinline__ void filter_span_cam2(const FilterPair *rec, const uint32_t *slotIdx, uint32_t spanSlots, const FilterRay &fa,
+__device__ __forceinline__ void filter_span_cam2(const FilterPair *rec, const uint32_t *slotIdx, SpanShape const shape, const FilterRay &fa,
                                                  const FilterRay &fb, GeomPtr geom, uint32_t n, V3 org, V3 dirA, float odA, V3 dirB,
                                                  float odB, uint32_t &minA, float &distA, uint32_t &minB, float &distB,
                                                  uint32_t &exactEvals, bool liveA, bool liveB)
 {
-    uint32_t const nWords = (spanSlots + kWordSpheres - 1u) / kWordSpheres;
-    uint32_t const tailQuads = (spanSlots - (nWords - 1u) * kWordSpheres) / kQuadSpheres;
-    uint32_t const nFull = tailQuads == kWordSpheres / kQuadSpheres ? nWords : nWords - 1u;
+    uint32_t const nWords = shape.nWords, tailQuads = shape.tailQuads, nFull = shape.nFull;
     uint32_t a0 = 0u, a1 = 0u, a2 = 0u, a3 = 0u, a4 = 0u, b0 = 0u, b1 = 0u, b2 = 0u, b3 = 0u, b4 = 0u, pend = 0u;
 #pragma unroll 1
     for (uint32_t w = 0; w < nWords;)
@@ -523,7 +537,7 @@ __device__ __forceinline__ uint32_t closest_hit_camera(const FilterScene &fs, Ge
     float const od = vdot(org, dir);
     exact_big_spheres(fs, geom, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
     FilterRay const fr = make_filter_ray_cam(dir, od, fs.epsTCam);
-    filter_span<true>(fs.pairs, fs.slotIdx, fs.nSlots, fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
+    filter_span<true>(fs.pairs, fs.slotIdx, fs.shape, fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
     return minIndex;
 }
 
@@ -538,7 +552,7 @@ __device__ __forceinline__ void closest_hit_camera2(const FilterScene &fs, GeomP
     exact_big_spheres(fs, geom, dirA, org, odA, idxA, distA, exactEvals, liveA);
     exact_big_spheres(fs, geom, dirB, org, odB, idxB, distB, exactEvals, liveB);
     FilterRay const fa = make_filter_ray_cam(dirA, odA, fs.epsTCam), fb = make_filter_ray_cam(dirB, odB, fs.epsTCam);
-    filter_span_cam2(fs.pairs, fs.slotIdx, fs.nSlots, fa, fb, geom, n, org, dirA, odA, dirB, odB, idxA, distA, idxB, distB, exactEvals, liveA,
+    filter_span_cam2(fs.pairs, fs.slotIdx, fs.shape, fa, fb, geom, n, org, dirA, odA, dirB, odB, idxA, distA, idxB, distB, exactEvals, liveA,
                      liveB);
 }
 

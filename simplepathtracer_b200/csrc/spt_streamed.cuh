@@ -155,7 +155,7 @@ __device__ __forceinline__ uint32_t streamed_closest_hit(const FilterScene &fs, 
     exact_big_spheres(fs, geom, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
     FilterRay const fr = CAM ? make_filter_ray_cam(dir, od, fs.epsTCam) : make_filter_ray(dir, org, od, fs.amax, fs.nearOO);
     stream_pass(fs, R, warpLive, liveWarps, [&](const FilterPair *rec, const uint32_t *slotIdx, uint32_t span) {
-        filter_span<CAM>(rec, slotIdx, span, fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
+        filter_span<CAM>(rec, slotIdx, span_shape(span), fr, geom, n, dir, org, od, minIndex, minDistanceSq, exactEvals, live);
     });
     return minIndex;
 }
@@ -173,7 +173,7 @@ __device__ __forceinline__ void streamed_closest_hit_cam2(const FilterScene &fs,
     exact_big_spheres(fs, geom, dirB, org, odB, idxB, distB, exactEvals, liveB);
     FilterRay const fa = make_filter_ray_cam(dirA, odA, fs.epsTCam), fb = make_filter_ray_cam(dirB, odB, fs.epsTCam);
     stream_pass(fs, R, warpLive, liveWarps, [&](const FilterPair *rec, const uint32_t *slotIdx, uint32_t span) {
-        filter_span_cam2(rec, slotIdx, span, fa, fb, geom, n, org, dirA, odA, dirB, odB, idxA, distA, idxB, distB, exactEvals, liveA, liveB);
+        filter_span_cam2(rec, slotIdx, span_shape(span), fa, fb, geom, n, org, dirA, odA, dirB, odB, idxA, distA, idxB, distB, exactEvals, liveA, liveB);
     });
 }
 

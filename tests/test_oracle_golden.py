@@ -157,3 +157,14 @@ def test_shell_acceptance_needs_no_square_root():
     rng = np.random.default_rng(0)
     xs = rng.uniform(0, 0.75, 2_000_000).astype(np.float32)
     assert np.array_equal(np.sqrt(xs) < np.float32(0.5), xs < q)
+
+
+def test_shell_fixed_point_fields_through_the_mantissa():
+    """spt_device.cuh's shell_attempt builds k * 2^-21 - 0.5 (2^-22 for z) by placing k in the mantissa of a float in [1, 2) and
+    subtracting 1.5 instead of convert * scale + min.  Both are exact, so they agree for EVERY k, the +0 at the midpoint
+    included -- the definition the oracle implements (canonical * (max - min) + min) is unchanged."""
+    for bits, shift in ((21, 2), (22, 1)):
+        k = np.arange(1 << bits, dtype=np.uint32)
+        want = (k.astype(np.float32) * np.float32(2.0 ** -bits) + np.float32(-0.5)).astype(np.float32)
+        got = ((np.uint32(0x3F800000) | (k << np.uint32(shift))).view(np.float32) + np.float32(-1.5)).astype(np.float32)
+        assert np.array_equal(want.view(np.uint32), got.view(np.uint32))

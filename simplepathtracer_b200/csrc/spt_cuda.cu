@@ -419,10 +419,14 @@ int launch_trace(SptContext *c, const SptCamera *cam, const SptParams *prm, SptS
         uint32_t const ctas = std::min<uint32_t>(tiles, uint32_t(std::max(perSm, 1)) * uint32_t(c->prop.multiProcessorCount)); \
         kernel<<<ctas, block, (SMEM), c->stream>>>(p, tileCounter);                                                  \
     } while (0)
-        if (geomBytes + pairBytes <= wfBudget)
+        if ((prm->flags & SPT_FLAG_STREAMED) && c->filter.nSlots > 0)
+            SPT_LAUNCH_WF(3, spt::kStreamSmemBytes);
+        else if (geomBytes + pairBytes <= wfBudget)
             SPT_LAUNCH_WF(2, geomBytes + pairBytes);
         else if (pairBytes <= wfBudget)
             SPT_LAUNCH_WF(1, pairBytes);
+        else if (c->filter.nSlots > 0)
+            SPT_LAUNCH_WF(3, spt::kStreamSmemBytes); // config 5: the blob streams through the chunk ring
         else
             SPT_LAUNCH_WF(0, 0);
 #undef SPT_LAUNCH_WF

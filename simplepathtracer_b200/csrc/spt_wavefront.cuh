@@ -9,6 +9,7 @@
 //     atomic counter until the segment is exhausted;
 //   * path state lives in shared memory as SoA, one slot per pixel of the tile (one sample in flight per
 //     pixel, so per-pixel sums are added in sample order exactly as in the megakernel and the oracle);
+//   * lists too long for shared memory stream through the megakernel family's TMA chunk ring (STAGE 3);
 //   * every pass builds the queues with warp ballot + popc prefix + one shared atomic per warp, and the
 //     stages run over the COMPACTED queues: thread k takes entry k, so all lanes of a warp intersect, or run
 //     the same material handler, together.
@@ -19,6 +20,7 @@
 #pragma once
 
 #include "spt_kernels.cuh"
+#include "spt_streamed.cuh"
 
 namespace spt
 {
@@ -78,6 +80,14 @@ __global__ void __launch_bounds__(kBlockThreads, 2) trace_wavefront(const __grid
         stage_scene_tma(smemRaw, p.filter.pairs, pairBytes, nullptr, nullptr, 0, &mbar);
         rebase_filter(fs, smemRaw);
     }
+    // STAGE 3: lists beyond shared memory stream through the TMA chunk ring (spt_streamed.cuh), as in the megakernel family.  The
+    // intersect stage is a CTA affair anyway (thread k traces ray-queue entry k between two barriers), and the warps that hold
+    // rays are known without counting: the first ceil(nRay / 32).
+    __shared__ __align__(8) uint64_t fullBar[kStages];
+    __shared__ uint32_t released[kStages];
+    StreamRing R{};
+    if (STAGE == 3)
+        stream_ring_init(R, smemRaw, fullBar, released);
 
     uint32_t const tid = threadIdx.x;
     uint32_t const segW = p.xEnd - p.xBegin, segH = p.yEnd - p.yBegin;
@@ -152,7 +162,8 @@ __global__ void __launch_bounds__(kBlockThreads, 2) trace_wavefront(const __grid
                 uint32_t const s = mine ? S.rayQ[tid] : 0u;
                 V3 const d = mine ? v3(S.dx[s], S.dy[s], S.dz[s]) : v3(0.f, 0.f, 1.f);
                 V3 const o = mine ? v3(S.ox[s], S.oy[s], S.oz[s]) : v3(0.f, 0.f, 0.f);
-                uint32_t const idx = closest_hit_filtered(fs, geom, p.n, d, o, exactEvals, mine);
+                uint32_t const idx = STAGE == 3 ? streamed_closest_hit<false>(fs, geom, p.n, d, o, R, exactEvals, mine, (tid & ~31u) < nRay, (nRay + 31u) / 32u)
+                                                : closest_hit_filtered(fs, geom, p.n, d, o, exactEvals, mine);
                 segments += mine ? 1u : 0u;
                 // ---- classify into the four material queues (TraceAndSampleColor(task, tasks)) ----
                 uint32_t m = 0;

@@ -301,15 +301,17 @@ def test_converged_render_matches_reference_own_render(tracer, cam, scene_init, 
 # ----------------------------------------------------------------------------- wavefront variant
 @pytest.mark.parametrize("which", ["init", "random"])
 @pytest.mark.parametrize("pass_cap", [0, 10, 1])
-def test_wavefront_variant_bit_exact(tracer, oracle, cam, scene_init, scene_random, which, pass_cap):
+@pytest.mark.parametrize("feed", [0, spt.FLAG_STREAMED])
+def test_wavefront_variant_bit_exact(tracer, oracle, cam, scene_init, scene_random, which, pass_cap, feed):
     """The wavefront kernel (persistent CTAs, per-material queues) computes the same per-sample radiance
-    and the same in-order per-pixel sums as the megakernel and the oracle."""
+    and the same in-order per-pixel sums as the megakernel and the oracle -- with the list resident in shared memory and
+    with its intersect stage fed by the TMA chunk ring (what config 5's list takes)."""
     scene = scene_init if which == "init" else scene_random
     w, h, spp, depth = 100, 45, 6, 8  # not a multiple of the 32x8 tile
     tracer.set_scene(scene)
     tracer.reset_counters()
     rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=pass_cap, seed=21, want_accum=True, variant=spt.WAVEFRONT,
-                             flags=spt.FLAG_COUNTERS)
+                             flags=spt.FLAG_COUNTERS | feed)
     c = tracer.counters()
     oacc, octr = oracle.render_accum(scene, cam, w, h, spp, depth, pass_cap=pass_cap, seed=21)
     assert_accum_equal(acc, oacc)

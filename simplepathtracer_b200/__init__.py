@@ -28,6 +28,7 @@ from .binding import (  # noqa: F401
     FLAG_SINGLE_KERNEL,
     FLAG_SERIAL_CHUNKS,
     FLAG_OWN_PIXELS,
+    FLAG_GRID,
     DIFFUSE,
     REFLECTIVE,
     REFRACTIVE,

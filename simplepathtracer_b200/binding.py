@@ -23,6 +23,7 @@ MEGAKERNEL, WAVEFRONT = 0, 1
 FLAG_STRICT_LOOP, FLAG_COUNTERS, FLAG_CROSS_CHECK, FLAG_STREAMED, FLAG_RESIDENT, FLAG_SPLIT, FLAG_SINGLE_KERNEL = 1, 2, 4, 8, 16, 32, 64
 FLAG_SERIAL_CHUNKS = 128
 FLAG_OWN_PIXELS = 256
+FLAG_GRID = 512
 SKYBOX, REFLECTIVE, REFRACTIVE, DIFFUSE = 0, 1, 2, 3  # include/Definitions.hpp:7-13
 
 f32p = C.POINTER(C.c_float)

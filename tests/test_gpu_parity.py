@@ -841,3 +841,62 @@ def test_pixel_cone_lists_streamed_and_dense(tracer, oracle, cam):
         _, acc = tracer.render(cam, w, h, 3, 6, pass_cap=10, seed=2, want_accum=True, flags=spt.FLAG_STREAMED)
         oacc, _ = oracle.render_accum(scene, cam, w, h, 3, 6, pass_cap=10, seed=2)
         assert_accum_equal(acc, oacc)
+
+
+# ----------------------------------------------------------------------------- SPT_FLAG_GRID (opt-in acceleration structure)
+def _probe_rays(rng, count, centre, spread, far):
+    d = rng.normal(size=(count, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True).astype(np.float32)
+    o = (rng.uniform(-1, 1, size=(count, 3)) * np.array(spread) + np.array(centre)).astype(np.float32)
+    # a share of axis-parallel directions (the walk's degenerate axes), of origins on the ground far outside the grid's
+    # reach (they take the fattened-box test or the full list) aimed back at the scene, and of grazing low rays
+    k = count // 8
+    d[:k] = np.eye(3, dtype=np.float32)[rng.integers(0, 3, k)] * rng.choice([-1, 1], size=(k, 1)).astype(np.float32)
+    o[k:2 * k] = (rng.uniform(-1, 1, size=(k, 3)) * np.array([far, 0, far]) + np.array([0, 0.05, 0])).astype(np.float32)
+    aim = (np.array(centre) + rng.uniform(-1, 1, size=(k, 3)) * np.array(spread) - o[k:2 * k]).astype(np.float32)
+    d[k:2 * k] = aim / np.linalg.norm(aim, axis=1, keepdims=True).astype(np.float32)
+    d[2 * k:3 * k, 1] *= np.float32(0.02)
+    d[2 * k:3 * k] /= np.linalg.norm(d[2 * k:3 * k], axis=1, keepdims=True).astype(np.float32)
+    return d, o
+
+
+@pytest.mark.parametrize("which", ["init", "random", "metal_glass", "lattice"])
+def test_grid_closest_hit_equals_the_linear_loop(tracer, oracle, scene_init, scene_random, scene_metal_glass, scene_lattice, which):
+    """SPT_FLAG_GRID: the closest hit found by walking the uniform grid is FindClosestIntersectionSphere's for every ray --
+    random, axis-parallel, grazing, starting inside spheres, starting thousands of units out on the ground -- on the device
+    against the strict loop (cross-check) and against the oracle."""
+    scene, centre, spread, far = {"init": (scene_init, (0, 1, 0), (3, 2, 3), 400.0), "random": (scene_random, (0, 2, 8), (25, 3, 14), 3000.0),
+                                  "metal_glass": (scene_metal_glass, (0, 1, 12), (30, 2, 20), 3000.0),
+                                  "lattice": (scene_lattice, (0, 1, 80), (85, 1.5, 85), 5000.0)}[which]
+    tracer.set_scene(scene)
+    rng = np.random.default_rng(77)
+    d, o = _probe_rays(rng, 40000 if which != "lattice" else 24000, centre, spread, far)
+    got, evals = tracer.closest_hit(d, o, flags=spt.FLAG_GRID | spt.FLAG_CROSS_CHECK, want_evals=True)
+    assert not (got == 0xFFFFFFFF).any()
+    assert np.array_equal(got, oracle.closest_hit_many(scene, d, o))
+    if which == "lattice":  # the point of it: a few dozen exact evaluations per ray, not 16 384 (far origins aimed at the scene take them all)
+        assert np.median(evals) < 64 and (evals >= 16383).mean() < 0.2
+
+
+@pytest.mark.parametrize("pass_cap", [0, 10])
+def test_grid_render_keeps_the_bits(tracer, oracle, cam, scene_random, scene_metal_glass, scene_lattice, pass_cap, monkeypatch):
+    """Renders with the bounce kernel on the grid: the oracle's accumulators and counters (segments and tests still count the
+    reference's work), resident and ring-fed camera kernels, both sample policies, several chunks, another eye."""
+    for scene, (w, h, spp, depth) in ((scene_random, (107, 61, 6, 12)), (scene_metal_glass, (50, 29, 4, 50)), (scene_lattice, (64, 40, 2, 16))):
+        tracer.set_scene(scene)
+        oacc, octr = oracle.render_accum(scene, cam, w, h, spp, depth, pass_cap=pass_cap, seed=41)
+        for chunk, own in ((0, 0), (3, 0), (0, spt.FLAG_OWN_PIXELS)):
+            monkeypatch.setattr(tracer, "split_chunk", chunk)
+            tracer.reset_counters()
+            rgb, acc = tracer.render(cam, w, h, spp, depth, pass_cap=pass_cap, seed=41, want_accum=True, flags=spt.FLAG_GRID | own | spt.FLAG_COUNTERS)
+            c = tracer.counters()
+            assert_accum_equal(acc, oacc)
+            assert np.array_equal(rgb, oracle.resolve(oacc))
+            assert c["segments"] == octr["segments"] and c["dropped"] == octr["dropped"]
+    monkeypatch.setattr(tracer, "split_chunk", 0)
+    tracer.set_scene(scene_random)
+    for eye in ((3.0, 2.5, -6.0), (0.0, 400.0, -1500.0)):
+        cam2 = oracle.camera(eye=eye, look=(0, 1, 5))
+        _, acc = tracer.render(cam2, 90, 50, 4, 8, pass_cap=pass_cap, seed=3, want_accum=True, flags=spt.FLAG_GRID)
+        oacc, _ = oracle.render_accum(scene_random, cam2, 90, 50, 4, 8, pass_cap=pass_cap, seed=3)
+        assert_accum_equal(acc, oacc)

@@ -435,6 +435,12 @@ def run_native_arm(args, wl):
         workloads = {}
         for name in ("c4", "c5"):
             workloads[name] = short_leg(pt, spt, torch, cam, WORKLOADS[name], peak, staging)
+        # the same two with SPT_FLAG_GRID: the OPT-IN acceleration structure of SURVEY 8(f)-4 (same bits; not the linear loop the
+        # roofline is defined on -- its "roofline" fields only say how much faster than the reference's work rate it runs)
+        for name in ("c4", "c5"):
+            leg = short_leg(pt, spt, torch, cam, WORKLOADS[name], peak, staging, extra_flags=spt.FLAG_GRID)
+            leg["note"] = "SPT_FLAG_GRID (opt-in uniform grid, bit-identical results); fractions are algorithmic work rates of the LINEAR loop, not kernel utilisation"
+            workloads[name + "_grid"] = leg
         pt.set_scene(scene)
 
     # ---- CPU baseline (rank 0, N == 1 only) ---------------------------------------------------------
@@ -465,7 +471,7 @@ def run_native_arm(args, wl):
         dist.destroy_process_group()
 
 
-def short_leg(pt, spt, torch, cam, wl, peak, staging):
+def short_leg(pt, spt, torch, cam, wl, peak, staging, extra_flags=0):
     """One warm-up and one timed render of a stress configuration (BASELINE.json configs 4 / 5) on the context of the headline:
     Msamples/s with the scene resident, the roofline fractions, and what the scene costs to set up (host generation + upload)."""
     t0 = time.perf_counter()
@@ -482,7 +488,8 @@ def short_leg(pt, spt, torch, cam, wl, peak, staging):
         accum.zero_()
         pt.reset_counters()
         ev[0].record()
-        pt.accumulate(cam, W, H, 0, spp, depth, accum, pass_cap=PASS_CAP, seed=SEED, flags=spt.FLAG_COUNTERS | (spt.FLAG_SERIAL_CHUNKS if rep == 0 else 0))
+        pt.accumulate(cam, W, H, 0, spp, depth, accum, pass_cap=PASS_CAP, seed=SEED,
+                      flags=spt.FLAG_COUNTERS | extra_flags | (spt.FLAG_SERIAL_CHUNKS if rep == 0 else 0))
         ev[1].record()
         torch.cuda.synchronize()
         ms = ev[0].elapsed_time(ev[1])

@@ -69,6 +69,8 @@ inline void SetDevices(std::vector<int> const &devices)
     GetState().devices = devices;
 }
 inline void SetSeed(uint64_t seed) { GetState().seed = seed; }
+// SPT_FLAG_* for every render that follows (e.g. SPT_FLAG_GRID: the opt-in acceleration structure for long sphere lists)
+inline void SetFlags(uint32_t flags) { GetState().flags = flags; }
 // first-hit staging budget of split rendering per device, in bytes (spt_cuda_set_staging_limit); 0 = library default
 inline void SetStagingLimit(uint64_t bytes) { GetState().stagingLimit = bytes; }
 

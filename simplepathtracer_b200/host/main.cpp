@@ -17,6 +17,8 @@
 //                [--devices a,b,..]  the same with an explicit list of CUDA ordinals (an ordinal may repeat: several internal
 //                                    contexts on one GPU)
 //                [--staging-mib M]   first-hit staging budget of split rendering per device (default 8192)
+//                [--grid 1]          SPT_FLAG_GRID: closest hits through the library's uniform grid instead of the linear loop
+//                                    (opt-in, same image; for long sphere lists such as --scene lattice)
 #include "../../include/spt_host/Scene.hpp"
 #include "../../include/spt_host/SceneFile.hpp"
 #include "../../include/spt_host/SceneGenerators.hpp"
@@ -35,7 +37,7 @@ int main(int argc, char **argv)
 {
     std::string scene = "reference", tracer = "recursive", out;
     std::string pfm, hdr, checkpoint, dumpScene, deviceList;
-    uint32_t seed = 1, width = 1440, height = 1440, spp = 100, depth = 10, tiles = 1, progressive = 0, gpus = 1, stagingMib = 0, repeat = 1;
+    uint32_t seed = 1, width = 1440, height = 1440, spp = 100, depth = 10, tiles = 1, progressive = 0, gpus = 1, stagingMib = 0, repeat = 1, grid = 0;
     for (int i = 1; i + 1 < argc; i += 2)
     {
         std::string const k = argv[i], v = argv[i + 1];
@@ -51,6 +53,7 @@ int main(int argc, char **argv)
         else if (k == "--progressive") progressive = uint32_t(std::stoul(v));
         else if (k == "--pfm") pfm = v;
         else if (k == "--hdr") hdr = v;
+        else if (k == "--grid") grid = uint32_t(std::stoul(v));
         else if (k == "--repeat") repeat = std::max<uint32_t>(1u, uint32_t(std::stoul(v)));
         else if (k == "--dump-scene") dumpScene = v;
         else if (k == "--checkpoint") checkpoint = v;
@@ -89,6 +92,8 @@ int main(int argc, char **argv)
     }
     if (stagingMib)
         spt_cuda::SetStagingLimit(uint64_t(stagingMib) << 20);
+    if (grid)
+        spt_cuda::SetFlags(SPT_FLAG_GRID);
 
     if ((!pfm.empty() || !hdr.empty() || !checkpoint.empty()) && progressive == 0)
         progressive = 1;

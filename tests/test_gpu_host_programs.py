@@ -117,6 +117,18 @@ def test_headless_scene_file(tmp_path):
     assert sc.n == 501
 
 
+def test_headless_grid_flag_same_image(tmp_path):
+    """spt_headless --grid 1 (SPT_FLAG_GRID through spt_cuda::SetFlags): the 16 384-sphere lattice and the mirror / glass scene
+    render to the same bytes as through the linear loop."""
+    exe = os.path.join(ROOT, "simplepathtracer_b200", "host", "spt_headless")
+    for scene, depth in (("lattice", "16"), ("metalglass", "50")):
+        common = ["--scene", scene, "--seed", "5", "--width", "96", "--height", "56", "--spp", "4", "--depth", depth, "--tracer", "task"]
+        a, b = str(tmp_path / "lin.bmp"), str(tmp_path / "grid.bmp")
+        assert subprocess.run([exe, "--out", a] + common).returncode == 0
+        assert subprocess.run([exe, "--out", b, "--grid", "1"] + common).returncode == 0
+        assert open(a, "rb").read() == open(b, "rb").read()
+
+
 def test_headless_multi_device_and_checkpoint_identity(tmp_path, oracle):
     """spt_headless --devices a,b: ONE render spread over two device contexts by the library (RenderImageParallelMain's role,
     Renderer.hpp:257-302).  8 samples over 2 devices = sample ranges: the image is the in-order sum of two partial renders,

@@ -472,8 +472,8 @@ def test_full_size_render_equals_oracle_on_crops(tracer, oracle, cam, scene_rand
 @pytest.mark.parametrize("which", ["c3", "c4", "c5"])
 def test_full_size_properties(tracer, cam, scene_random, scene_metal_glass, scene_lattice, which):
     """Size-independent properties at BASELINE's full image sizes (the oracle comparison at these sizes is
-    test_full_size_render_equals_oracle_on_crops): every code path (split, single kernel, streamed, resident, strict loop,
-    wavefront) produces identical accumulators over the WHOLE image, sample ranges compose, and count + dropped == spp."""
+    test_full_size_render_equals_oracle_on_crops): every code path (split, single kernel, streamed, resident, the opt-in grid,
+    strict loop, wavefront) produces identical accumulators over the WHOLE image, sample ranges compose, and count + dropped == spp."""
     import torch
 
     scene, depth, spp = {"c3": (scene_random, 50, 4), "c4": (scene_metal_glass, 50, 4), "c5": (scene_lattice, 16, 1)}[which]
@@ -481,7 +481,7 @@ def test_full_size_properties(tracer, cam, scene_random, scene_metal_glass, scen
     tracer.set_scene(scene)
     outs = []
     for variant, flags in ((spt.MEGAKERNEL, 0), (spt.MEGAKERNEL, spt.FLAG_SINGLE_KERNEL), (spt.MEGAKERNEL, spt.FLAG_STREAMED),
-                           (spt.MEGAKERNEL, spt.FLAG_RESIDENT),
+                           (spt.MEGAKERNEL, spt.FLAG_RESIDENT), (spt.MEGAKERNEL, spt.FLAG_GRID),
                            (spt.MEGAKERNEL, spt.FLAG_STRICT_LOOP), (spt.WAVEFRONT, 0)):
         if which == "c5" and flags == spt.FLAG_STRICT_LOOP:  # the strict loop over 16k spheres at full HD is minutes: use a band of it
             continue

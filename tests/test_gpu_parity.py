@@ -878,6 +878,37 @@ def test_grid_closest_hit_equals_the_linear_loop(tracer, oracle, scene_init, sce
         assert np.median(evals) < 64 and (evals >= 16383).mean() < 0.2
 
 
+def test_grid_far_from_the_world_origin_and_degenerate_scenes(tracer, oracle, scene_random):
+    """The grid's paddings grow with the coordinates (the float test is sloppier far from the world origin): the random scene
+    moved 2 500 units away -- float spacing 2.4e-4 there, every discriminant a difference of numbers around 1e7 -- still gives
+    the strict loop's and the oracle's answers; so do a scene of one small sphere and one of coincident spheres (ties)."""
+    rng = np.random.default_rng(91)
+    moved = spt.Scene.of(scene_random)
+    moved = spt.Scene(moved.centers.copy(), moved.radii.copy(), moved.materials.copy(), moved.colors.copy(), moved.fuzz.copy())
+    small = moved.radii < 64
+    moved.centers[small, 0] += np.float32(1800.0)
+    moved.centers[small, 2] += np.float32(1700.0)
+    tracer.set_scene(moved)
+    d, o = _probe_rays(rng, 40000, (1800, 2, 1708), (25, 3, 14), 6000.0)
+    got = tracer.closest_hit(d, o, flags=spt.FLAG_GRID | spt.FLAG_CROSS_CHECK)
+    assert not (got == 0xFFFFFFFF).any()
+    assert np.array_equal(got, oracle.closest_hit_many(moved, d, o))
+    assert (got < moved.n).mean() > 0.3
+    # one filterable sphere; then eight coincident ones (the lowest index must win every tie)
+    for count in (1, 8):
+        centers = np.zeros((count + 1, 4), np.float32)
+        centers[0] = (0, -1000.5, 0, 0)
+        centers[1:] = (0.25, 1.0, 3.0, 0)
+        radii = np.array([1000.0] + [0.5] * count, np.float32)
+        sc = spt.Scene(centers, radii, np.full(count + 1, 3, np.uint8), np.full((count + 1, 4), 100, np.float32), np.zeros(count + 1, np.float32))
+        tracer.set_scene(sc)
+        d, o = _probe_rays(rng, 8000, (0.25, 1.0, 3.0), (3, 2, 3), 500.0)
+        got = tracer.closest_hit(d, o, flags=spt.FLAG_GRID | spt.FLAG_CROSS_CHECK)
+        assert not (got == 0xFFFFFFFF).any()
+        assert np.array_equal(got, oracle.closest_hit_many(sc, d, o))
+        assert set(np.unique(got)) <= {0, 1, count + 1}
+
+
 @pytest.mark.parametrize("pass_cap", [0, 10])
 def test_grid_render_keeps_the_bits(tracer, oracle, cam, scene_random, scene_metal_glass, scene_lattice, pass_cap, monkeypatch):
     """Renders with the bounce kernel on the grid: the oracle's accumulators and counters (segments and tests still count the

@@ -764,6 +764,9 @@ def test_multi_device_context_sample_ranges(tracer, oracle, cam, scene_random, n
         _, one = tracer_render_single(tracer, scene_random, cam, w, h, spp, depth)
         assert np.array_equal(acc[..., 3], one[..., 3])
         np.testing.assert_allclose(acc[..., :3], one[..., :3], rtol=2e-6, atol=0)
+        # the opt-in grid on every device of the context: the same sums
+        _, gacc = multi.render(cam, w, h, spp, depth, pass_cap=10, seed=6, want_accum=True, flags=spt.FLAG_GRID)
+        assert_accum_equal(gacc, want)
         # fewer samples than devices: AUTO falls back to bands, which are bit-identical to one GPU
         _, few = multi.render(cam, w, h, 1, depth, pass_cap=10, seed=6, want_accum=True)
         _, few1 = tracer.render(cam, w, h, 1, depth, pass_cap=10, seed=6, want_accum=True)

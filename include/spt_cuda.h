@@ -97,12 +97,13 @@ enum {
                                   other (no camera kernel under the tail of the previous bounce kernel), so that
                                   SptTiming.primary_ms / secondary_ms are the kernels' own durations */
     SPT_FLAG_GRID = 512u,      /* OPT-IN, outside the reference's algorithm (the acceleration structure for long lists): the
-                                  bounce kernel finds its closest hit by walking a uniform grid over the spheres (built at the first use
+                                  bounce kernel (and, for lists on the chunk ring, the camera kernel) finds its closest hit by walking a uniform grid over the spheres (built at the first use
                                   after spt_cuda_set_scene) and running the reference's exact sequence on the spheres of the cells the ray
                                   crosses, instead of testing every sphere.  Same result, bit for bit -- the grid only skips spheres that
                                   provably cannot pass, ties and the origin-inside rule are the exact sequence's own -- but NOT the
                                   linear loop the roofline is defined on: SptCounters.tests then still counts segments x spheres, the
-                                  work the reference would do.  Split rendering only; ignored by the other kernels. */
+                                  work the reference would do.  Split rendering only; ignored by the other kernels.  spt_cuda_closest_hit
+                                  takes it too (with SPT_FLAG_CROSS_CHECK: grid against strict loop, 0xFFFFFFFF on disagreement). */
     SPT_FLAG_OWN_PIXELS = 256u /* split rendering, comparison: every lane of the bounce kernel traces the samples of its own pixel
                                   only.  The default shares the samples of a warp's 8x4-pixel tile among its 32 lanes (a lane
                                   whose pixel is through takes samples of the pixel with the most left) and adds each pixel's
